@@ -380,7 +380,26 @@ int oracle_infdist(const double *B, int n, int m, const int64_t *u, int k, const
 /* ---- closest() ----
  * lat: n x m int64 row-major (rows = basis vectors), con: m x 2.  sol: n (uhat).  hist: n+1 counters, hist[kk] =
  * number of layer-distance solves with kk free coefficients.  stats[0..3] = pivots, refactors, quick prunes, cold
- * starts.  max_nodes = 0 means unlimited, otherwise stop with ORACLE_TRUNCATED after that many solves. */
+ * starts.  max_nodes = 0 means unlimited, otherwise stop with ORACLE_TRUNCATED after that many solves.
+ *
+ * Warm-start policy ("side chains"): at every level the siblings below the real centre xc and
+ * the siblings above it form two chains.  The first node of a chain starts from the parent's optimal basis with the
+ * level's coefficient fixed (lp_child); every later node of the chain starts from the final basis of the previous
+ * node on the same side.  The basis a node starts from is therefore a function of its path alone. */
+typedef struct { double *H; int *row, *sg; int init; } Chain;
+
+static void chain_store(Chain *ch, const LP *lp) {
+    const int K = lp->K, ld = lp->ld;
+    memcpy(ch->H, lp->H, (size_t)K * ld * sizeof(double));
+    memcpy(ch->row, lp->row, K * sizeof(int)); memcpy(ch->sg, lp->sg, K * sizeof(int));
+}
+static void chain_load(LP *lp, const Chain *ch, int K) {
+    const int ld = lp->ld;
+    lp->K = K;
+    memcpy(lp->H, ch->H, (size_t)K * ld * sizeof(double));
+    memcpy(lp->row, ch->row, K * sizeof(int)); memcpy(lp->sg, ch->sg, K * sizeof(int));
+}
+
 int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter_out,
                    uint64_t *nprune_out, uint64_t *hist, uint64_t *stats, uint64_t max_nodes) {
     if (n <= 0 || m <= 0 || m < n) return BLT_STATUS_INPUT_ERROR; /* closest.cc:173-177 */
@@ -395,17 +414,23 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
     int64_t *u = (int64_t *)calloc(n, sizeof(int64_t)), *uhat = (int64_t *)calloc(n, sizeof(int64_t));
     int64_t *step = (int64_t *)calloc(n, sizeof(int64_t));
     unsigned char *pruned = (unsigned char *)calloc(n, 1);
-    double *c = (double *)calloc(m, sizeof(double)), *cpar = (double *)calloc(m, sizeof(double));
-    /* level store: entry k holds the basis of LP(k-1) and the parent right-hand side of state k */
-    double **sH = (double **)calloc(n + 2, sizeof(double *)), **sc = (double **)calloc(n + 2, sizeof(double *));
-    int **srow = (int **)calloc(n + 2, sizeof(int *)), **ssg = (int **)calloc(n + 2, sizeof(int *));
+    double *c = (double *)calloc(m, sizeof(double));
+    /* per level k (state k solves LP(k-1)): two chains, the parent's right-hand side, the real centre, the side of
+     * the node we descended through */
+    Chain (*ch)[2] = (Chain (*)[2])calloc(n + 2, sizeof(Chain[2]));
+    double **cparL = (double **)calloc(n + 2, sizeof(double *));
+    double *xc = (double *)calloc(n + 2, sizeof(double));
+    int *curside = (int *)calloc(n + 2, sizeof(int));
     for (int k = 0; k <= n + 1; ++k) {
-        sH[k] = (double *)calloc((size_t)ld * ld, sizeof(double)); sc[k] = (double *)calloc(m, sizeof(double));
-        srow[k] = (int *)calloc(ld, sizeof(int)); ssg[k] = (int *)calloc(ld, sizeof(int));
+        cparL[k] = (double *)calloc(m, sizeof(double));
+        for (int s = 0; s < 2; ++s) {
+            ch[k][s].H = (double *)calloc((size_t)ld * ld, sizeof(double));
+            ch[k][s].row = (int *)calloc(ld, sizeof(int)); ch[k][s].sg = (int *)calloc(ld, sizeof(int));
+        }
     }
     uint64_t counter = 0, nprune = 0, nodes = 0;
     int rc = BLT_STATUS_OK;
-    int k = n, cold = 1;
+    int k = n;
     double xlast = 0.0, d = 0.0;
     if (hist) memset(hist, 0, (size_t)(n + 1) * sizeof(uint64_t));
 
@@ -421,17 +446,18 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
     }
     u[n - 1] = (int64_t)round(xlast);          /* set_index, closest.cc:74-82 */
     step[n - 1] = sgn(xlast - (double)u[n - 1]);
-    memcpy(cpar, p, (size_t)m * sizeof(double));
+    xc[n] = xlast;
+    memcpy(cparL[n], p, (size_t)m * sizeof(double));
 
     for (;;) {
         if (max_nodes && nodes >= max_nodes) { rc = ORACLE_TRUNCATED; goto done; }
         /* right-hand side of this node: c = cpar - u[k-1] * B[k-1]  (D2) */
         {
             const double mu = -(double)u[k - 1];
-            const double *Bk = B + (size_t)(k - 1) * m;
-            for (int j = 0; j < m; ++j) c[j] = fma(mu, Bk[j], cpar[j]);
+            const double *Bk = B + (size_t)(k - 1) * m, *cp = cparL[k];
+            for (int j = 0; j < m; ++j) c[j] = fma(mu, Bk[j], cp[j]);
         }
-        int status;
+        int status, side = 0;
         nodes++;
         if (hist) hist[k - 1]++;
         if (k == 1) { /* LP(0): plain max-abs */
@@ -439,23 +465,25 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
             for (int j = 0; j < m; ++j) if (fabs(c[j]) > d) d = fabs(c[j]);
             status = approximatelyLE(d, radius, DIST_EPS) ? NODE_EXPLORE : NODE_PRUNE;
         } else {
-            if (cold) {
-                if (lp_cold(lp, k, c) != 0) { rc = BLT_STATUS_LP_FAIL; goto done; }
-                cold = 0;
-            }
+            const int dir = sgn(xc[k] - (double)u[k - 1]);
+            side = dir > 0 ? 0 : 1;
+            if (!ch[k][side].init) {
+                if (k == n) {
+                    if (lp_cold(lp, k, c) != 0) { rc = BLT_STATUS_LP_FAIL; goto done; }
+                } else {
+                    chain_load(lp, &ch[k + 1][curside[k + 1]], k + 1);
+                    if (lp_child(lp, dir)) { rc = BLT_STATUS_LP_FAIL; goto done; }
+                }
+                ch[k][side].init = 1;
+            } else chain_load(lp, &ch[k][side], k);
             status = lp_solve(lp, c, radius, &d, &xlast);
             if (status == NODE_FAIL) { rc = BLT_STATUS_LP_FAIL; goto done; }
+            chain_store(&ch[k][side], lp);
         }
         if (status == NODE_PRUNE) {
             if (k < n) { /* ascend, closest.cc:110-122 */
-                if (pruned[k - 1]) {
-                    k++;
-                    /* restore the basis and parent rhs of the level we return to */
-                    lp->K = k;
-                    memcpy(lp->H, sH[k], (size_t)ld * ld * sizeof(double));
-                    memcpy(lp->row, srow[k], ld * sizeof(int)); memcpy(lp->sg, ssg[k], ld * sizeof(int));
-                    memcpy(cpar, sc[k], (size_t)m * sizeof(double));
-                } else pruned[k - 1] = 1;
+                if (pruned[k - 1]) k++;
+                else pruned[k - 1] = 1;
                 u[k - 1] += step[k - 1];
                 step[k - 1] = -step[k - 1] - sgn((double)step[k - 1]);
                 nprune++;
@@ -466,25 +494,20 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
         }
         /* explore */
         if (k > 1) { /* descend, closest.cc:88-95 */
-            memcpy(sH[k], lp->H, (size_t)ld * ld * sizeof(double));
-            memcpy(srow[k], lp->row, ld * sizeof(int)); memcpy(ssg[k], lp->sg, ld * sizeof(int));
-            memcpy(sc[k], cpar, (size_t)m * sizeof(double));
-            memcpy(cpar, c, (size_t)m * sizeof(double));
-            const int64_t un = (int64_t)round(xlast);
-            const int dir = sgn(xlast - (double)un);
+            curside[k] = side;
+            memcpy(cparL[k - 1], c, (size_t)m * sizeof(double));
+            xc[k - 1] = xlast;
             k--;
-            u[k - 1] = un; step[k - 1] = dir; pruned[k - 1] = 0;
-            if (k >= 2) { if (lp_child(lp, dir)) { rc = BLT_STATUS_LP_FAIL; goto done; } }
+            u[k - 1] = (int64_t)round(xlast);
+            step[k - 1] = sgn(xlast - (double)u[k - 1]);
+            pruned[k - 1] = 0;
+            ch[k][0].init = ch[k][1].init = 0;
         } else {
             memcpy(uhat, u, n * sizeof(int64_t)); /* record */
             if (oracle_check_soln(lat, con, n, m, u)) { rc = BLT_STATUS_OK; goto done; }
             if (n == 1) { rc = BLT_STATUS_OK; goto done; } /* D4 */
             /* explore(), closest.cc:99-104 */
             k = 2;
-            lp->K = 2;
-            memcpy(lp->H, sH[2], (size_t)ld * ld * sizeof(double));
-            memcpy(lp->row, srow[2], ld * sizeof(int)); memcpy(lp->sg, ssg[2], ld * sizeof(int));
-            memcpy(cpar, sc[2], (size_t)m * sizeof(double));
             u[1] += step[1];
             step[1] = -step[1] - sgn((double)step[1]);
         }
@@ -495,9 +518,12 @@ done:
     if (niter_out) *niter_out = counter;
     if (nprune_out) *nprune_out = nprune;
     if (stats) { stats[0] = lp->pivots; stats[1] = lp->refactors; stats[2] = lp->quick; stats[3] = lp->colds; }
-    for (int kk = 0; kk <= n + 1; ++kk) { free(sH[kk]); free(sc[kk]); free(srow[kk]); free(ssg[kk]); }
-    free(sH); free(sc); free(srow); free(ssg);
-    free(u); free(uhat); free(step); free(pruned); free(c); free(cpar); free(B); free(p);
+    for (int kk = 0; kk <= n + 1; ++kk) {
+        free(cparL[kk]);
+        for (int s = 0; s < 2; ++s) { free(ch[kk][s].H); free(ch[kk][s].row); free(ch[kk][s].sg); }
+    }
+    free(ch); free(cparL); free(xc); free(curside);
+    free(u); free(uhat); free(step); free(pruned); free(c); free(B); free(p);
     lp_free(lp);
     return rc;
 }
