@@ -1,0 +1,14 @@
+"""blt_b200 -- B200-native (sm_100a) implementation of BLT's lattice-search hot path.
+
+Host-side mirror of the reference's interface for that path:
+  closest()     <-> libblt/closest.h:50-54     (search over the LLL-reduced basis)
+  infdist()     <-> libblt/glpk_wrapper.h:26-34 (one layer-distance solve)
+  check_soln()  <-> libblt/closest.cc:330-340
+All of them call the CUDA kernels through the C ABI declared in include/bltcu.h.  There is no CPU fallback: if
+libbltcu.so is missing or no CUDA device is usable the calls raise / return BLT_STATUS_ERROR.
+"""
+from .search import (BLT_CHECK_SAT, BLT_CHECK_UNSAT, BLT_STATUS_ERROR, BLT_STATUS_INPUT_ERROR, BLT_STATUS_LP_FAIL,
+                     BLT_STATUS_OK, check_soln, closest, closest_dev, infdist, lib, version)
+
+__all__ = ["closest", "closest_dev", "infdist", "check_soln", "lib", "version", "BLT_STATUS_OK", "BLT_STATUS_ERROR",
+           "BLT_STATUS_LP_FAIL", "BLT_STATUS_INPUT_ERROR", "BLT_CHECK_SAT", "BLT_CHECK_UNSAT"]

@@ -1,0 +1,135 @@
+"""ctypes binding of include/bltcu.h (the product's C ABI).  Never imports oracle/."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import numpy as np
+
+BLT_STATUS_OK, BLT_STATUS_ERROR, BLT_STATUS_LP_FAIL, BLT_STATUS_INPUT_ERROR = 0, 1, 2, 3  # libblt/codes.h:5-11
+BLT_CHECK_SAT, BLT_CHECK_UNSAT = 10, 11                                                    # libblt/codes.h:13-18
+MAX_DIM = 96
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class Opts(ctypes.Structure):
+    _fields_ = [("device", ctypes.c_int), ("rank", ctypes.c_int), ("world", ctypes.c_int),
+                ("split_depth", ctypes.c_int), ("donate_min_level", ctypes.c_int), ("no_early_exit", ctypes.c_int),
+                ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int)]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("niter", ctypes.c_uint64), ("nprune", ctypes.c_uint64), ("nodes", ctypes.c_uint64),
+                ("pivots", ctypes.c_uint64), ("quick_prunes", ctypes.c_uint64), ("refactors", ctypes.c_uint64),
+                ("cold_starts", ctypes.c_uint64), ("donated", ctypes.c_uint64),
+                ("hist", ctypes.c_uint64 * (MAX_DIM + 1)), ("kernel_ms", ctypes.c_double),
+                ("total_ms", ctypes.c_double), ("found", ctypes.c_int), ("launches", ctypes.c_int),
+                ("warps", ctypes.c_int), ("ctas", ctypes.c_int), ("scratch_bytes", ctypes.c_uint64)]
+
+
+def lib() -> ctypes.CDLL:
+    """Loads blt_b200/lib/libbltcu.so.  Fails loudly when the CUDA library has not been built."""
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "lib", "libbltcu.so")
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                               "(nvcc, sm_100a).  blt_b200 has no CPU fallback.")
+        L = ctypes.CDLL(path)
+        i64p, u64p, f64p = (ctypes.POINTER(t) for t in (ctypes.c_int64, ctypes.c_uint64, ctypes.c_double))
+        L.bltcu_closest.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, u64p, u64p]
+        L.bltcu_closest.restype = ctypes.c_int
+        L.bltcu_closest_ex.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(Opts), i64p,
+                                       ctypes.POINTER(Stats)]
+        L.bltcu_closest_ex.restype = ctypes.c_int
+        L.bltcu_closest_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
+                                        ctypes.POINTER(Opts), i64p, ctypes.POINTER(Stats)]
+        L.bltcu_closest_dev.restype = ctypes.c_int
+        L.bltcu_check_soln.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
+        L.bltcu_check_soln.restype = ctypes.c_int
+        L.bltcu_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
+        L.bltcu_infdist.restype = ctypes.c_int
+        L.bltcu_release.argtypes = []
+        L.bltcu_release.restype = None
+        L.bltcu_version.argtypes = []
+        L.bltcu_version.restype = ctypes.c_char_p
+        _LIB = L
+    return _LIB
+
+
+def version() -> str:
+    return lib().bltcu_version().decode()
+
+
+def _i64(a):
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+def _p(a, t):
+    return a.ctypes.data_as(ctypes.POINTER(t))
+
+
+def _stats_dict(rc, sol, st, n):
+    return dict(rc=rc, sol=sol, niter=int(st.niter), nprune=int(st.nprune), nodes=int(st.nodes),
+                pivots=int(st.pivots), quick=int(st.quick_prunes), refactors=int(st.refactors),
+                colds=int(st.cold_starts), donated=int(st.donated),
+                hist=np.array(list(st.hist)[:n + 1], dtype=np.uint64), kernel_ms=float(st.kernel_ms),
+                total_ms=float(st.total_ms), found=bool(st.found), launches=int(st.launches), warps=int(st.warps),
+                ctas=int(st.ctas), scratch_bytes=int(st.scratch_bytes))
+
+
+def closest(lat, con, **opts):
+    """closest() of libblt/closest.h:50-54 on the GPU, host buffers in and out.
+    opts: device, rank, world, split_depth, donate_min_level, no_early_exit, warps_per_cta, ctas."""
+    lat = _i64(lat)
+    con = _i64(con)
+    if lat.ndim != 2 or con.ndim != 2 or con.shape[1] != 2 or con.shape[0] != lat.shape[1]:
+        return dict(rc=BLT_STATUS_INPUT_ERROR, sol=None, niter=0, nprune=0)  # closest.cc:173-177
+    n, m = lat.shape
+    if n == 0 or m == 0:
+        return dict(rc=BLT_STATUS_INPUT_ERROR, sol=None, niter=0, nprune=0)
+    sol = np.zeros(n, dtype=np.int64)
+    o = Opts(**opts)
+    st = Stats()
+    rc = lib().bltcu_closest_ex(_p(lat, ctypes.c_int64), _p(con, ctypes.c_int64), n, m, ctypes.byref(o),
+                                _p(sol, ctypes.c_int64), ctypes.byref(st))
+    return _stats_dict(rc, sol, st, n)
+
+
+def closest_dev(d_lat_ptr: int, d_con_ptr: int, n: int, m: int, **opts):
+    """Same search with lat/con already in device memory (raw device pointers, e.g. torch tensor .data_ptr())."""
+    sol = np.zeros(n, dtype=np.int64)
+    o = Opts(**opts)
+    st = Stats()
+    rc = lib().bltcu_closest_dev(ctypes.c_void_p(d_lat_ptr), ctypes.c_void_p(d_con_ptr), n, m, ctypes.byref(o),
+                                 _p(sol, ctypes.c_int64), ctypes.byref(st))
+    return _stats_dict(rc, sol, st, n)
+
+
+def check_soln(lat, con, u) -> bool:
+    """check_soln() of libblt/closest.cc:330-340 on the GPU."""
+    lat = _i64(lat)
+    con = _i64(con)
+    u = _i64(u)
+    n, m = lat.shape
+    ok = ctypes.c_int(0)
+    rc = lib().bltcu_check_soln(_p(lat, ctypes.c_int64), _p(con, ctypes.c_int64), n, m, _p(u, ctypes.c_int64),
+                                ctypes.byref(ok))
+    if rc != BLT_STATUS_OK:
+        raise RuntimeError(f"bltcu_check_soln failed with status {rc}")
+    return bool(ok.value)
+
+
+def infdist(B, u, k: int, p):
+    """infdist() of libblt/glpk_wrapper.h:26-34 on the GPU (one cold solve).  Returns (rc, dist, x[0:k])."""
+    B = np.ascontiguousarray(B, dtype=np.float64)
+    u = _i64(u)
+    p = np.ascontiguousarray(p, dtype=np.float64)
+    n, m = B.shape
+    x = np.zeros(max(n, 1), dtype=np.float64)
+    d = ctypes.c_double(0.0)
+    rc = lib().bltcu_infdist(_p(B, ctypes.c_double), n, m, _p(u, ctypes.c_int64), k, _p(p, ctypes.c_double),
+                             _p(x, ctypes.c_double), ctypes.byref(d))
+    return rc, float(d.value), x[:k].copy()

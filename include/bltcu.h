@@ -1,0 +1,89 @@
+/*
+ * bltcu.h -- C ABI of libbltcu.so, the CUDA (sm_100a) implementation of BLT's lattice-search hot path.
+ *
+ * These are the two seams that BLT's Context::check() crosses (reference paths relative to /root/reference):
+ *     rank = LLL(L, U)                                  libblt/context.cc:176   -> bltcu_lll()
+ *     rc   = closest(newL, C, yok, presoln_b, stats)    libblt/context.cc:236   -> bltcu_closest()
+ * Plain pointers and sizes only; caller-owned host buffers unless a function says "device"; blocking; no
+ * exceptions cross the boundary.  Return values are BLT's own codes (libblt/codes.h:5-24).
+ *
+ * There is no CPU fallback anywhere behind this header: without a usable CUDA device every compute entry point
+ * returns BLT_STATUS_ERROR and prints the CUDA error on stderr.
+ */
+#ifndef BLTCU_H
+#define BLTCU_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* libblt/codes.h:5-24 (values are fixed: the Haskell binding hard-codes them, src/BLT/Internal.hsc:40-45) */
+#define BLTCU_STATUS_OK 0
+#define BLTCU_STATUS_ERROR 1
+#define BLTCU_STATUS_LP_FAIL 2
+#define BLTCU_STATUS_INPUT_ERROR 3
+
+#define BLTCU_MAX_DIM 96 /* largest n (basis rows) and m (coordinates) the search kernel accepts */
+
+/* Options of one search.  Zero-initialise, then set what you need. */
+typedef struct bltcu_opts {
+    int device;          /* CUDA device ordinal */
+    int rank, world;     /* this process searches the subtrees  i % world == rank  of the static split (world<=1: all) */
+    int split_depth;     /* static split: expand this many top levels into subtrees first (0 = none; needed for world>1) */
+    int donate_min_level;/* dynamic split: only subtrees rooted at a level >= this are handed to idle warps (0 = default) */
+    int no_early_exit;   /* 1 = keep enumerating after a solution was found (exhaustive count) */
+    int warps_per_cta;   /* 0 = as many as shared memory allows */
+    int ctas;            /* 0 = one per SM */
+} bltcu_opts;
+
+/* Statistics of one search.  niter/nprune are SolverStats of libblt/closest.h:14-17. */
+typedef struct bltcu_stats {
+    uint64_t niter, nprune;
+    uint64_t nodes;        /* layer-distance solves = niter + nprune + 2 on a complete single-rank run */
+    uint64_t pivots, quick_prunes, refactors, cold_starts;
+    uint64_t donated;      /* subtrees handed over through the global queue */
+    uint64_t hist[BLTCU_MAX_DIM + 1]; /* hist[kk] = solves with kk free coefficients (roofline input) */
+    double kernel_ms;      /* CUDA-event time of the search kernel(s) */
+    double total_ms;       /* wall time of the call including copies */
+    int found;             /* 1 = a lattice point inside the box was found */
+    int launches;          /* kernels launched by this call */
+    int warps, ctas;       /* launch shape */
+    uint64_t scratch_bytes;/* global scratch used (level store + subtree pool) */
+} bltcu_stats;
+
+/* closest(): libblt/closest.h:50-54, libblt/closest.cc:166-327.
+ * lat: n x m row-major (rows = basis vectors), con: m x 2 (lower, upper).  sol: n coefficients w.r.t. lat (the
+ * point found, or the last recorded candidate `uhat`, exactly as the reference returns).  Returns
+ * BLT_STATUS_OK / LP_FAIL / INPUT_ERROR / ERROR.  Runs on device 0 with default options. */
+int bltcu_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter,
+                  uint64_t *nprune);
+
+/* Same seam with options and statistics (opts and stats may be NULL). */
+int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts *opts, int64_t *sol,
+                     bltcu_stats *stats);
+
+/* Same search with lat/con already resident in device memory (d_lat: n*m int64, d_con: 2*m int64, on
+ * opts->device).  sol and stats stay host pointers.  Used to time the search without the input copies. */
+int bltcu_closest_dev(const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
+                      int64_t *sol, bltcu_stats *stats);
+
+/* check_soln(): libblt/closest.cc:330-340, evaluated on the device (int64, wraps like the reference). */
+int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok);
+
+/* infdist(): libblt/glpk_wrapper.h:26-34, one cold layer-distance solve on the device (test seam for the
+ * reference's LP known answers, libblt/test_glpk.cc).  B: n x m doubles, u: n, p: m, x: k outputs. */
+int bltcu_infdist(const double *B, int n, int m, const int64_t *u, int k, const double *p, double *x,
+                  double *dist);
+
+/* Releases the cached device workspace of every device this process used. */
+void bltcu_release(void);
+
+/* Version string of the library. */
+const char *bltcu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
