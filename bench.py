@@ -1,0 +1,264 @@
+#!/usr/bin/env python
+"""bench.py -- enumeration nodes/s of the lattice search (BASELINE.json metric) on N B200s of one node.
+
+A step = one complete exhaustive search of the workload instance (dense UNSAT BILP, n = m = 60, LLL-reduced,
+committed under tests/golden/ with the script that made it).  A node = one layer-distance solve.
+
+  python bench.py --gpus 1 --steps 3 --warmup 3                 (our arm)
+  python bench.py --impl reference --gpus 1 --steps 2 --warmup 1 (the reference arm: CPU restatement, see below)
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+`value`  : nodes / device time of the search kernel(s), inputs resident in HBM (CUDA events on the launching stream,
+           max over ranks, summed over the K steps).
+`e2e`    : the same metric through the C ABI call bltcu_closest_ex() with pinned HOST buffers: host->device copy of
+           the basis and bounds, search, device->host copy of the result, wall clock around the call.
+N > 1    : every rank runs the deterministic static split and then searches its own share of the subtrees
+           (bltcu_opts.rank/world); no collective on the data path, one all-reduce of the counters at the end.
+           Total work is fixed => "strong" scaling.
+
+The reference arm: GaloisInc/blt cannot be built on this image (needs NTL, GLPK, Boost; none present, no network),
+so `--impl reference` times the CPU restatement in oracle/ (kind "port", single thread like the reference itself)
+on a bounded sample of the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FIXTURE = os.path.join(ROOT, "tests", "golden", "bench_dense60.npz")
+METRIC = "enum_nodes_per_s"
+UNIT = "nodes/s"
+
+
+def f_alg(k: int, m: int) -> float:
+    """Algorithmic fp64 flops of one node with k unknowns in ambient dimension m."""
+    return m * (2 * k + 3) + 4.0 * (k + 1) ** 2
+
+
+def load_workload():
+    z = np.load(FIXTURE)
+    return dict(lat=z["lat"].astype(np.int64), con=z["con"].astype(np.int64), w=int(z["w"]), seed=int(z["seed"]),
+                n=int(z["lat"].shape[0]), m=int(z["lat"].shape[1]))
+
+
+def workload_config(wl):
+    return {"workload": f"dense UNSAT BILP n={wl['n']} m={wl['m']} |a|<=100 width={wl['w']} seed={wl['seed']}, "
+                        "LLL-reduced, exhaustive enumeration",
+            "fixture": "tests/golden/bench_dense60.npz",
+            "l2": "L2 flushed (256 MiB write) between timed steps; the per-warp level store (~0.9 GB) also exceeds L2"}
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons with nvidia-smi while the timed region runs."""
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index = index
+        self.samples = []
+        self.stop_flag = False
+        self.smax = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                f = [x.strip() for x in out.strip().split(",")]
+                if len(f) >= 6:
+                    self.samples.append(f)
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unsampled"]}
+        mhz = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [nm for i, nm in enumerate(names) if any(s[2 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": mhz[len(mhz) // 2] if mhz else None, "sm_max_mhz": float(self.samples[0][1]),
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def cpu_sample(wl, max_nodes):
+    import oracle  # the one place bench.py executes oracle/: the timed CPU baseline
+
+    t0 = time.perf_counter()
+    r = oracle.closest(wl["lat"], wl["con"], max_nodes=max_nodes)
+    dt = time.perf_counter() - t0
+    return r["nodes"] / dt, r["nodes"], dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return 0
+    wl = load_workload()
+    sample_nodes = 60000
+    for _ in range(args.warmup):
+        cpu_sample(wl, 5000)
+    tot_nodes, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        v, nodes, dt = cpu_sample(wl, sample_nodes)
+        tot_nodes += nodes
+        tot_t += dt
+    value = tot_nodes / tot_t
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": workload_config(wl),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": 1, "kind": "port",
+                             "sample": f"first {sample_nodes} nodes in DFS order per step; CPU restatement "
+                                       "(oracle/blt_oracle.c), single thread like the reference; GaloisInc/blt itself "
+                                       "cannot be built here (no NTL/GLPK/Boost)"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-nodes", type=int, default=150000, help="size of the CPU baseline sample (nodes)")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+
+    import blt_b200
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the search has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    wl = load_workload()
+    n, m = wl["n"], wl["m"]
+    lat_h = torch.from_numpy(wl["lat"]).contiguous().pin_memory()
+    con_h = torch.from_numpy(wl["con"]).contiguous().pin_memory()
+    lat_d = lat_h.cuda(non_blocking=False)
+    con_d = con_h.cuda(non_blocking=False)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    opts = dict(device=local_rank, rank=rank, world=world, split_depth=(8 if world > 1 else 0), timeout_ms=600000)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_dev():
+        flush.zero_()
+        torch.cuda.synchronize()
+        r = blt_b200.closest_dev(lat_d.data_ptr(), con_d.data_ptr(), n, m, **opts)
+        if r["rc"] != 0:
+            raise SystemExit(f"bench.py: search failed with status {r['rc']}")
+        return r
+
+    def step_e2e():
+        flush.zero_()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        r = blt_b200.closest(lat_h.numpy(), con_h.numpy(), **opts)
+        dt = time.perf_counter() - t0
+        if r["rc"] != 0:
+            raise SystemExit(f"bench.py: search failed with status {r['rc']}")
+        return r, dt
+
+    for _ in range(max(args.warmup, 3)):
+        step_dev()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    t_wall0 = time.perf_counter()
+    kernel_ms, nodes, launches = 0.0, 0, 0
+    hist = np.zeros(n + 1, dtype=np.float64)
+    last = None
+    for _ in range(args.steps):
+        r = step_dev()
+        kernel_ms += r["kernel_ms"]
+        nodes += r["nodes"]
+        launches += r["launches"]
+        hist += r["hist"].astype(np.float64)
+        last = r
+    barrier()
+    wall_s = time.perf_counter() - t_wall0
+    # end to end through the host-buffer ABI
+    e2e_s, e2e_nodes = 0.0, 0
+    for _ in range(args.steps):
+        r, dt = step_e2e()
+        e2e_s += dt
+        e2e_nodes += r["nodes"]
+    barrier()
+    sampler.stop_flag = True
+
+    red = torch.tensor([kernel_ms, e2e_s], dtype=torch.float64, device="cuda")
+    tot = torch.tensor([float(nodes), float(e2e_nodes), float(last["niter"]), float(last["nprune"]), float(launches)],
+                       dtype=torch.float64, device="cuda")
+    hist_t = torch.from_numpy(hist).cuda()
+    if world > 1:
+        dist.all_reduce(red, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(hist_t, op=dist.ReduceOp.SUM)
+    kernel_ms_max, e2e_s_max = red.tolist()
+    nodes_all, e2e_nodes_all, niter_all, nprune_all, launches_all = tot.tolist()
+    hist_all = hist_t.cpu().numpy()
+
+    if rank == 0:
+        value = nodes_all / (kernel_ms_max * 1e-3)
+        flops = float(sum(hist_all[k] * f_alg(k, m) for k in range(n + 1)))
+        peak = blt_b200.fp64_peak(local_rank, 5)
+        achieved = flops / (kernel_ms_max * 1e-3) / 1e12 / max(world, 1)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+                "warmup": max(args.warmup, 3), "ms_per_step": kernel_ms_max / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": workload_config(wl),
+                "niter": int(niter_all), "nprune": int(nprune_all), "nodes_per_step": nodes_all / args.steps,
+                "time_to_decision_ms": kernel_ms_max / args.steps, "wall_ms_per_step": 1e3 * wall_s / args.steps,
+                "pivots_per_node": last["pivots"] / max(1, last["nodes"]), "donated": last["donated"],
+                "warps": last["warps"],
+                "e2e": {"value": e2e_nodes_all / e2e_s_max, "unit": UNIT, "h2d_bytes_per_step": (n * m + 2 * m) * 8,
+                        "d2h_bytes_per_step": n * 8 + 1024},
+                "gpu_launches": int(launches_all),
+                "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                             "frac": achieved / peak, "traffic": None,
+                             "note": "achieved = sum_k N_k*F_alg(k,m) per GPU / search-kernel time; peak = FP64 FMA "
+                                     "throughput measured on this GPU by bltcu_fp64_peak (MEASURED_PEAKS.json has no "
+                                     "FP64 figure)"},
+                "clocks": sampler.summary()}
+        if not args.no_cpu and world == 1:
+            v, cn, dt = cpu_sample(wl, args.cpu_nodes)
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",
+                                    "sample": f"first {cn} nodes of the same instance in DFS order, {dt:.1f} s, "
+                                              "oracle/blt_oracle.c single thread"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -54,7 +54,9 @@ struct QCtl {
     int status;                 // BLT status code of the search
     int found;                  // a solution has been written to sol
     unsigned int out_count;     // static split: number of collected subtrees
-    int pad0, pad1;
+    int timed_out;              // watchdog fired: 1 node loop, 2 idle loop, 3 pop spin, 4 push spin
+    int pad1;
+    unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
     unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated;
     unsigned long long hist[MAXD + 1];
 };
@@ -452,25 +454,42 @@ __device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *d
     __syncwarp();
 }
 
+__device__ __forceinline__ unsigned long long gtimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// watchdog: a search that overruns its deadline stops with BLT_STATUS_ERROR instead of hanging the device
+__device__ __forceinline__ bool overdue(QCtl *q, int where) {
+    const unsigned long long dl = *(volatile unsigned long long *)&q->deadline_ns;
+    if (dl == 0 || gtimer() < dl) return false;
+    if (atomicCAS(&q->timed_out, 0, where) == 0) { q->status = BLTCU_STATUS_ERROR; }
+    q->abort = 1;
+    __threadfence();
+    return true;
+}
+
 // MPMC rings -------------------------------------------------------------------------------------------------
-__device__ __forceinline__ int ring_pop(volatile unsigned int *head, volatile unsigned int *tail, int *ring, unsigned int mask) {
+__device__ __forceinline__ int ring_pop(QCtl *q, volatile unsigned int *head, volatile unsigned int *tail, int *ring, unsigned int mask) {
     for (;;) {
         const unsigned int h = *head, t = *tail;
         if ((int)(t - h) <= 0) return -1;
         if (atomicCAS((unsigned int *)head, h, h + 1) == h) {
             volatile int *slot = ring + (h & mask);
             int v;
-            while ((v = *slot) < 0) __nanosleep(20);
+            unsigned int spins = 0;
+            while ((v = *slot) < 0) { __nanosleep(20); if ((++spins & 1023u) == 0 && overdue(q, 3)) return -1; }
             *slot = -1;
             __threadfence();
             return v;
         }
     }
 }
-__device__ __forceinline__ void ring_push(unsigned int *tail, int *ring, unsigned int mask, int val) {
+__device__ __forceinline__ void ring_push(QCtl *q, unsigned int *tail, int *ring, unsigned int mask, int val) {
     const unsigned int t = atomicAdd(tail, 1u);
     volatile int *slot = ring + (t & mask);
-    while (*slot >= 0) __nanosleep(20);
+    unsigned int spins = 0;
+    while (*slot >= 0) { __nanosleep(20); if ((++spins & 1023u) == 0 && overdue(q, 4)) return; }
     __threadfence();
     *slot = val;
 }
@@ -519,7 +538,7 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
     }
     __syncwarp();
     __threadfence();
-    if (lane == 0) ring_push(&P.q->ftail, P.fring, P.ring_mask, rec);  // the record slot is free again
+    if (lane == 0) ring_push(P.q, &P.q->ftail, P.fring, P.ring_mask, rec);  // the record slot is free again
 
     double d = 0.0, xlast = 0.0;
     if (is_root) {  // initial solve LP(n), closest.cc:206
@@ -543,8 +562,16 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
     const int depth0 = n - k0;
     const bool forced = depth0 < P.static_depth;  // static split: emit every explored child of this record
 
+    unsigned int wd = 0;
     for (;;) {
-        if (*(volatile int *)&P.q->abort) return;
+        {   // one lane reads the stop flag so that the whole warp takes the same branch
+            int ab = 0;
+            if (lane == 0) {
+                ab = *(volatile int *)&P.q->abort;
+                if (!ab && (++wd & 255u) == 0) ab = overdue(P.q, 1) ? 1 : 0;
+            }
+            if (__shfl_sync(FULLMASK, ab, 0)) return;
+        }
         // c = cpar - u[k-1] * B[k-1]
         {
             const double mu = -(double)s.u[k - 1];
@@ -607,7 +634,7 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
             bool emit = false;
             int slot = -1;
             if (forced && k == k0) emit = true;
-            else if (P.dynamic && (k - 1) >= P.donate_min_level) {
+            else if (P.dynamic && (k - 1) >= P.donate_min_level && s.ord[k - 1] > 0) {  // keep the first (nearest) child
                 int want = 0;
                 if (lane == 0) {
                     const int idle = *(volatile int *)&P.q->idle;
@@ -617,7 +644,7 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
                 emit = __shfl_sync(FULLMASK, want, 0) != 0;
             }
             if (emit) {
-                if (lane == 0) slot = ring_pop(&P.q->fhead, &P.q->ftail, P.fring, P.ring_mask);
+                if (lane == 0) slot = ring_pop(P.q, &P.q->fhead, &P.q->ftail, P.fring, P.ring_mask);
                 slot = __shfl_sync(FULLMASK, slot, 0);
                 if (slot < 0) {
                     if (forced && k == k0) { if (lane == 0) { P.q->status = BLTCU_STATUS_ERROR; P.q->abort = 1; } return; }
@@ -643,7 +670,7 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
                         P.out_list[o] = slot;
                     } else {
                         atomicAdd(&P.q->pending, 1);
-                        ring_push(&P.q->tail, P.ring, P.ring_mask, slot);
+                        ring_push(P.q, &P.q->tail, P.ring, P.ring_mask, slot);
                     }
                     // continue with the next sibling as if the subtree had returned
                     const int st = s.step[k - 1];
@@ -672,7 +699,10 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
                 unsigned char *bk = P.best_key + (size_t)gwarp * n;
                 int64_t *bu = P.best_u + (size_t)gwarp * n;
                 bool newer = true;
-                if (P.best_valid[gwarp]) {  // lexicographic compare of ordinal paths from the top level down
+                int bvld = 0;
+                if (lane == 0) bvld = P.best_valid[gwarp];
+                bvld = __shfl_sync(FULLMASK, bvld, 0);
+                if (bvld) {  // lexicographic compare of ordinal paths from the top level down
                     int cmp = 0;
                     for (int e = n - 1; e >= 0 && cmp == 0; --e) cmp = (int)s.ord[e] - (int)bk[e];
                     newer = cmp >= 0;
@@ -745,12 +775,13 @@ __global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
         if (lane == 0) {
             if (*(volatile int *)&q->abort) stop = 1;
             else {
-                rec = ring_pop(&q->head, &q->tail, P.ring, P.ring_mask);
+                rec = ring_pop(q, &q->head, &q->tail, P.ring, P.ring_mask);
                 if (rec < 0) {
                     if (*(volatile int *)&q->pending == 0) stop = 1;
                     else {
                         if (!am_idle) { atomicAdd(&q->idle, 1); am_idle = true; }
                         __nanosleep(200);
+                        if (overdue(q, 2)) stop = 1;
                     }
                 } else if (am_idle) { atomicSub(&q->idle, 1); am_idle = false; }
             }
@@ -775,8 +806,10 @@ __global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
 }
 
 // small helper kernels ---------------------------------------------------------------------------------------
-__global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p) {
+__global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p,
+                                   unsigned long long *now) {
     const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid == 0) *now = gtimer();
     if (tid < n * m) B[tid] = (double)lat[tid];                                   // closest.cc:203
     if (tid < m) p[tid] = (double)(con[2 * tid + 1] + con[2 * tid]) / 2.0;        // closest.cc:180-185
 }
@@ -958,16 +991,24 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     P.warps_per_cta = wpc;
     P.warp_smem_doubles = warp_bytes / 8;
 
-    // radius: closest.cc:193-194 uses row 0 only
-    int64_t con0[2];
-    CK(cudaMemcpyAsync(con0, d_con, 16, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    P.radius = (double)(con0[1] - con0[0]) / 2.0;
-
     CK(cudaFuncSetAttribute(bltcu_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     int launches = 0;
-    bltcu_setup_kernel<<<(n * m + 255) / 256, 256, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p);
+    bltcu_setup_kernel<<<(n * m + 255) / 256, 256, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p,
+                                                          (unsigned long long *)P.sol);
+    CK(cudaGetLastError());
     launches++;
+    // radius: closest.cc:193-194 uses row 0 only; device clock for the watchdog deadline
+    int64_t con0[2];
+    unsigned long long now_ns = 0, deadline_ns = 0;
+    CK(cudaMemcpyAsync(con0, d_con, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&now_ns, P.sol, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    P.radius = (double)(con0[1] - con0[0]) / 2.0;
+    {
+        long long tmo = o.timeout_ms;
+        if (tmo <= 0) { const char *e = getenv("BLTCU_TIMEOUT_MS"); if (e) tmo = atoll(e); }
+        if (tmo > 0) deadline_ns = now_ns + (unsigned long long)tmo * 1000000ull;
+    }
 
     // host images of the control block and rings
     std::vector<int> ring(ring_cap, -1), fring(ring_cap);
@@ -986,6 +1027,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         for (int i = 0; i < pool_cap; ++i) if (!used[i] && i >= first_free) fring[nf++] = i;
         for (int i = 0; i < std::min(first_free, pool_cap); ++i) if (!used[i]) fring[nf++] = i;
         hq.ftail = nf;
+        hq.deadline_ns = deadline_ns;
         CK(cudaMemcpyAsync(P.q, &hq, sizeof hq, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(P.ring, ring.data(), ring_cap * 4, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(P.fring, fring.data(), ring_cap * 4, cudaMemcpyHostToDevice, st));
@@ -1024,6 +1066,9 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
         kernel_ms += ms;
         launches++;
+        if (hq.timed_out)
+            fprintf(stderr, "bltcu: watchdog fired (where=%d) pending=%d idle=%d head=%u tail=%u fhead=%u ftail=%u found=%d\n",
+                    hq.timed_out, hq.pending, hq.idle, hq.head, hq.tail, hq.fhead, hq.ftail, hq.found);
         return 0;
     };
 

@@ -17,7 +17,7 @@ _LIB = None
 class Opts(ctypes.Structure):
     _fields_ = [("device", ctypes.c_int), ("rank", ctypes.c_int), ("world", ctypes.c_int),
                 ("split_depth", ctypes.c_int), ("donate_min_level", ctypes.c_int), ("no_early_exit", ctypes.c_int),
-                ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int)]
+                ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int), ("timeout_ms", ctypes.c_int)]
 
 
 class Stats(ctypes.Structure):
@@ -51,6 +51,8 @@ def lib() -> ctypes.CDLL:
         L.bltcu_check_soln.restype = ctypes.c_int
         L.bltcu_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
         L.bltcu_infdist.restype = ctypes.c_int
+        L.bltcu_fp64_peak.argtypes = [ctypes.c_int, ctypes.c_int, f64p]
+        L.bltcu_fp64_peak.restype = ctypes.c_int
         L.bltcu_release.argtypes = []
         L.bltcu_release.restype = None
         L.bltcu_version.argtypes = []
@@ -133,3 +135,12 @@ def infdist(B, u, k: int, p):
     rc = lib().bltcu_infdist(_p(B, ctypes.c_double), n, m, _p(u, ctypes.c_int64), k, _p(p, ctypes.c_double),
                              _p(x, ctypes.c_double), ctypes.byref(d))
     return rc, float(d.value), x[:k].copy()
+
+
+def fp64_peak(device: int = 0, reps: int = 5) -> float:
+    """Measured FP64 FMA peak of the device in TFLOP/s (roofline denominator of the search kernel)."""
+    v = ctypes.c_double(0.0)
+    rc = lib().bltcu_fp64_peak(device, reps, ctypes.byref(v))
+    if rc != BLT_STATUS_OK:
+        raise RuntimeError(f"bltcu_fp64_peak failed with status {rc}")
+    return float(v.value)

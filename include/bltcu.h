@@ -36,6 +36,8 @@ typedef struct bltcu_opts {
     int no_early_exit;   /* 1 = keep enumerating after a solution was found (exhaustive count) */
     int warps_per_cta;   /* 0 = as many as shared memory allows */
     int ctas;            /* 0 = one per SM */
+    int timeout_ms;      /* device-side watchdog: give up with BLT_STATUS_ERROR after this long (0 = env
+                            BLTCU_TIMEOUT_MS, else none) */
 } bltcu_opts;
 
 /* Statistics of one search.  niter/nprune are SolverStats of libblt/closest.h:14-17. */
@@ -76,6 +78,10 @@ int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const
  * reference's LP known answers, libblt/test_glpk.cc).  B: n x m doubles, u: n, p: m, x: k outputs. */
 int bltcu_infdist(const double *B, int n, int m, const int64_t *u, int k, const double *p, double *x,
                   double *dist);
+
+/* Measurement helper (no counterpart in the reference): FP64 FMA throughput of `device` in TFLOP/s, best of
+ * `reps` launches.  bench.py uses it as the roofline denominator of the search kernel. */
+int bltcu_fp64_peak(int device, int reps, double *tflops);
 
 /* Releases the cached device workspace of every device this process used. */
 void bltcu_release(void);

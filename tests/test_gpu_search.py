@@ -164,3 +164,21 @@ def test_subset_sum_sat(gpu):  # config 3 shape, small
     assert got["found"] == oracle.check_soln(lat, con, ref["sol"])
     if got["found"]:
         assert oracle.check_soln(lat, con, got["sol"])
+
+
+def test_bench_workload_full_size(gpu, golden):
+    """BASELINE.json's metric shape (n = m = 60) at full size: counts, histogram, pivots and uhat equal the values
+    the oracle produced when the fixture was made (tests/golden/make_bench_fixture.py)."""
+    z = np.load(f"{golden}/bench_dense60.npz")
+    got = gpu.closest(z["lat"], z["con"], timeout_ms=300000)
+    assert got["rc"] == 0 and not got["found"]
+    assert got["niter"] == int(z["niter"]) and got["nprune"] == int(z["nprune"]) and got["nodes"] == int(z["nodes"])
+    assert (got["hist"] == z["hist"]).all() and got["pivots"] == int(z["pivots"])
+    assert (got["sol"] == z["sol"]).all()
+    # 2 ranks' shares add up (world-size-2 run on one device, one rank after the other)
+    tot = 0
+    for r in range(2):
+        g = gpu.closest(z["lat"], z["con"], rank=r, world=2, split_depth=6, timeout_ms=300000)
+        assert g["rc"] == 0
+        tot += g["nodes"]
+    assert tot == int(z["nodes"])
