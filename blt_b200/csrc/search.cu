@@ -1267,3 +1267,200 @@ extern "C" void bltcu_release(void) {
 }
 
 extern "C" const char *bltcu_version(void) { return "blt-b200 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the search
+// ------------------------------------------------------------------------------------------------------------
+// Who needs this: code that runs the search from a place where device memory may not be requested or returned --
+// a plugin hosted inside another application whose memory manager owns the GPU heap, a solver callback in a
+// real-time loop where a cudaMalloc (which may synchronise the whole device) is not acceptable, or a process that
+// has given all free HBM to an arena and would get cudaErrorMemoryAllocation from any further request.  The normal
+// entry points grow a cached workspace with cudaMalloc; this one never does.  All global scratch of the search
+// kernel (control block, subtree queue and pool, per-warp level store, staging for the inputs) is carved out of
+// the fixed array below, which is part of the library image: every GPU that loads libbltcu.so holds these 20 MiB
+// from the moment the library is loaded until the process exits, whether or not this entry point is ever called.
+#define BLTCU_NOALLOC_BYTES (20u << 20)
+#define BLTCU_NOALLOC_WPC 2       // warps per CTA of this variant (fixed so that the level store has a fixed size)
+#define BLTCU_NOALLOC_CTAS 148    // at most this many CTAs
+#define BLTCU_NOALLOC_POOL 512    // subtree records (power of two)
+#define BLTCU_NOALLOC_MAXDEV 64
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BLTCU_NOALLOC_BYTES];
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime's symbol table, not an address a kernel can
+// dereference; the device address is looked up once per device and cached here.
+static unsigned char *g_noalloc_dev[BLTCU_NOALLOC_MAXDEV];
+static int g_noalloc_sms[BLTCU_NOALLOC_MAXDEV];
+static size_t g_noalloc_smem[BLTCU_NOALLOC_MAXDEV];
+
+// Puts the shared array into the state a fresh search expects.  The array still holds whatever the previous call
+// left behind, so everything the kernel reads before writing is rewritten here: the control block, both rings, the
+// root record, the result slot and the per-warp "recorded a candidate" flags.
+__global__ void bltcu_noalloc_init_kernel(Params P, unsigned long long deadline_ns, int nwarps) {
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    const RecLayout RL = rec_layout(P.n, P.m);
+    unsigned char *q = (unsigned char *)P.q;
+    for (size_t i = tid; i < sizeof(QCtl); i += nth) q[i] = 0;
+    for (int i = tid; i <= (int)P.ring_mask; i += nth) {
+        P.ring[i] = (i == 0) ? 0 : -1;                      // the root record sits in slot 0
+        P.fring[i] = (i + 1 <= (int)P.ring_mask) ? i + 1 : -1;  // slots 1..cap-1 are free
+    }
+    for (size_t i = tid; i < RL.stride; i += nth) P.pool[i] = 0;
+    for (int i = tid; i < P.n; i += nth) P.sol[i] = 0;
+    for (int i = tid; i < nwarps; i += nth) P.best_valid[i] = 0;
+    __threadfence();
+    __syncthreads();
+    if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) {
+            P.q->tail = 1; P.q->pending = 1; P.q->ftail = P.ring_mask; P.q->deadline_ns = deadline_ns;
+            ((int *)P.pool)[0] = P.n;
+            ((int *)P.pool)[1] = REC_ROOT;
+        }
+        for (int j = threadIdx.x; j < P.m; j += blockDim.x) ((double *)(P.pool + RL.off_cpar))[j] = P.p[j];
+    }
+}
+
+// bltcu_closest_noalloc: closest() (libblt/closest.h:50-54) without any device or host allocation.
+//
+//   lat, con, sol, niter, nprune, found   host pointers, same meaning as bltcu_closest(); n, m <= BLTCU_NOALLOC_MAX_DIM
+//
+// * The first call on a device looks up the device address of the scratch array (cudaGetSymbolAddress) and the
+//   device's SM count; make that first call before starting any stream capture.  Later calls reuse the cached values.
+// * Work is issued on the legacy default stream of `device`; the call blocks until the result is on the host.
+// * All calls share the one scratch array.  Two calls whose kernels overlap on the same GPU (two host threads, or
+//   two processes' worth of streams through this library in one process) corrupt each other's search: serialise them.
+// * Returns BLT_STATUS_INPUT_ERROR with a message on stderr when n or m exceed the limit, otherwise the same
+//   status codes as bltcu_closest().
+extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int n, int m, int device, int64_t *sol,
+                                     uint64_t *niter, uint64_t *nprune, int *found) {
+    if (n <= 0 || m <= 0 || m < n || !lat || !con) return BLTCU_STATUS_INPUT_ERROR;  // closest.cc:173-177
+    if (n > BLTCU_NOALLOC_MAX_DIM || m > BLTCU_NOALLOC_MAX_DIM) {
+        fprintf(stderr, "bltcu_closest_noalloc: %d x %d exceeds the allocation-free limit of %d x %d "
+                        "(the scratch array is fixed at %u MiB); use bltcu_closest() for larger problems\n",
+                n, m, BLTCU_NOALLOC_MAX_DIM, BLTCU_NOALLOC_MAX_DIM, BLTCU_NOALLOC_BYTES >> 20);
+        return BLTCU_STATUS_INPUT_ERROR;
+    }
+    if (device < 0 || device >= BLTCU_NOALLOC_MAXDEV) return BLTCU_STATUS_INPUT_ERROR;
+    std::lock_guard<std::mutex> lk(g_mu);
+    CK(cudaSetDevice(device));
+    if (!g_noalloc_dev[device]) {  // once per device, with that device current
+        unsigned char *ptr = nullptr;
+        CK(cudaGetSymbolAddress((void **)&ptr, g_noalloc_scratch));
+        int v = 0;
+        CK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device)); g_noalloc_sms[device] = v;
+        CK(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)); g_noalloc_smem[device] = (size_t)v;
+        g_noalloc_dev[device] = ptr;
+    }
+    unsigned char *base = g_noalloc_dev[device];
+    const int wpc = BLTCU_NOALLOC_WPC;
+    const int ctas = std::min(g_noalloc_sms[device], BLTCU_NOALLOC_CTAS);
+    const int nwarps = ctas * wpc;
+
+    // same shared-memory and workspace carving as search_impl(), but inside the fixed array
+    const int KMAX = n + 1, LD = KMAX | 1, LDB = m | 1;
+    const size_t wd = (size_t)KMAX * LD + 5 * (size_t)KMAX + 2 * (size_t)m + (n + 2) + n;
+    const size_t wi = 4 * (size_t)KMAX + (n + 1) + (n + 1);
+    const size_t wb = 2 * (size_t)((n + 8) / 8 * 8) + 16;
+    const size_t warp_bytes = align_up(wd * 8 + wi * 4 + wb, 16);
+    const size_t smem_bytes = (size_t)n * LDB * 8 + (size_t)wpc * warp_bytes;
+    if (smem_bytes > g_noalloc_smem[device]) return BLTCU_STATUS_ERROR;
+    const RecLayout RL = rec_layout(n, m);
+    const size_t scrD_stride = align_up(chain_off(n + 1) + (size_t)(n + 2) * m, 32);
+    const size_t scrI_stride = align_up(chain_ioff(n + 1) + 8, 32);
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
+    const size_t o_q = carve(sizeof(QCtl));
+    const size_t o_in = carve(((size_t)n * m + 2 * (size_t)m) * 8);
+    const size_t o_B = carve((size_t)n * m * 8);
+    const size_t o_p = carve((size_t)m * 8);
+    const size_t o_ring = carve((size_t)BLTCU_NOALLOC_POOL * 4);
+    const size_t o_fring = carve((size_t)BLTCU_NOALLOC_POOL * 4);
+    const size_t o_out = carve((size_t)BLTCU_NOALLOC_POOL * 4);
+    const size_t o_sol = carve((size_t)n * 8);
+    const size_t o_bu = carve((size_t)nwarps * n * 8);
+    const size_t o_bk = carve((size_t)nwarps * n);
+    const size_t o_bv = carve((size_t)nwarps * 4);
+    const size_t o_pool = carve((size_t)BLTCU_NOALLOC_POOL * RL.stride);
+    const size_t o_scrD = carve((size_t)nwarps * scrD_stride * 8);
+    const size_t o_scrI = carve((size_t)nwarps * scrI_stride * 4);
+    if (off > (size_t)BLTCU_NOALLOC_BYTES) {
+        fprintf(stderr, "bltcu_closest_noalloc: internal layout (%zu bytes) exceeds the scratch array\n", off);
+        return BLTCU_STATUS_ERROR;
+    }
+    int64_t *d_lat = (int64_t *)(base + o_in), *d_con = d_lat + (size_t)n * m;
+    Params P;
+    memset(&P, 0, sizeof P);
+    P.n = n; P.m = m; P.LD = LD; P.LDB = LDB; P.KMAX = KMAX;
+    P.B = (double *)(base + o_B); P.p = (double *)(base + o_p);
+    P.lat = d_lat; P.con = d_con;
+    P.q = (QCtl *)(base + o_q);
+    P.ring = (int *)(base + o_ring); P.fring = (int *)(base + o_fring); P.ring_mask = BLTCU_NOALLOC_POOL - 1;
+    P.pool = base + o_pool; P.rec_stride = RL.stride; P.pool_cap = BLTCU_NOALLOC_POOL;
+    P.scrD = (double *)(base + o_scrD); P.scrD_stride = scrD_stride;
+    P.scrI = (int *)(base + o_scrI); P.scrI_stride = scrI_stride;
+    P.sol = (int64_t *)(base + o_sol);
+    P.best_u = (int64_t *)(base + o_bu); P.best_key = base + o_bk; P.best_valid = (int *)(base + o_bv);
+    P.out_list = (int *)(base + o_out);
+    P.static_depth = 0; P.dynamic = 1;
+    P.donate_min_level = std::min(6, std::max(2, n / 3));
+    P.lowwater = std::min(nwarps, BLTCU_NOALLOC_POOL / 4);
+    P.no_early_exit = 0;
+    P.warps_per_cta = wpc;
+    P.warp_smem_doubles = warp_bytes / 8;
+    P.radius = (double)(con[1] - con[0]) / 2.0;  // closest.cc:193-194: row 0 only
+
+    cudaStream_t st = 0;  // legacy default stream: creating a stream would be an allocation
+    CK(cudaMemcpyAsync(d_lat, lat, (size_t)n * m * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(d_con, con, (size_t)2 * m * 8, cudaMemcpyHostToDevice, st));
+    bltcu_setup_kernel<<<(n * m + 255) / 256, 256, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p,
+                                                          (unsigned long long *)P.sol);
+    CK(cudaGetLastError());
+    unsigned long long deadline_ns = 0;
+    if (const char *e = getenv("BLTCU_TIMEOUT_MS")) {
+        const long long tmo = atoll(e);
+        if (tmo > 0) {
+            unsigned long long now_ns = 0;
+            CK(cudaMemcpyAsync(&now_ns, P.sol, 8, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            deadline_ns = now_ns + (unsigned long long)tmo * 1000000ull;
+        }
+    }
+    bltcu_noalloc_init_kernel<<<1, 256, 0, st>>>(P, deadline_ns, nwarps);  // one block: its barrier orders the clears
+    CK(cudaGetLastError());
+    CK(cudaFuncSetAttribute(bltcu_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    bltcu_search_kernel<<<ctas, wpc * 32, smem_bytes, st>>>(P);
+    CK(cudaGetLastError());
+    static QCtl hq;  // host copies live in static storage: no heap use on the host either
+    static int64_t h_bu[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * BLTCU_NOALLOC_MAX_DIM];
+    static unsigned char h_bk[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * BLTCU_NOALLOC_MAX_DIM];
+    static int h_bv[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC];
+    CK(cudaMemcpyAsync(&hq, P.q, sizeof hq, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if (hq.timed_out) fprintf(stderr, "bltcu_closest_noalloc: watchdog fired (where=%d)\n", hq.timed_out);
+    int64_t hsol[BLTCU_NOALLOC_MAX_DIM] = {0};
+    if (hq.found) {
+        CK(cudaMemcpy(hsol, P.sol, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    } else {  // last recorded candidate in depth-first order, as the reference returns on UNSAT
+        CK(cudaMemcpy(h_bv, P.best_valid, (size_t)nwarps * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(h_bk, P.best_key, (size_t)nwarps * n, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(h_bu, P.best_u, (size_t)nwarps * n * 8, cudaMemcpyDeviceToHost));
+        int bestw = -1;
+        for (int i = 0; i < nwarps; ++i) {
+            if (!h_bv[i]) continue;
+            bool ge = true;
+            if (bestw >= 0) {
+                for (int e = n - 1; e >= 0; --e) {  // ordinal paths, top level first
+                    const int a = h_bk[(size_t)i * n + e], b = h_bk[(size_t)bestw * n + e];
+                    if (a != b) { ge = a > b; break; }
+                }
+            }
+            if (ge) bestw = i;
+        }
+        if (bestw >= 0) for (int e = 0; e < n; ++e) hsol[e] = h_bu[(size_t)bestw * n + e];
+    }
+    if (sol) for (int e = 0; e < n; ++e) sol[e] = hsol[e];
+    if (niter) *niter = hq.niter;
+    if (nprune) *nprune = hq.nprune;
+    if (found) *found = hq.found;
+    return hq.status;
+}

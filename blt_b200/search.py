@@ -51,6 +51,9 @@ def lib() -> ctypes.CDLL:
         L.bltcu_check_soln.restype = ctypes.c_int
         L.bltcu_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
         L.bltcu_infdist.restype = ctypes.c_int
+        L.bltcu_closest_noalloc.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.c_int, i64p, u64p, u64p,
+                                            ctypes.POINTER(ctypes.c_int)]
+        L.bltcu_closest_noalloc.restype = ctypes.c_int
         L.bltcu_fp64_peak.argtypes = [ctypes.c_int, ctypes.c_int, f64p]
         L.bltcu_fp64_peak.restype = ctypes.c_int
         L.bltcu_release.argtypes = []
@@ -144,3 +147,22 @@ def fp64_peak(device: int = 0, reps: int = 5) -> float:
     if rc != BLT_STATUS_OK:
         raise RuntimeError(f"bltcu_fp64_peak failed with status {rc}")
     return float(v.value)
+
+
+NOALLOC_MAX_DIM = 20
+
+
+def closest_noalloc(lat, con, device: int = 0):
+    """closest() through bltcu_closest_noalloc: same search, but the library neither allocates nor frees device
+    memory (for hosts that own the GPU heap themselves).  n, m <= 20.  Calls must not overlap on one GPU."""
+    lat = _i64(lat)
+    con = _i64(con)
+    if lat.ndim != 2 or con.ndim != 2 or con.shape[1] != 2 or con.shape[0] != lat.shape[1]:
+        return dict(rc=BLT_STATUS_INPUT_ERROR, sol=None, niter=0, nprune=0, found=False)
+    n, m = lat.shape
+    sol = np.zeros(max(n, 1), dtype=np.int64)
+    niter, nprune, found = ctypes.c_uint64(0), ctypes.c_uint64(0), ctypes.c_int(0)
+    rc = lib().bltcu_closest_noalloc(_p(lat, ctypes.c_int64), _p(con, ctypes.c_int64), n, m, device,
+                                     _p(sol, ctypes.c_int64), ctypes.byref(niter), ctypes.byref(nprune),
+                                     ctypes.byref(found))
+    return dict(rc=rc, sol=sol[:n], niter=int(niter.value), nprune=int(nprune.value), found=bool(found.value))

@@ -79,6 +79,18 @@ int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const
 int bltcu_infdist(const double *B, int n, int m, const int64_t *u, int k, const double *p, double *x,
                   double *dist);
 
+/* No counterpart in the reference.  closest() for callers that must not allocate: a plugin inside a host
+ * application that owns the GPU heap, a real-time loop that cannot afford a device-synchronising cudaMalloc, a
+ * process that has handed all free HBM to its own arena.  Calls no cudaMalloc/cudaFree and creates no stream or
+ * event; all kernel scratch lives in one fixed 20 MiB array inside the library image (held by every GPU that loads
+ * the library until the process exits).  n, m <= BLTCU_NOALLOC_MAX_DIM, otherwise BLT_STATUS_INPUT_ERROR and a
+ * message on stderr.  The first call on a device resolves the array's device address: make it before any stream
+ * capture.  All calls share the array, so calls that overlap on one GPU race: serialise them.  Pointers are host
+ * pointers with the meaning they have in bltcu_closest(); found receives 1 if a lattice point was found. */
+#define BLTCU_NOALLOC_MAX_DIM 20
+int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int n, int m, int device, int64_t *sol,
+                          uint64_t *niter, uint64_t *nprune, int *found);
+
 /* Measurement helper (no counterpart in the reference): FP64 FMA throughput of `device` in TFLOP/s, best of
  * `reps` launches.  bench.py uses it as the roofline denominator of the search kernel. */
 int bltcu_fp64_peak(int device, int reps, double *tflops);
