@@ -5,7 +5,13 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SRC = [os.path.join(HERE, "csrc", "search.cu"), os.path.join(HERE, "csrc", "peaks.cu")]
+SRC = [os.path.join(HERE, "csrc", "search.cu"), os.path.join(HERE, "csrc", "peaks.cu"),
+       os.path.join(HERE, "csrc", "host", "lll.cpp")]
+HOST_SRC = [os.path.join(HERE, "csrc", "host", f) for f in ("context.cpp", "blt_api.cpp")]
+HOST_HDR = [os.path.join(HERE, "csrc", "host", "context.h"), os.path.join(HERE, "..", "include", "blt.h"),
+            os.path.join(HERE, "..", "include", "codes.h")]
+LIBBLT = os.path.join(HERE, "lib", "libblt.so")
+RUN_BLT = os.path.join(HERE, "lib", "run_blt")
 OUT = os.path.join(HERE, "lib", "libbltcu.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
@@ -15,10 +21,27 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
     deps = SRC + [os.path.join(HERE, "..", "include", "bltcu.h")]
     if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in deps):
+        build_host()
         return OUT
     cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + SRC
     subprocess.check_call(cmd)
+    build_host(force=True)
     return OUT
+
+
+def build_host(force: bool = False) -> str:
+    """libblt.so (the blt.h API: Context, Expr, parser) and the run_blt CLI, linked against libbltcu.so."""
+    deps = HOST_SRC + HOST_HDR + [os.path.join(HERE, "csrc", "host", "run_blt.cpp"), OUT]
+    if not force and os.path.exists(LIBBLT) and os.path.exists(RUN_BLT) and all(
+            os.path.getmtime(LIBBLT) >= os.path.getmtime(d) for d in deps):
+        return LIBBLT
+    libdir = os.path.dirname(OUT)
+    cxx = ["g++", "-O2", "-std=c++17", "-fPIC", "-Wall"]
+    link = ["-L" + libdir, "-lbltcu", "-Wl,-rpath,$ORIGIN"]
+    subprocess.check_call(cxx + ["-shared", "-o", LIBBLT] + HOST_SRC + link)
+    subprocess.check_call(cxx + ["-o", RUN_BLT, os.path.join(HERE, "csrc", "host", "run_blt.cpp")] +
+                          ["-L" + libdir, "-lblt", "-lbltcu", "-Wl,-rpath,$ORIGIN"])
+    return LIBBLT
 
 
 if __name__ == "__main__":

@@ -1,0 +1,282 @@
+// context.cpp -- Context::check() and friends (reference: libblt/context.cc, libblt/expr.cc, libblt/parser.cc).
+// Plain C++17, no Boost.  The two hot seams go to the GPU library: bltcu_lll() and bltcu_closest_ex().
+#include "context.h"
+
+#include <math.h>
+
+#include <algorithm>
+#include <chrono>
+#include <iostream>
+#include <sstream>
+
+#include "../../../include/bltcu.h"
+#include "../../../include/codes.h"
+
+#define ERROR(x) do { std::cerr << "Error [" << __FILE__ << ":" << __LINE__ << "]: " << x << std::endl; } while (0)
+#define WARN(x) do { std::cerr << "Warning: " << x << std::endl; } while (0)
+
+// ---- integer helpers (boost::math::gcd / lcm semantics on int64; products wrap like the reference's) ----------
+static int64 gcd64(int64 a, int64 b) {
+    uint64_t x = a < 0 ? (uint64_t)0 - (uint64_t)a : (uint64_t)a, y = b < 0 ? (uint64_t)0 - (uint64_t)b : (uint64_t)b;
+    while (y) { const uint64_t t = x % y; x = y; y = t; }
+    return (int64)x;
+}
+static int64 lcm64(int64 a, int64 b) {
+    if (a == 0 || b == 0) return 0;
+    const int64 g = gcd64(a, b);
+    const uint64_t x = a < 0 ? (uint64_t)0 - (uint64_t)a : (uint64_t)a, y = b < 0 ? (uint64_t)0 - (uint64_t)b : (uint64_t)b;
+    return (int64)((x / (uint64_t)g) * y);  // wraps on overflow; callers test for it the way the reference does
+}
+
+// ---- rat64 ----------------------------------------------------------------------------------------------------
+static rat64 make_rat(__int128 n, __int128 d) {
+    rat64 r;
+    if (d == 0) { r.num = 0; r.den = 1; return r; }  // the reference throws bad_rational here
+    if (d < 0) { n = -n; d = -d; }
+    __int128 a = n < 0 ? -n : n, b = d;
+    while (b) { const __int128 t = a % b; a = b; b = t; }
+    if (a > 1) { n /= a; d /= a; }
+    r.num = (int64)n; r.den = (int64)d;
+    return r;
+}
+rat64::rat64(int64 n, int64 d) { *this = make_rat(n, d); }
+rat64 operator+(const rat64 &a, const rat64 &b) { return make_rat((__int128)a.num * b.den + (__int128)b.num * a.den, (__int128)a.den * b.den); }
+rat64 operator-(const rat64 &a, const rat64 &b) { return make_rat((__int128)a.num * b.den - (__int128)b.num * a.den, (__int128)a.den * b.den); }
+rat64 operator*(const rat64 &a, const rat64 &b) { return make_rat((__int128)a.num * b.num, (__int128)a.den * b.den); }
+bool operator<=(const rat64 &a, const rat64 &b) { return (__int128)a.num * b.den <= (__int128)b.num * a.den; }
+bool operator==(const rat64 &a, const rat64 &b) { return a.num == b.num && a.den == b.den; }
+
+// ---- Expr (libblt/expr.cc) ---------------------------------------------------------------------------------------
+rat64 Expr::operator[](int idx) const {
+    auto it = coeff_map_.find(idx);
+    return it == coeff_map_.end() ? rat64(0) : it->second;
+}
+Expr &Expr::operator+=(const Expr &rhs) {
+    for (auto &kv : rhs.coeff_map_) {
+        coeff_map_[kv.first] = (*this)[kv.first] + kv.second;
+        indices_.insert(kv.first);
+    }
+    const_ = const_ + rhs.const_;
+    return *this;
+}
+Expr &Expr::operator*=(const rat64 &s) {
+    for (auto &kv : coeff_map_) kv.second = kv.second * s;
+    const_ = const_ * s;
+    return *this;
+}
+Expr Expr::rounded() const {  // expr.cc:120-136: coefficients with denominator 1 are kept, others go through double
+    Expr r = *this;
+    for (int idx : indices_) {
+        const rat64 c = r[idx];
+        if (c.denominator() == 1) continue;
+        r.coeff_map_[idx] = rat64((int64)::round(c.to_double()));
+    }
+    r.const_ = rat64((int64)::round(r.const_.to_double()));
+    return r;
+}
+
+// ---- Context ----------------------------------------------------------------------------------------------------
+int Context::nvars() const { return (int)std::count(mask.begin(), mask.end(), true); }
+
+Expr Context::mkVar(const std::string &name) {  // context.cc:51-63
+    int idx;
+    auto it = std::find(names.begin(), names.end(), name);
+    if (it == names.end()) {
+        idx = (int)names.size();
+        names.push_back(name);
+        indices[name] = idx;
+        mask.resize(names.size());
+    } else idx = indices[name];
+    return Expr(idx);
+}
+bool Context::varActive(const std::string &name) const {
+    auto it = indices.find(name);
+    return it != indices.end() && mask[it->second];
+}
+int Context::assume(const rat64 &lower, const Expr &expr, const rat64 &upper) {  // context.cc:113-131
+    if (lower <= upper) {
+        try {
+            assumptions.push_back(Atom{lower, upper, expr});
+            for (int i : expr.indices()) mask[i] = true;
+            return BLT_STATUS_OK;
+        } catch (std::bad_alloc &e) {
+            ERROR("Context::assume: Out of memory" << std::endl << e.what());
+            return BLT_STATUS_ERROR;
+        }
+    }
+    return BLT_CHECK_UNSAT;
+}
+void Context::update_mask() {  // context.cc:379-393
+    mask.assign(names.size(), false);
+    for (auto &a : assumptions) for (int vi : a.expr.indices()) mask[vi] = true;
+}
+int Context::backtrack(SolvState st) {  // context.cc:318-330
+    if (st.pos <= assumptions.size()) {
+        assumptions.resize(st.pos);
+        update_mask();
+        return BLT_STATUS_OK;
+    }
+    return BLT_STATUS_ERROR;
+}
+int Context::get_model(const std::string &name, int64 *val) const {  // context.cc:286-293
+    auto it = model.find(name);
+    if (it != model.end()) { *val = it->second; return BLT_STATUS_OK; }
+    return BLT_STATUS_INPUT_ERROR;
+}
+
+int convert_to_integral(const std::vector<rat64> &L0, const std::vector<rat64> &C0, size_t nrows, size_t ncols,
+                        std::vector<int64> &L, std::vector<int64> &C) {  // context.cc:405-444
+    L.assign(nrows * ncols, 0);
+    C.assign(ncols * 2, 0);
+    for (size_t c = 0; c < ncols; ++c) {
+        int64 mult = 1;
+        for (size_t r = 0; r < nrows; ++r) {
+            const int64 t = lcm64(mult, L0[r * ncols + c].denominator());
+            if (t < mult) { ERROR("integer overflow detected!"); return BLT_STATUS_ERROR; }
+            mult = t;
+        }
+        mult = lcm64(mult, C0[2 * c].denominator());
+        mult = lcm64(mult, C0[2 * c + 1].denominator());
+        for (size_t r = 0; r < nrows; ++r) {
+            const rat64 &q = L0[r * ncols + c];
+            L[r * ncols + c] = (int64)((uint64_t)(mult / q.denominator()) * (uint64_t)q.numerator());
+        }
+        for (int t = 0; t < 2; ++t) {
+            const rat64 &q = C0[2 * c + t];
+            C[2 * c + t] = (int64)((uint64_t)(mult / q.denominator()) * (uint64_t)q.numerator());
+        }
+    }
+    return BLT_STATUS_OK;
+}
+
+int stretch_to_cube(std::vector<int64> &L, std::vector<int64> &C, size_t nrows, size_t ncols) {  // context.cc:455-501
+    int64 l = 1;
+    for (size_t i = 0; i < ncols; ++i) {
+        const int64 r = (int64)((uint64_t)C[2 * i + 1] - (uint64_t)C[2 * i]);
+        if (r <= 0) { ERROR("upper and lower bound coincide or conflict"); return BLT_STATUS_INPUT_ERROR; }
+        const int64 tmpl = lcm64(l, r);
+        if (tmpl == 0 || tmpl % l != 0 || tmpl % r != 0) { ERROR("integer overflow in lcm detected"); return BLT_STATUS_INPUT_ERROR; }
+        l = tmpl;
+    }
+    for (size_t i = 0; i < ncols; ++i) {
+        const int64 mult = l / (C[2 * i + 1] - C[2 * i]);
+        C[2 * i] = (int64)((uint64_t)C[2 * i] * (uint64_t)mult);
+        C[2 * i + 1] = (int64)((uint64_t)C[2 * i + 1] * (uint64_t)mult);
+        for (size_t j = 0; j < nrows; ++j) L[j * ncols + i] = (int64)((uint64_t)L[j * ncols + i] * (uint64_t)mult);
+    }
+    return BLT_STATUS_OK;
+}
+
+bool check_soln_host(const std::vector<int64> &lat, const std::vector<int64> &con, size_t n, size_t m,
+                     const std::vector<int64> &u) {  // closest.cc:330-340
+    for (size_t j = 0; j < m; ++j) {
+        uint64_t z = 0;
+        for (size_t i = 0; i < n; ++i) z += (uint64_t)u[i] * (uint64_t)lat[i * m + j];
+        const int64 zz = (int64)z;
+        if (con[2 * j] > zz || zz > con[2 * j + 1]) return false;
+    }
+    return true;
+}
+
+int Context::check() {  // context.cc:139-280
+    using clk = std::chrono::steady_clock;
+    const size_t m = (size_t)nvars();       // lattice vectors (rows) = active variables
+    const size_t n = assumptions.size();    // constraints = dimension of the ambient space
+    if (n == 0 || m == 0) {
+        WARN("Context::check: zero-dimensional input lattice or constraint set");
+        return BLT_STATUS_INPUT_ERROR;
+    }
+    // compute_lattice / compute_constr, context.cc:336-377
+    std::vector<rat64> L0(m * n), C0(n * 2);
+    for (size_t col = 0; col < n; ++col) {
+        const Expr &e = assumptions[col].expr;
+        size_t row = 0;
+        for (size_t idx = 0; idx < mask.size(); ++idx)
+            if (mask[idx]) L0[(row++) * n + col] = e[(int)idx];
+        const rat64 c = e.get_const();
+        C0[2 * col] = assumptions[col].lower - c;
+        C0[2 * col + 1] = assumptions[col].upper - c;
+    }
+    std::vector<int64> L, C;
+    int rc = convert_to_integral(L0, C0, m, n, L, C);
+    if (rc != BLT_STATUS_OK) return rc;
+    rc = stretch_to_cube(L, C, m, n);
+    if (rc != BLT_STATUS_OK) return rc;
+
+    // reduction seam: rank = LLL(L, U), context.cc:176
+    std::vector<int64> U(m * m);
+    int rank = 0;
+    auto t0 = clk::now();
+    rc = bltcu_lll(L.data(), U.data(), (int)m, (int)n, &rank);
+    last.lll_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
+    if (rc != BLT_STATUS_OK) return rc;
+    last.rank = rank;
+    if (rank == 0) return BLT_STATUS_INPUT_ERROR;
+    std::vector<int64> newL((size_t)rank * n);
+    for (size_t i = 0; i < (size_t)rank; ++i)
+        for (size_t j = 0; j < n; ++j) newL[i * n + j] = L[(i + m - rank) * n + j];
+
+    if (enable_yices_) {  // context.cc:210-228: this build carries no Yices; same failure as a missing libyices.so
+        ERROR("Context::check: ERROR Yices support was requested, but libyices.so failed to load!");
+        return BLT_STATUS_ERROR;
+    }
+
+    // search seam: closest(newL, C, yok, presoln_b, stats), context.cc:236
+    std::vector<int64> presoln_b((size_t)rank, 0);
+    bltcu_stats st;
+    t0 = clk::now();
+    rc = bltcu_closest_ex(newL.data(), C.data(), rank, (int)n, nullptr, presoln_b.data(), &st);
+    last.search_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
+    if (rc != BLT_STATUS_OK) return rc;
+    last.niter = st.niter; last.nprune = st.nprune;
+
+    // back-substitution soln = [0 .. 0 | presoln_b] * U, context.cc:246-254 (int64 products wrap like ublas prod)
+    std::vector<int64> soln(m, 0);
+    for (size_t j = 0; j < m; ++j) {
+        uint64_t acc = 0;
+        for (size_t i = m - rank; i < m; ++i) acc += (uint64_t)presoln_b[i - (m - rank)] * (uint64_t)U[i * m + j];
+        soln[j] = (int64)acc;
+    }
+    model.clear();
+    for (size_t i = 0, j = 0; i < mask.size(); ++i)
+        if (mask[i]) model[names[i]] = soln[j++];
+    return check_soln_host(newL, C, (size_t)rank, n, presoln_b) ? BLT_CHECK_SAT : BLT_CHECK_UNSAT;  // context.cc:276-279
+}
+
+// ---- parser (libblt/parser.cc:72-166) -------------------------------------------------------------------------------
+static int parse_row(std::istream &in, std::vector<int64> &row) {
+    std::vector<std::string> toks;
+    std::string w;
+    while (in >> w) toks.push_back(w);
+    const size_t nt = toks.size();
+    if (nt < 5 || toks[1] != "<=" || toks[nt - 2] != "<=") { ERROR("malformed row: " << w); return 1; }
+    try {
+        row.resize(nt - 2);
+        row[0] = std::stoll(toks[0]);
+        row[nt - 3] = std::stoll(toks[nt - 1]);
+        for (size_t i = 2; i < nt - 2; ++i) row[i - 1] = std::stoll(toks[i]);
+    } catch (const std::exception &e) {
+        ERROR("parser failed, expecting integer");
+        ERROR(e.what());
+        return 1;
+    }
+    return 0;
+}
+int read_bilp(std::istream &in, std::vector<int64> &L, std::vector<int64> &C, size_t &nr, size_t &nc) {
+    if (!in) { ERROR("could not open input stream for parsing"); return 1; }
+    nr = nc = 0;
+    L.clear(); C.clear();
+    std::string line;
+    while (std::getline(in, line)) {
+        std::vector<int64> row;
+        std::istringstream iss(line);
+        if (parse_row(iss, row) != 0 || (nc != 0 && row.size() - 2 != nc)) { ERROR("parse error on input line " << nr + 1); return 1; }
+        if (nc == 0) nc = row.size() - 2;
+        C.push_back(row.front());
+        C.push_back(row.back());
+        for (size_t i = 0; i < nc; ++i) L.push_back(row[i + 1]);
+        ++nr;
+    }
+    if (nr == 0 || nc == 0) { ERROR("input stream is empty"); return 1; }
+    return 0;
+}

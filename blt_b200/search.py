@@ -47,6 +47,8 @@ def lib() -> ctypes.CDLL:
         L.bltcu_closest_dev.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int,
                                         ctypes.POINTER(Opts), i64p, ctypes.POINTER(Stats)]
         L.bltcu_closest_dev.restype = ctypes.c_int
+        L.bltcu_lll.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+        L.bltcu_lll.restype = ctypes.c_int
         L.bltcu_check_soln.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
         L.bltcu_check_soln.restype = ctypes.c_int
         L.bltcu_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
@@ -166,3 +168,15 @@ def closest_noalloc(lat, con, device: int = 0):
                                      _p(sol, ctypes.c_int64), ctypes.byref(niter), ctypes.byref(nprune),
                                      ctypes.byref(found))
     return dict(rc=rc, sol=sol[:n], niter=int(niter.value), nprune=int(nprune.value), found=bool(found.value))
+
+
+def lll(B):
+    """LLL() of libblt/ntl_wrapper.h:20 (exact, delta = 3/4).  Returns (rank, B_reduced, U) as int64 arrays."""
+    B = _i64(B).copy()
+    r, c = B.shape
+    U = np.zeros((r, r), dtype=np.int64)
+    rk = ctypes.c_int(0)
+    rc = lib().bltcu_lll(_p(B, ctypes.c_int64), _p(U, ctypes.c_int64), r, c, ctypes.byref(rk))
+    if rc != BLT_STATUS_OK:
+        raise RuntimeError(f"bltcu_lll failed with status {rc}")
+    return int(rk.value), B, U

@@ -1,0 +1,51 @@
+/* blt.h -- the BLT C API, unchanged (reference: libblt/blt.h:16-134).  libblt.so of this repository exports these
+ * twelve functions with the reference's signatures, ownership rules and return codes; behind blt_check() the
+ * reduction and the search run through include/bltcu.h on the GPU. */
+#ifndef BLT_H
+#define BLT_H
+
+#include <stdint.h>
+
+#define __BLT_VERSION "1.0.0"
+
+typedef int64_t int64;
+
+typedef struct Context_internal_ *CContext;     /* a problem context */
+typedef struct Expr_internal_ *CExpr;           /* an affine expression, owned by the library */
+typedef struct SolvState_internal_ *CSolvState; /* a bookmark in the assumption stack */
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* libblt/blt.cc:25-28.  enable_yices != 0 asks for sound mode; this build has no Yices, so blt_check() then fails
+ * with BLT_STATUS_ERROR exactly like the reference does when libyices.so cannot be loaded (context.cc:211-226). */
+CContext blt_init(int enable_yices);
+/* libblt/blt.cc:30-35: a fresh (or the existing) variable of that name as an expression. */
+CExpr blt_var(CContext, const char *);
+/* libblt/blt.cc:37-42: the constant n/d. */
+CExpr blt_const(CContext, int64 n, int64 d);
+/* libblt/blt.cc:44-52 */
+CExpr blt_add(CContext, const CExpr, const CExpr);
+/* libblt/blt.cc:54-65: (n/d) * expr; NULL when d == 0. */
+CExpr blt_smul(CContext, int64 n, int64 d, CExpr expr);
+/* libblt/blt.cc:67-74: round(s * expr) coefficient-wise. */
+CExpr blt_tof(CContext, int64 s, CExpr expr);
+/* libblt/blt.cc:76-83: push n1/d1 <= expr <= n2/d2.  BLT_STATUS_OK, BLT_STATUS_ERROR, or BLT_CHECK_UNSAT when the
+ * bounds cross. */
+int blt_assume(CContext, int64 n1, int64 d1, const CExpr expr, int64 n2, int64 d2);
+/* libblt/blt.cc:85-88: BLT_CHECK_SAT / BLT_CHECK_UNSAT / BLT_STATUS_* */
+int blt_check(CContext);
+/* libblt/blt.cc:90-94 */
+int blt_model(const CContext, const char *name, int64 *x0);
+/* libblt/blt.cc:96-99 */
+CSolvState blt_save(CContext);
+/* libblt/blt.cc:101-105 */
+int blt_backtrack(CContext, CSolvState);
+/* libblt/blt.cc:109-120 */
+void blt_free(CContext);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -71,6 +71,11 @@ int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, int m, const
 int bltcu_closest_dev(const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
                       int64_t *sol, bltcu_stats *stats);
 
+/* LLL(): libblt/ntl_wrapper.h:20, libblt/ntl_wrapper.cc:37-52 (exact integral LLL, delta = 3/4, NTL::LLL(det2,B,U)).
+ * B: r x c row-major, reduced in place: zero rows first, the `rank` reduced basis rows last.  U: r x r output with
+ * U * B_in = B_out (may be NULL).  Returns BLT_STATUS_OK or BLT_STATUS_INPUT_ERROR. */
+int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank);
+
 /* check_soln(): libblt/closest.cc:330-340, evaluated on the device (int64, wraps like the reference). */
 int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok);
 

@@ -17,7 +17,7 @@ import oracle  # noqa: E402
 from tests.instances import dense_bilp, reduced_search_input  # noqa: E402
 
 n = 60
-w = int(sys.argv[1]) if len(sys.argv) > 1 else 105
+w = int(sys.argv[1]) if len(sys.argv) > 1 else 110
 seed = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 A, C = dense_bilp(n, w, seed)
 lat, con, U = reduced_search_input(A, C)

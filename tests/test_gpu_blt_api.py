@@ -1,0 +1,153 @@
+"""The blt.h API and run_blt on the GPU: the reference's own integration tests (libblt/test_context.cc,
+libblt/test_blt.c, test/UnitTests.hs) re-expressed against libblt.so, with the oracle's restated Context::check as the
+cross-check for decision, model and counters."""
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from fractions import Fraction as Fr
+from oracle import bltio, context
+from tests.conftest import ROOT
+
+pytestmark = pytest.mark.gpu
+RUN_BLT = os.path.join(ROOT, "blt_b200", "lib", "run_blt")
+SAT, UNSAT = 10, 11
+
+
+@pytest.fixture(scope="module")
+def api():
+    from blt_b200 import api
+    return api
+
+
+def _system(api, rows, names):
+    ctx = api.Context()
+    v = [ctx.var(nm) for nm in names]
+    for lo, coef, hi, const in rows:
+        e = ctx.const(const)
+        for c, x in zip(coef, v):
+            if c != 0:
+                e = e + c * x
+        assert ctx.assume(lo, e, hi) == 0
+    return ctx
+
+
+def _oracle(rows, nvars):
+    L0 = [[Fr(r[1][v]) for r in rows] for v in range(nvars)]
+    C0 = [[Fr(r[0]) - Fr(r[3]), Fr(r[2]) - Fr(r[3])] for r in rows]
+    return context.check(L0, C0)
+
+
+CASES = [
+    ("sat_2d", [(0, [1, 0], 3, 0), (3, [0, 1], 5, 0)], "xy", SAT),                                  # test_context.cc:107-121
+    ("sat_3d", [(-1, [1, 0, 1], 1, 0), (-3, [0, 1, -1], 5, 0), (-1, [1, 13, 101], 2, 0)], "uvz", SAT),  # :123-143
+    ("unsat", [(1, [3, 0], 2, 0), (3, [0, 5], 4, 0)], "ab", UNSAT),                                  # :145-153
+    ("pentagon", [(0, [0, 1], 2, 0), (-5, [1, 0], 3, 0), (-5, [1, -1], 2, 0), (-5, [-2, 1], 0, 0)], "xy", SAT),  # :187-208
+    ("2ip_hard", [(0, [3, -4], 20, 0), (-20, [1, -4], 0, 0), (-20, [-2, -1], -4, 0), (-5, [-1, -2], 20, 0),
+                  (-20, [2, -1], 4, 0)], "xy", SAT),                                                   # :219-242
+    ("affine", [(1, [1, 0], 2, 3), (100, [1, 1], 125, 6)], "xy", SAT),                               # :244-261
+    ("parallelogram", [(0, [4283000000, -3245000001], 999999, 0), (1, [4283000001, -3245000000], 1000000, 0)], "xy",
+     UNSAT),                                                                                           # test_blt.c:82-106
+    ("parallelogram_simple", [(0, [428300, -324501], 99, 0), (1, [428301, -324500], 100, 0)], "xy", UNSAT),  # :126-150
+]
+
+
+@pytest.mark.parametrize("name,rows,names,want", CASES, ids=[c[0] for c in CASES])
+def test_reference_systems(api, name, rows, names, want):
+    ctx = _system(api, rows, names)
+    rc = ctx.check()
+    assert rc == want
+    ref = _oracle(rows, len(names))
+    assert ref["rc"] == rc
+    if rc == SAT:
+        vals = [ctx.model(nm) for nm in names]
+        assert all(v[0] == 0 for v in vals)
+        x = [v[1] for v in vals]
+        for lo, coef, hi, const in rows:
+            s = sum(c * xi for c, xi in zip(coef, x)) + const
+            assert lo <= s <= hi
+        if name == "2ip_hard":
+            assert x == [2, 1]  # the unique model
+    else:
+        st = ctx.last_stats()
+        assert (st["niter"], st["nprune"]) == (ref["niter"], ref["nprune"])
+    ctx.free()
+
+
+def test_rational_rows(api):  # test_context.cc:156-178
+    h, t, f = Fr(1, 2), Fr(1, 3), Fr(1, 5)
+    ctx = api.Context()
+    u, v, z = ctx.var("u"), ctx.var("v"), ctx.var("z")
+    ctx.assume(-h, h * (u + z), h)
+    ctx.assume(-3 * t, t * (v - z), 5 * t)
+    ctx.assume(-f, f * (u + 13 * v + 101 * z), 2 * f)
+    assert ctx.check() == SAT
+    u0, v0, z0 = (ctx.model(n)[1] for n in "uvz")
+    assert -1 <= u0 + z0 <= 1 and -3 <= v0 - z0 <= 5 and -1 <= u0 + 13 * v0 + 101 * z0 <= 2
+    ctx.free()
+
+
+def test_incremental_check_and_backtrack(api):  # test_context.cc:123-143 + blt_save/blt_backtrack
+    ctx = api.Context()
+    u, v, z = ctx.var("u"), ctx.var("v"), ctx.var("z")
+    ctx.assume(-1, u + z, 1)
+    ctx.assume(-3, v - z, 5)
+    assert ctx.check() == SAT
+    st = ctx.save()
+    ctx.assume(1, 3 * u, 2)       # no integer u
+    assert ctx.check() == UNSAT
+    assert ctx.backtrack(st) == 0
+    assert ctx.check() == SAT
+    ctx.free()
+
+
+def test_yices_request_fails_like_missing_library(api):  # context.cc:211-226
+    ctx = api.Context(1)
+    x = ctx.var("x")
+    ctx.assume(0, x, 3)
+    assert ctx.check() == 1  # BLT_STATUS_ERROR
+    ctx.free()
+
+
+def test_tof(api):  # libblt/test_expr.cc: round(2/7 * (4x + y + 2/7)) -> x:1, y:0, const 0
+    ctx = api.Context()
+    x, y = ctx.var("x"), ctx.var("y")
+    e = (Fr(2, 7) * (4 * x + y + ctx.const(Fr(2, 7)))).tof(1)
+    ctx.assume(5, e, 6)   # i.e. 5 <= x <= 6
+    ctx.assume(0, y, 0 + 1)
+    assert ctx.check() == SAT
+    assert 5 <= ctx.model("x")[1] <= 6
+    ctx.free()
+
+
+@pytest.mark.parametrize("name", ["pentagon", "test_4x4"])
+def test_run_blt_fixtures(golden, name):  # config 1 of BASELINE.json
+    path = f"{golden}/{name}.bilp"
+    r = subprocess.run([RUN_BLT, "-m", path], capture_output=True, text=True, timeout=120)
+    assert r.returncode == SAT
+    lines = r.stdout.strip().splitlines()
+    assert re.fullmatch(rf"PROBLEM {re.escape(path)} RUNTIME \S+ niter XXX npru XXX rc XXX check  SAT ", lines[0])
+    mt = re.fullmatch(rf"PROBLEM {re.escape(path)} MODEL \((.*)\)", lines[1])
+    x = np.array([int(t) for t in mt.group(1).split(",")], dtype=np.int64)
+    A, C = bltio.read_bilp(path)
+    v = A @ x
+    assert (C[:, 0] <= v).all() and (v <= C[:, 1]).all()
+    ref = context.check_bilp(A, C)
+    assert ref["rc"] == SAT
+
+
+def test_run_blt_dense_unsat(tmp_path):  # config 2/5 shape: n = 20, counters through BLT_STATS
+    from tests.instances import dense_bilp
+    A, C = dense_bilp(20, 110, 0)
+    p = tmp_path / "d20.bilp"
+    p.write_text("\n".join(f"{C[i, 0]} <= {' '.join(str(a) for a in A[i])} <= {C[i, 1]}" for i in range(20)) + "\n")
+    r = subprocess.run([RUN_BLT, str(p)], capture_output=True, text=True, timeout=120, env=dict(os.environ, BLT_STATS="1"))
+    assert r.returncode == UNSAT and "check  UNSAT " in r.stdout
+    ref = context.check_bilp(A, C)
+    assert ref["rc"] == UNSAT
+    mt = re.search(r"BLT_STATS niter (\d+) nprune (\d+) rank (\d+)", r.stderr)
+    assert (int(mt.group(1)), int(mt.group(2)), int(mt.group(3))) == (ref["niter"], ref["nprune"], 20)

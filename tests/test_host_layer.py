@@ -1,0 +1,89 @@
+"""Host side of the boundary on a machine without a GPU: bltcu_lll against the oracle's exact LLL (bit-exact B, U,
+rank), the blt.h bookkeeping that never reaches the device, the .bilp parser through run_blt."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import blt_b200
+from blt_b200 import api
+from oracle import bltio
+from oracle.lll import lll as oracle_lll
+from tests.conftest import ROOT
+
+RUN_BLT = os.path.join(ROOT, "blt_b200", "lib", "run_blt")
+
+
+def _to_i64(M):
+    return np.array([[((int(x) + (1 << 63)) % (1 << 64)) - (1 << 63) for x in row] for row in M], dtype=np.int64)
+
+
+def test_lll_matches_oracle_random():
+    rng = np.random.default_rng(0)
+    for _ in range(150):
+        r, c = int(rng.integers(1, 10)), int(rng.integers(1, 10))
+        B = rng.integers(-9, 10, size=(r, c))
+        rk, Bo, Uo = blt_b200.lll(B)
+        rk2, B2, U2 = oracle_lll(B.tolist())
+        assert rk == rk2 and (Bo == _to_i64(B2)).all() and (Uo == _to_i64(U2)).all()
+
+
+@pytest.mark.parametrize("r,c,a", [(40, 20, 100), (20, 20, 100), (60, 60, 100), (24, 30, 10**9)])
+def test_lll_matches_oracle_shapes(r, c, a):  # 40 x 20: config 2, the dependent-row branch
+    B = np.random.default_rng(r * 1000 + c).integers(-a, a + 1, size=(r, c))
+    rk, Bo, Uo = blt_b200.lll(B)
+    rk2, B2, U2 = oracle_lll(B.tolist())
+    assert rk == rk2 == min(r, c)
+    assert (Bo == _to_i64(B2)).all() and (Uo == _to_i64(U2)).all()   # U narrowed like NTL's to_long()
+    assert not Bo[: r - rk].any()                                    # zero rows first (context.cc:176-181)
+
+
+def test_lll_rank_kats(golden):  # libblt/test_ntl.cc:32-44 (entries fit int64)
+    N = np.array(bltio.read_ntl(f"{golden}/lattice_95.tst"), dtype=np.int64)
+    assert blt_b200.lll(N)[0] == 64
+    assert blt_b200.lll(N[:, :32])[0] == 32
+
+
+def test_lll_fixture_bases(golden):
+    for name in ("test_95", "test_50"):
+        M = bltio.read_boost(f"{golden}/{name}.lat")
+        rk, Bo, Uo = blt_b200.lll(M)
+        rk2, B2, U2 = oracle_lll(M.tolist())
+        assert rk == rk2 == 64 and (Bo == _to_i64(B2)).all() and (Uo == _to_i64(U2)).all()
+
+
+def test_api_bookkeeping():  # libblt/test_context.cc:67-104 and blt.h contracts, no device needed
+    ctx = api.Context()
+    x, y = ctx.var("x"), ctx.var("y")
+    assert ctx.assume(0, x + y, 1) == blt_b200.BLT_STATUS_OK
+    s1 = ctx.save()
+    z = ctx.var("z")
+    assert ctx.assume(3, z, 5) == blt_b200.BLT_STATUS_OK
+    s2 = ctx.save()
+    assert ctx.backtrack(s1) == blt_b200.BLT_STATUS_OK
+    assert ctx.backtrack(s2) == blt_b200.BLT_STATUS_ERROR          # no backtracking forward
+    assert ctx.assume(2, x, 1) == blt_b200.BLT_CHECK_UNSAT          # crossing bounds (context.cc:113-131)
+    assert api.lib().blt_smul(ctx.h, 1, 0, x.h) is None             # d == 0 -> NULL (blt.cc:54-65)
+    assert ctx.model("nope")[0] == blt_b200.BLT_STATUS_INPUT_ERROR
+    ctx.free()
+
+
+def test_check_input_errors_before_the_device():
+    ctx = api.Context()
+    assert ctx.check() == blt_b200.BLT_STATUS_INPUT_ERROR           # nothing assumed (context.cc:146-149)
+    x = ctx.var("x")
+    assert ctx.assume(3, x, 3) == blt_b200.BLT_STATUS_OK
+    assert ctx.check() == blt_b200.BLT_STATUS_INPUT_ERROR           # zero width is rejected (context.cc:465-468)
+    ctx.free()
+
+
+def test_run_blt_cli_errors(tmp_path):
+    r = subprocess.run([RUN_BLT, "-v"], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "BLT version 1.0.0"
+    bad = tmp_path / "bad.bilp"
+    bad.write_text("1 <= 2 3\n")
+    r = subprocess.run([RUN_BLT, str(bad)], capture_output=True, text=True)
+    assert r.returncode == 1 and "cannot parse input file" in r.stderr
+    r = subprocess.run([RUN_BLT], capture_output=True, text=True)
+    assert r.returncode == 1 and "Usage:" in r.stdout
