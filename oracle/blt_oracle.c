@@ -17,8 +17,8 @@
  * PARITY STATUS -- read this.  The LP itself is solved in the reference by GLPK 4.55 (glp_simplex, primal,
  * cold slack basis per node), a third-party dependency that is not under /root/reference and cannot be built in
  * this image (no GLPK/NTL/Boost headers).  This oracle therefore restates the *published problem* (the LP above,
- * set up exactly as glpk_wrapper.cc:141-186 does) and solves it with its own deterministic exchange ("dual
- * simplex on reference sets") method, specified in DESIGN.md section 3.  Pinned against the reference's own known
+ * set up exactly as glpk_wrapper.cc:141-186 does) and solves it with its own deterministic dual simplex in the
+ * coordinates of the orthogonal complement of the free basis vectors, specified in DESIGN.md section 3.  Pinned against the reference's own known
  * answers: every infdist value / minimiser / rounding in libblt/test_glpk.cc:35-169, the prune sets of
  * libblt/test_yices.cc:37-123, closest() results of libblt/test_closest.cc and the SAT decisions of
  * libblt/test_regression.cc:84-106 (tests/test_oracle_kats.py).  NOT pinned by anything in the reference, hence
@@ -93,241 +93,317 @@ static double treedot(const double *a, const double *b, int len) {
     return p[0];
 }
 
-/* ---- LP engine: basis inverse H (K x K), reference rows/signs, current point z = (t, x_0..x_{K-2}) ---- */
+static double butterfly32(double *p) {
+    double q[32];
+    for (int off = 16; off >= 1; off >>= 1) {
+        for (int l = 0; l < 32; ++l) q[l] = p[l] + p[l ^ off];
+        memcpy(p, q, 32 * sizeof(double));
+    }
+    return p[0];
+}
+
+/* ---- geometry shared by every node of one problem: B^T = Q R (orthonormal Q by Gram-Schmidt applied twice) ----
+ * q_0..q_{n-1} span the basis rows in order, q_n..q_{m-1} complete R^m.  Qrev[j][i] = q_{m-1-i}[j], so that the
+ * first `qd` entries of row j of Qrev are row j of N = [q_{m-1} .. q_{m-qd}], the complement of the first m-qd
+ * directions.  Rm[j][i] = q_j . b_i (upper triangular), QTp[j] = q_j . p. */
 typedef struct {
-    int n, m, ld;
-    const double *B; /* n x m row-major, (double)lat  (closest.cc:203) */
-    int K;
-    double *H;       /* ld x ld; H[v*ld+s], v = variable (0 = t, i+1 = x_i), s = reference slot */
-    int *row, *sg;   /* per slot: lattice coordinate index j (or -1 = artificial), sign sigma */
-    double *z, *w, *g, *a, *cS, *lam;
-    int *tmpi, *tmps;
-    unsigned char *used;
+    int n, m;
+    double *Q;    /* m x m, row t = vector q_t */
+    double *Qrev; /* m x m */
+    double *Rm;   /* n x n */
+    double *QTp;  /* m */
+} Geo;
+
+static void geo_project(const Geo *g, int t, double *v, double *coef) { /* v -= (q_j . v) q_j for j < t, twice */
+    const int m = g->m;
+    for (int pass = 0; pass < 2; ++pass)
+        for (int j = 0; j < t; ++j) {
+            const double *qj = g->Q + (size_t)j * m;
+            const double h = treedot(qj, v, m);
+            for (int e = 0; e < m; ++e) v[e] = fma(-h, qj[e], v[e]);
+            if (coef) coef[j] += h;
+        }
+}
+static int geo_build(Geo *g, const double *B, const double *p, int n, int m) {
+    g->n = n; g->m = m;
+    g->Q = (double *)calloc((size_t)m * m, sizeof(double)); g->Qrev = (double *)calloc((size_t)m * m, sizeof(double));
+    g->Rm = (double *)calloc((size_t)n * n, sizeof(double)); g->QTp = (double *)calloc(m, sizeof(double));
+    double *v = (double *)calloc(m, sizeof(double)), *coef = (double *)calloc(m, sizeof(double));
+    int ok = 1;
+    for (int t = 0; t < m && ok; ++t) {
+        if (t < n) memcpy(v, B + (size_t)t * m, m * sizeof(double));
+        else { /* completion: the unit vector with the largest part outside the current span (ties: lowest j) */
+            int best = -1; double bv = -1.0;
+            for (int j = 0; j < m; ++j) {
+                double sres = 1.0;
+                for (int i = 0; i < t; ++i) { const double x = g->Q[(size_t)i * m + j]; sres = fma(-x, x, sres); }
+                if (sres > bv) { bv = sres; best = j; }
+            }
+            memset(v, 0, m * sizeof(double)); v[best] = 1.0;
+        }
+        memset(coef, 0, m * sizeof(double));
+        geo_project(g, t, v, coef);
+        const double nrm = sqrt(treedot(v, v, m));
+        if (!(nrm > 0.0)) { ok = 0; break; }
+        for (int e = 0; e < m; ++e) g->Q[(size_t)t * m + e] = v[e] / nrm;
+        if (t < n) { for (int j = 0; j < t; ++j) g->Rm[(size_t)j * n + t] = coef[j]; g->Rm[(size_t)t * n + t] = nrm; }
+    }
+    for (int j = 0; j < m; ++j) for (int i = 0; i < m; ++i) g->Qrev[(size_t)j * m + i] = g->Q[(size_t)(m - 1 - i) * m + j];
+    for (int t = 0; t < m; ++t) g->QTp[t] = treedot(g->Q + (size_t)t * m, p, m);
+    free(v); free(coef);
+    return ok ? 0 : -1;
+}
+static void geo_free(Geo *g) { free(g->Q); free(g->Qrev); free(g->Rm); free(g->QTp); }
+
+/* ---- LP engine in complement coordinates -------------------------------------------------------------------
+ * Node LP(kk):  min |r|_inf  s.t.  N^T r = chat   (N = first qd = m-kk columns of Qrev, chat = N^T c).
+ * Vertex: rows in Z (qd-1 of them, "basic") are strictly inside, all other rows sit at r_j = sg_j t.
+ * A = [ s | n_z1 .. n_z(qd-1) ] with s = sum_{j active} sg_j n_j;  H = A^-1;  (t, r_Z) = H chat;  y = row 0 of H is
+ * the dual vector, invariant sg_j (n_j . y) >= 0 for active j, hence t = y . chat is a lower bound of the optimum. */
+typedef struct {
+    const Geo *g;
+    int m, ld, qd;
+    double *H;
+    int *zrow, *pos;     /* zrow[p] = row held by basic position p >= 1 (-1 = artificial); pos[j] = position or 0 */
+    signed char *sg;     /* sign of each active row */
+    double *chat, *val, *alpha, *beta, *w, *a, *r, *v;
     uint64_t pivots, refactors, quick, colds;
 } LP;
 
-static void lp_gather(LP *lp, const double *c) {
-    for (int s = 0; s < lp->K; ++s) lp->cS[s] = lp->row[s] >= 0 ? c[lp->row[s]] : 0.0;
-}
-static void lp_point(LP *lp) { /* z = H cS, one dot4 per variable */
-    for (int v = 0; v < lp->K; ++v) lp->z[v] = dot4(lp->H + (size_t)v * lp->ld, 1, lp->cS, 1, lp->K);
-}
-/* entering row for coordinate q with sign sq: a = (sq, B[0][q], ..., B[K-2][q]) */
-static void lp_row(LP *lp, int q, int sq) {
-    lp->a[0] = (double)sq;
-    for (int i = 0; i + 1 < lp->K; ++i) lp->a[i + 1] = lp->B[(size_t)i * lp->m + q];
-}
-static void lp_w(LP *lp) { /* w_s = sum_v a_v H[v][s] */
-    for (int s = 0; s < lp->K; ++s) lp->w[s] = dot4(lp->a, 1, lp->H + s, lp->ld, lp->K);
-}
-/* replace slot l by the row whose coefficients w.r.t. the current rows are w: H <- H - g (w - e_l)^T, g = H[:,l]/w_l */
-static void lp_pivot(LP *lp, int l) {
-    const int K = lp->K, ld = lp->ld;
-    const double wl = lp->w[l];
-    for (int v = 0; v < K; ++v) lp->g[v] = lp->H[(size_t)v * ld + l] / wl;
-    for (int v = 0; v < K; ++v) {
-        double *Hv = lp->H + (size_t)v * ld;
-        const double gv = lp->g[v];
-        for (int s = 0; s < K; ++s) Hv[s] = (s == l) ? gv : fma(-gv, lp->w[s], Hv[s]);
-    }
-    lp->pivots++;
-}
-/* ratio test: among slots with sq*sg_s*w_s > PIV_TOL*|w|_inf pick min max(0,sg_s*lambda_s)/(sq*sg_s*w_s); ties: lowest s */
-static int lp_ratio(LP *lp, int sq) {
-    const int K = lp->K;
-    double wmax = 0.0;
-    for (int s = 0; s < K; ++s) if (fabs(lp->w[s]) > wmax) wmax = fabs(lp->w[s]);
-    const double thr = PIV_TOL * wmax;
-    int best = -1;
-    double br = 0.0;
-    for (int s = 0; s < K; ++s) {
-        const double den = (double)(sq * lp->sg[s]) * lp->w[s];
-        if (!(den > thr)) continue;
-        double num = (double)lp->sg[s] * lp->H[s]; /* row 0 of H = lambda */
-        if (num < 0.0) num = 0.0;
-        const double r = num / den;
-        if (best < 0 || r < br) { best = s; br = r; }
-    }
-    return best;
-}
-
-/* rebuild H from the current reference rows/signs (Gauss-Jordan as K pivots from the identity) */
-static int lp_refactor(LP *lp) {
-    const int K = lp->K, ld = lp->ld;
-    for (int s = 0; s < K; ++s) { lp->tmpi[s] = lp->row[s]; lp->tmps[s] = lp->sg[s]; lp->row[s] = -1; lp->sg[s] = 1; }
-    for (int v = 0; v < K; ++v) for (int s = 0; s < K; ++s) lp->H[(size_t)v * ld + s] = (v == s) ? 1.0 : 0.0;
-    for (int i = 0; i < K; ++i) {
-        lp_row(lp, lp->tmpi[i], lp->tmps[i]);
-        lp_w(lp);
-        int l = -1; double bw = 0.0;
-        for (int s = 0; s < K; ++s) if (lp->row[s] < 0 && fabs(lp->w[s]) > bw) { bw = fabs(lp->w[s]); l = s; }
-        if (l < 0) return -1;
-        lp_pivot(lp, l);
-        lp->row[l] = lp->tmpi[i]; lp->sg[l] = lp->tmps[i];
-    }
-    lp->refactors++;
-    return 0;
-}
-
-static double residual(const LP *lp, const double *c, int j) {
-    return c[j] - dot4(lp->B + j, lp->m, lp->z + 1, 1, lp->K - 1);
-}
-
-/* cold start for LP(K-1) with right-hand side c: build a dual-feasible basis of K real rows.
- * If K-1 == m (square system, only reachable for the root solve) there is no K-th row: stop after stage A with
- * the interpolating point in z and return 1. */
-static int lp_cold(LP *lp, int K, const double *c) {
-    const int ld = lp->ld, m = lp->m, kk = K - 1;
-    lp->K = K; lp->colds++;
-    for (int s = 0; s < K; ++s) { lp->row[s] = -1; lp->sg[s] = 1; }
-    for (int v = 0; v < K; ++v) for (int s = 0; s < K; ++s) lp->H[(size_t)v * ld + s] = (v == s) ? 1.0 : 0.0;
-    memset(lp->used, 0, (size_t)m);
-    /* stage A: one real row per x-variable slot, largest pivot first */
-    for (int v = 1; v <= kk; ++v) {
-        int q = -1; double bp = 0.0;
-        for (int j = 0; j < m; ++j) {
-            if (lp->used[j]) continue;
-            lp_row(lp, j, 1);
-            const double pv = fabs(dot4(lp->a, 1, lp->H + v, ld, K));
-            if (pv > bp) { bp = pv; q = j; }
-        }
-        if (q < 0) return -1;
-        lp_row(lp, q, 1); lp_w(lp); lp_pivot(lp, v);
-        lp->row[v] = q; lp->sg[v] = 1; lp->used[q] = 1;
-    }
-    lp_gather(lp, c); lp_point(lp);
-    if (kk >= m) return 1;
-    /* stage B: the unused row with the largest interpolation residual takes slot 0 (the t slot) */
-    {
-        int q = -1; double br = -1.0;
-        for (int j = 0; j < m; ++j) {
-            if (lp->used[j]) continue;
-            const double r = fabs(residual(lp, c, j));
-            if (r > br) { br = r; q = j; }
-        }
-        if (q < 0) return -1;
-        const double rho = dot4(lp->B + q, m, lp->H + ld, ld, kk); /* sum_i B[i][q] * H[i+1][0] */
-        const int sq = (rho >= 0.0) ? 1 : -1;
-        lp_row(lp, q, sq); lp_w(lp);
-        if (lp->w[0] == 0.0) return -1;
-        lp_pivot(lp, 0);
-        lp->row[0] = q; lp->sg[0] = sq; lp->used[q] = 1;
-    }
-    /* sign fix: sigma'_s = sign(lambda_s); Sherman-Morrison on the t column of M */
-    {
-        int any = 0;
-        for (int s = 0; s < K; ++s) {
-            const double l = lp->H[s];
-            lp->lam[s] = l;
-            const int ns = l > 0.0 ? 1 : (l < 0.0 ? -1 : lp->sg[s]);
-            lp->w[s] = (double)(ns - lp->sg[s]); /* Delta */
-            lp->cS[s] = (double)ns;
-            if (ns != lp->sg[s]) any = 1;
-            lp->tmps[s] = ns;
-        }
-        if (any) {
-            const double D = dot4(lp->lam, 1, lp->cS, 1, K);
-            if (!(D > 0.0)) return -1;
-            for (int v = 0; v < K; ++v) lp->g[v] = dot4(lp->H + (size_t)v * ld, 1, lp->w, 1, K) / D;
-            for (int v = 0; v < K; ++v) {
-                double *Hv = lp->H + (size_t)v * ld;
-                for (int s = 0; s < K; ++s) Hv[s] = fma(-lp->g[v], lp->lam[s], Hv[s]);
-            }
-            for (int s = 0; s < K; ++s) lp->sg[s] = lp->tmps[s];
-        }
-    }
-    return 0;
-}
-
-static void lp_flip(LP *lp) { /* flip every sign: negate row 0 of H */
-    for (int s = 0; s < lp->K; ++s) { lp->H[s] = -lp->H[s]; lp->sg[s] = -lp->sg[s]; }
-    lp->z[0] = -lp->z[0];
-}
-
-/* Solve the node LP(K-1) from the current (dual-feasible) basis.  radius = +inf disables pruning. */
-static int lp_solve(LP *lp, const double *c, double radius, double *d_out, double *xlast_out) {
-    const int K = lp->K, m = lp->m;
-    lp_gather(lp, c);
-    /* quick bound: |lambda . cS| is a lower bound on the optimum */
-    {
-        double tq = treedot(lp->H, lp->cS, K);
-        if (tq < 0.0) tq = -tq;
-        if (!approximatelyLE(tq, radius, DIST_EPS)) { lp->quick++; return NODE_PRUNE; }
-    }
-    lp_point(lp);
-    if (lp->z[0] < 0.0) lp_flip(lp);
-    double cmax = 0.0;
-    for (int j = 0; j < m; ++j) if (fabs(c[j]) > cmax) cmax = fabs(c[j]);
-    const int cap = 100 * K + 1000;
-    int refactored = 0;
-    for (int iter = 0;; ++iter) {
-        const double t = lp->z[0];
-        if (!approximatelyLE(t, radius, DIST_EPS)) return NODE_PRUNE;
-        int q = -1; double rmax = -1.0, rq = 0.0;
-        for (int j = 0; j < m; ++j) {
-            const double r = residual(lp, c, j);
-            if (fabs(r) > rmax) { rmax = fabs(r); q = j; rq = r; }
-        }
-        const double tol = EPS_OPT * (cmax + t);
-        if (rmax <= t + tol) { *d_out = t; *xlast_out = lp->z[K - 1]; return NODE_EXPLORE; }
-        if (iter >= cap) return NODE_FAIL;
-        int dup = 0;
-        for (int s = 0; s < K; ++s) if (lp->row[s] == q) dup = 1;
-        if (dup) { /* a reference row is violated: H has drifted; rebuild once */
-            if (refactored) return NODE_FAIL;
-            refactored = 1;
-            if (lp_refactor(lp)) return NODE_FAIL;
-            lp_gather(lp, c); lp_point(lp);
-            if (lp->z[0] < 0.0) lp_flip(lp);
-            continue;
-        }
-        const int sq = rq > 0.0 ? 1 : -1;
-        lp_row(lp, q, sq); lp_w(lp);
-        const int l = lp_ratio(lp, sq);
-        if (l < 0) return NODE_FAIL;
-        lp_pivot(lp, l);
-        lp->row[l] = q; lp->sg[l] = sq;
-        const double delta = (double)sq * (rmax - t);
-        for (int v = 0; v < K; ++v) lp->z[v] = fma(lp->g[v], delta, lp->z[v]);
-    }
-}
-
-/* child transform: variable x_{K-2} (last row of H) becomes fixed; dir = sgn(x_last - u).  K -> K-1. */
-static int lp_child(LP *lp, int dir) {
-    const int K = lp->K, ld = lp->ld;
-    for (int s = 0; s < K; ++s) lp->w[s] = lp->H[(size_t)(K - 1) * ld + s];
-    const int l = lp_ratio(lp, -dir);
-    if (l < 0) return -1;
-    const double wl = lp->w[l];
-    for (int v = 0; v < K - 1; ++v) lp->g[v] = lp->H[(size_t)v * ld + l] / wl;
-    for (int v = 0; v < K - 1; ++v) {
-        double *Hv = lp->H + (size_t)v * ld;
-        const double gv = lp->g[v];
-        for (int s = 0; s < K; ++s) if (s != l) Hv[s] = fma(-gv, lp->w[s], Hv[s]);
-        if (l != K - 1) Hv[l] = Hv[K - 1];
-    }
-    if (l != K - 1) { lp->row[l] = lp->row[K - 1]; lp->sg[l] = lp->sg[K - 1]; }
-    lp->K = K - 1;
-    lp->pivots++;
-    return 0;
-}
-
-static LP *lp_new(int n, int m, const double *B) {
+static LP *lp_new(const Geo *g) {
     LP *lp = (LP *)calloc(1, sizeof(LP));
-    const int ld = n + 1;
-    lp->n = n; lp->m = m; lp->ld = ld; lp->B = B;
+    const int m = g->m, ld = m + 1;
+    lp->g = g; lp->m = m; lp->ld = ld;
     lp->H = (double *)calloc((size_t)ld * ld, sizeof(double));
-    lp->row = (int *)calloc(ld, sizeof(int)); lp->sg = (int *)calloc(ld, sizeof(int));
-    lp->tmpi = (int *)calloc(ld, sizeof(int)); lp->tmps = (int *)calloc(ld, sizeof(int));
-    lp->z = (double *)calloc(ld, sizeof(double)); lp->w = (double *)calloc(ld, sizeof(double));
-    lp->g = (double *)calloc(ld, sizeof(double)); lp->a = (double *)calloc(ld, sizeof(double));
-    lp->cS = (double *)calloc(ld, sizeof(double)); lp->lam = (double *)calloc(ld, sizeof(double));
-    lp->used = (unsigned char *)calloc(m > 0 ? m : 1, 1);
+    lp->zrow = (int *)calloc(ld, sizeof(int)); lp->pos = (int *)calloc(m, sizeof(int));
+    lp->sg = (signed char *)calloc(m, 1);
+    lp->chat = (double *)calloc(ld, sizeof(double)); lp->val = (double *)calloc(ld, sizeof(double));
+    lp->alpha = (double *)calloc(m, sizeof(double)); lp->beta = (double *)calloc(m, sizeof(double));
+    lp->w = (double *)calloc(ld, sizeof(double)); lp->a = (double *)calloc(ld, sizeof(double));
+    lp->r = (double *)calloc(m, sizeof(double)); lp->v = (double *)calloc(ld, sizeof(double));
     return lp;
 }
 static void lp_free(LP *lp) {
-    free(lp->H); free(lp->row); free(lp->sg); free(lp->tmpi); free(lp->tmps); free(lp->z); free(lp->w);
-    free(lp->g); free(lp->a); free(lp->cS); free(lp->lam); free(lp->used); free(lp);
+    free(lp->H); free(lp->zrow); free(lp->pos); free(lp->sg); free(lp->chat); free(lp->val); free(lp->alpha);
+    free(lp->beta); free(lp->w); free(lp->a); free(lp->r); free(lp->v); free(lp);
+}
+static void lp_values(LP *lp) {
+    for (int p = 0; p < lp->qd; ++p) lp->val[p] = dot4(lp->H + (size_t)p * lp->ld, 1, lp->chat, 1, lp->qd);
+}
+static void lp_flip(LP *lp) {
+    for (int c = 0; c < lp->qd; ++c) lp->H[c] = -lp->H[c];
+    for (int j = 0; j < lp->m; ++j) lp->sg[j] = (signed char)-lp->sg[j];
+    lp->val[0] = -lp->val[0];
+}
+/* alpha_j = n_j . y, beta_j = n_j . H[pe] for the active rows; returns |N y|_1 */
+static double lp_alpha_beta(LP *lp, int pe) {
+    const int m = lp->m, qd = lp->qd;
+    double part[32];
+    for (int l = 0; l < 32; ++l) part[l] = 0.0;
+    for (int j = 0; j < m; ++j) {
+        if (lp->pos[j]) { lp->alpha[j] = 0.0; lp->beta[j] = 0.0; continue; }
+        const double *nj = lp->g->Qrev + (size_t)j * m;
+        lp->alpha[j] = dot4(nj, 1, lp->H, 1, qd);
+        lp->beta[j] = dot4(nj, 1, lp->H + (size_t)pe * lp->ld, 1, qd);
+        part[j & 31] += fabs(lp->alpha[j]);
+    }
+    return butterfly32(part);
+}
+/* Entering row (Harris two-pass ratio test).  With den_j = -se*sg_j*beta_j and num_j = max(0, sg_j*alpha_j):
+ * pass 1: theta_max = min over den_j > dmin of (num_j + HARRIS_DELTA) / den_j;
+ * pass 2: among den_j > dmin with num_j/den_j <= theta_max the largest den_j wins (ties: lowest j).
+ * dmin = 0 when a row of Z leaves (its pivot is num+den), PIV_TOL*scale when an artificial leaves (its pivot is den).
+ * If no row qualifies and a row of Z leaves, the dual vector moves all the way onto the leaving row's own ray, where
+ * exactly the rows with beta_j = 0 vanish: take the one with the largest alpha among |beta_j| <= PIV_TOL*scale. */
+#define HARRIS_DELTA 1.0e-10
+static int lp_ratio(LP *lp, int se, int pe) {
+    const int m = lp->m;
+    const int artificial = lp->zrow[pe] < 0;
+    double scale = 0.0;
+    for (int c = 0; c < lp->qd; ++c) if (fabs(lp->H[(size_t)pe * lp->ld + c]) > scale) scale = fabs(lp->H[(size_t)pe * lp->ld + c]);
+    for (int j = 0; j < m; ++j) if (!lp->pos[j] && fabs(lp->beta[j]) > scale) scale = fabs(lp->beta[j]);
+    const double tiny = PIV_TOL * scale, dmin = artificial ? tiny : 0.0;
+    double tmax = INFINITY;
+    for (int j = 0; j < m; ++j) {
+        if (lp->pos[j]) continue;
+        const double den = -(double)(se * lp->sg[j]) * lp->beta[j];
+        if (!(den > dmin)) continue;
+        double num = (double)lp->sg[j] * lp->alpha[j];
+        if (num < 0.0) num = 0.0;
+        const double rt = (num + HARRIS_DELTA) / den;
+        if (rt < tmax) tmax = rt;
+    }
+    int best = -1; double bd = 0.0;
+    for (int j = 0; j < m; ++j) {
+        if (lp->pos[j]) continue;
+        const double den = -(double)(se * lp->sg[j]) * lp->beta[j];
+        if (!(den > dmin)) continue;
+        double num = (double)lp->sg[j] * lp->alpha[j];
+        if (num < 0.0) num = 0.0;
+        if (num / den <= tmax && den > bd) { bd = den; best = j; }
+    }
+    if (best >= 0 || artificial) return best;
+    double ba = -1.0;
+    for (int j = 0; j < m; ++j) {
+        if (lp->pos[j] || fabs(lp->beta[j]) > tiny) continue;
+        if (fabs(lp->alpha[j]) > ba) { ba = fabs(lp->alpha[j]); best = j; }
+    }
+    return best;
+}
+/* basic position pe (row zrow[pe], or artificial) leaves with sign se, active row l takes the position */
+static int lp_replace(LP *lp, int pe, int l, int se) {
+    const int qd = lp->qd, ld = lp->ld, m = lp->m;
+    double *H = lp->H, *Hp = H + (size_t)pe * ld;
+    const int e = lp->zrow[pe];
+    if (e >= 0) for (int c = 0; c < qd; ++c) Hp[c] = Hp[c] - (double)se * H[c];       /* s += se * n_e */
+    const double *nl = lp->g->Qrev + (size_t)l * m;
+    for (int i = 0; i < qd; ++i) lp->w[i] = dot4(H + (size_t)i * ld, 1, nl, 1, qd);
+    const double wp = lp->w[pe];
+    if (wp == 0.0) return -1;
+    for (int c = 0; c < qd; ++c) lp->v[c] = Hp[c] / wp;
+    for (int i = 0; i < qd; ++i) {
+        if (i == pe) continue;
+        double *Hi = H + (size_t)i * ld;
+        const double wi = lp->w[i];
+        for (int c = 0; c < qd; ++c) Hi[c] = fma(-wi, lp->v[c], Hi[c]);
+    }
+    const double sl = (double)lp->sg[l];
+    for (int c = 0; c < qd; ++c) Hp[c] = lp->v[c] + sl * H[c];                        /* s -= sg_l * n_l */
+    if (e >= 0) { lp->sg[e] = (signed char)se; lp->pos[e] = 0; }
+    lp->zrow[pe] = l; lp->pos[l] = pe;
+    lp->pivots++;
+    return 0;
+}
+/* first coordinate: qd = 1, no basic rows */
+static int lp_init1(LP *lp) {
+    const int m = lp->m;
+    double part[32];
+    for (int l = 0; l < 32; ++l) part[l] = 0.0;
+    for (int j = 0; j < m; ++j) {
+        const double x = lp->g->Qrev[(size_t)j * m];
+        lp->sg[j] = x >= 0.0 ? 1 : -1; lp->pos[j] = 0;
+        part[j & 31] += fabs(x);
+    }
+    const double s = butterfly32(part);
+    if (!(s > 0.0)) return -1;
+    lp->H[0] = 1.0 / s; lp->qd = 1; lp->zrow[0] = -1;
+    lp->colds++;
+    return 0;
+}
+/* one more coordinate (index qd): border H with an artificial basic column at position qd */
+static void lp_extend(LP *lp) {
+    const int m = lp->m, qd = lp->qd, ld = lp->ld;
+    const double *Qr = lp->g->Qrev;
+    double part[32];
+    for (int l = 0; l < 32; ++l) part[l] = 0.0;
+    for (int j = 0; j < m; ++j) if (!lp->pos[j]) part[j & 31] = fma((double)lp->sg[j], Qr[(size_t)j * m + qd], part[j & 31]);
+    lp->a[0] = butterfly32(part);
+    for (int p = 1; p < qd; ++p) lp->a[p] = Qr[(size_t)lp->zrow[p] * m + qd];
+    for (int c = 0; c < qd; ++c) lp->H[(size_t)qd * ld + c] = -dot4(lp->a, 1, lp->H + c, ld, qd);
+    for (int p = 0; p < qd; ++p) lp->H[(size_t)p * ld + qd] = 0.0;
+    lp->H[(size_t)qd * ld + qd] = 1.0;
+    lp->zrow[qd] = -1;
+    lp->qd = qd + 1;
+}
+/* drive the artificial at the last position out; sf = sign of its value (= side of the fixed coefficient) */
+static int lp_drop_artificial(LP *lp, int sf) {
+    const int pe = lp->qd - 1;
+    lp_alpha_beta(lp, pe);
+    const int l = lp_ratio(lp, sf, pe);
+    if (l < 0) return -1;
+    return lp_replace(lp, pe, l, sf);
+}
+/* rebuild H = A^-1 from Z and the signs: plain Gauss-Jordan with row pivoting (rare path) */
+static int lp_refactor(LP *lp) {
+    const int qd = lp->qd, ld = lp->ld, m = lp->m;
+    const double *Qr = lp->g->Qrev;
+    double *A = (double *)calloc((size_t)qd * qd, sizeof(double));
+    for (int c = 0; c < qd; ++c) { /* A[c][0] = s_c, A[c][p] = n_{z_p}[c] */
+        double s = 0.0;
+        for (int j = 0; j < m; ++j) if (!lp->pos[j]) s = fma((double)lp->sg[j], Qr[(size_t)j * m + c], s);
+        A[(size_t)c * qd] = s;
+        for (int p = 1; p < qd; ++p) A[(size_t)c * qd + p] = lp->zrow[p] >= 0 ? Qr[(size_t)lp->zrow[p] * m + c] : (c == p ? 1.0 : 0.0);
+    }
+    for (int i = 0; i < qd; ++i) for (int c = 0; c < qd; ++c) lp->H[(size_t)i * ld + c] = (i == c) ? 1.0 : 0.0;
+    int rc = 0;
+    for (int col = 0; col < qd; ++col) {
+        int pr = -1; double bv = 0.0;
+        for (int i = col; i < qd; ++i) if (fabs(A[(size_t)i * qd + col]) > bv) { bv = fabs(A[(size_t)i * qd + col]); pr = i; }
+        if (pr < 0) { rc = -1; break; }
+        if (pr != col) {
+            for (int c = 0; c < qd; ++c) {
+                double t = A[(size_t)pr * qd + c]; A[(size_t)pr * qd + c] = A[(size_t)col * qd + c]; A[(size_t)col * qd + c] = t;
+                t = lp->H[(size_t)pr * ld + c]; lp->H[(size_t)pr * ld + c] = lp->H[(size_t)col * ld + c]; lp->H[(size_t)col * ld + c] = t;
+            }
+        }
+        const double pv = A[(size_t)col * qd + col];
+        for (int c = 0; c < qd; ++c) { A[(size_t)col * qd + c] /= pv; lp->H[(size_t)col * ld + c] /= pv; }
+        for (int i = 0; i < qd; ++i) {
+            if (i == col) continue;
+            const double f = A[(size_t)i * qd + col];
+            if (f == 0.0) continue;
+            for (int c = 0; c < qd; ++c) {
+                A[(size_t)i * qd + c] = fma(-f, A[(size_t)col * qd + c], A[(size_t)i * qd + c]);
+                lp->H[(size_t)i * ld + c] = fma(-f, lp->H[(size_t)col * ld + c], lp->H[(size_t)i * ld + c]);
+            }
+        }
+    }
+    free(A);
+    lp->refactors++;
+    return rc;
+}
+
+/* full residual vector and its image: v[i] = sum_j Qrev[j][i] r_j for i < nv */
+static void lp_image(LP *lp, int nv) {
+    const int m = lp->m;
+    for (int j = 0; j < m; ++j) lp->r[j] = lp->pos[j] ? lp->val[lp->pos[j]] : (double)lp->sg[j] * lp->val[0];
+    for (int i = 0; i < nv; ++i) lp->v[i] = dot4(lp->g->Qrev + i, m, lp->r, 1, m);
+}
+
+/* Solve from the current dual-feasible vertex.  radius = +inf disables pruning.  On NODE_EXPLORE *d_out is the
+ * optimum and lp->v[qd] (if qd < m) the next coordinate of the residual's image (used for x_last). */
+static int lp_solve(LP *lp, double radius, double cmax, double *d_out) {
+    const int qd = lp->qd, m = lp->m;
+    lp_values(lp);
+    if (lp->val[0] < 0.0) lp_flip(lp);
+    const int cap = 100 * m + 1000;
+    int refactored = 0;
+    for (int iter = 0;; ++iter) {
+        const double t = lp->val[0];
+        if (!approximatelyLE(t, radius, DIST_EPS)) { if (iter == 0) lp->quick++; return NODE_PRUNE; }
+        int pe = -1; double vmax = -1.0;
+        for (int p = 1; p < qd; ++p) if (fabs(lp->val[p]) > vmax) { vmax = fabs(lp->val[p]); pe = p; }
+        const double tol = EPS_OPT * (cmax + t);
+        if (pe < 0 || vmax <= t + tol) {
+            /* optimal by the books: verify the vertex against the data before trusting it */
+            const int nv = qd < m ? qd + 1 : qd;
+            lp_image(lp, nv);
+            double err = 0.0;
+            for (int i = 0; i < qd; ++i) { const double e = fabs(lp->v[i] - lp->chat[i]); if (e > err) err = e; }
+            if (err <= 1.0e-8 * ((double)m * cmax + t)) { *d_out = t; return NODE_EXPLORE; }
+            if (refactored) return NODE_FAIL;
+            refactored = 1;
+            if (lp_refactor(lp)) return NODE_FAIL;
+            lp_values(lp);
+            if (lp->val[0] < 0.0) lp_flip(lp);
+            continue;
+        }
+        if (iter >= cap) return NODE_FAIL;
+        const int se = lp->val[pe] > 0.0 ? 1 : -1;
+        const double nrm1 = lp_alpha_beta(lp, pe);
+        if (fabs(nrm1 - 1.0) > 1.0e-6) { /* the dual vector has drifted */
+            if (refactored) return NODE_FAIL;
+            refactored = 1;
+            if (lp_refactor(lp)) return NODE_FAIL;
+            lp_values(lp);
+            if (lp->val[0] < 0.0) lp_flip(lp);
+            continue;
+        }
+        const int l = lp_ratio(lp, se, pe);
+        if (l < 0) return NODE_FAIL;
+        if (lp_replace(lp, pe, l, se)) return NODE_FAIL;
+        lp_values(lp);
+    }
 }
 
 /* ---- closest.cc:330-340 ---- */
@@ -353,27 +429,42 @@ int oracle_infdist(const double *B, int n, int m, const int64_t *u, int k, const
         c[i] = rhs1;
     }
     int rc = 0;
-    if (k == 0) {
-        double d = 0.0;
-        for (int j = 0; j < m; ++j) if (fabs(c[j]) > d) d = fabs(c[j]);
-        *dist = d;
-    } else {
-        LP *lp = lp_new(n, m, B);
-        const int st = lp_cold(lp, k + 1, c);
-        if (st < 0) rc = -1;
-        else if (st == 1) {
-            double d = 0.0;
-            for (int j = 0; j < m; ++j) { const double r = fabs(residual(lp, c, j)); if (r > d) d = r; }
-            *dist = d;
-            for (int i = 0; i < k; ++i) x[i] = lp->z[i + 1];
-        } else {
-            double d, xl;
-            if (lp_solve(lp, c, INFINITY, &d, &xl) != NODE_EXPLORE) rc = -1;
-            else { *dist = d; for (int i = 0; i < k; ++i) x[i] = lp->z[i + 1]; }
+    double cmax = 0.0;
+    for (int j = 0; j < m; ++j) if (fabs(c[j]) > cmax) cmax = fabs(c[j]);
+    if (k == 0) { *dist = cmax; free(c); return 0; }
+    Geo g;
+    if (geo_build(&g, B, p, n, m)) { free(c); geo_free(&g); return -1; }
+    LP *lp = lp_new(&g);
+    const int qd = m - k;
+    double d = 0.0;
+    for (int j = 0; j < m; ++j) lp->r[j] = 0.0;
+    if (qd > 0) {
+        for (int i = 0; i < qd; ++i) lp->chat[i] = dot4(g.Qrev + i, m, c, 1, m);
+        if (lp_init1(lp)) rc = -1;
+        for (int i = 1; i < qd && rc == 0; ++i) {
+            lp_extend(lp);
+            lp_values(lp);
+            if (lp_drop_artificial(lp, lp->val[i] > 0.0 ? 1 : -1)) rc = -1;
         }
-        lp_free(lp);
+        if (rc == 0 && lp_solve(lp, INFINITY, cmax, &d) != NODE_EXPLORE) rc = -1;
+        if (rc == 0) for (int j = 0; j < m; ++j) lp->r[j] = lp->pos[j] ? lp->val[lp->pos[j]] : (double)lp->sg[j] * lp->val[0];
     }
-    free(c);
+    if (rc == 0) { /* x = R_k^-1 Q_k^T (c - r) */
+        *dist = d;
+        double *y = (double *)calloc(k, sizeof(double));
+        for (int i = 0; i < k; ++i) {
+            double s = 0.0;
+            for (int j = 0; j < m; ++j) s = fma(g.Q[(size_t)i * m + j], c[j] - lp->r[j], s);
+            y[i] = s;
+        }
+        for (int i = k - 1; i >= 0; --i) {
+            double s = y[i];
+            for (int t = i + 1; t < k; ++t) s = fma(-g.Rm[(size_t)i * n + t], x[t], s);
+            x[i] = s / g.Rm[(size_t)i * n + i];
+        }
+        free(y);
+    }
+    lp_free(lp); geo_free(&g); free(c);
     return rc;
 }
 
@@ -383,21 +474,23 @@ int oracle_infdist(const double *B, int n, int m, const int64_t *u, int k, const
  * starts.  max_nodes = 0 means unlimited, otherwise stop with ORACLE_TRUNCATED after that many solves.
  *
  * Warm-start policy ("side chains"): at every level the siblings below the real centre xc and
- * the siblings above it form two chains.  The first node of a chain starts from the parent's optimal basis with the
- * level's coefficient fixed (lp_child); every later node of the chain starts from the final basis of the previous
- * node on the same side.  The basis a node starts from is therefore a function of its path alone. */
-typedef struct { double *H; int *row, *sg; int init; } Chain;
+ * the siblings above it form two chains.  The first node of a chain starts from the parent's optimal vertex extended
+ * by the level's coordinate; every later node of the chain starts from the final vertex of the previous node on the
+ * same side.  The vertex a node starts from is therefore a function of its path alone. */
+typedef struct { double *H; int *zrow; signed char *sg; int init; } Chain;
 
 static void chain_store(Chain *ch, const LP *lp) {
-    const int K = lp->K, ld = lp->ld;
-    memcpy(ch->H, lp->H, (size_t)K * ld * sizeof(double));
-    memcpy(ch->row, lp->row, K * sizeof(int)); memcpy(ch->sg, lp->sg, K * sizeof(int));
+    memcpy(ch->H, lp->H, (size_t)lp->qd * lp->ld * sizeof(double));
+    memcpy(ch->zrow, lp->zrow, lp->qd * sizeof(int));
+    memcpy(ch->sg, lp->sg, lp->m);
 }
-static void chain_load(LP *lp, const Chain *ch, int K) {
-    const int ld = lp->ld;
-    lp->K = K;
-    memcpy(lp->H, ch->H, (size_t)K * ld * sizeof(double));
-    memcpy(lp->row, ch->row, K * sizeof(int)); memcpy(lp->sg, ch->sg, K * sizeof(int));
+static void chain_load(LP *lp, const Chain *ch, int qd) {
+    lp->qd = qd;
+    memcpy(lp->H, ch->H, (size_t)qd * lp->ld * sizeof(double));
+    memcpy(lp->zrow, ch->zrow, qd * sizeof(int));
+    memcpy(lp->sg, ch->sg, lp->m);
+    for (int j = 0; j < lp->m; ++j) lp->pos[j] = 0;
+    for (int p = 1; p < qd; ++p) if (lp->zrow[p] >= 0) lp->pos[lp->zrow[p]] = p;
 }
 
 int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter_out,
@@ -409,40 +502,57 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
     for (int j = 0; j < m; ++j) p[j] = (double)(con[2 * j + 1] + con[2 * j]) / 2.0; /* closest.cc:180-185 */
     const double radius = (double)(con[1] - con[0]) / 2.0;                          /* closest.cc:193-194: row 0 only */
 
-    LP *lp = lp_new(n, m, B);
+    Geo g;
+    uint64_t counter = 0, nprune = 0, nodes = 0;
+    int rc = BLT_STATUS_OK;
+    if (hist) memset(hist, 0, (size_t)(n + 1) * sizeof(uint64_t));
+    if (geo_build(&g, B, p, n, m)) { geo_free(&g); free(B); free(p); return BLT_STATUS_LP_FAIL; }
+    LP *lp = lp_new(&g);
     const int ld = lp->ld;
     int64_t *u = (int64_t *)calloc(n, sizeof(int64_t)), *uhat = (int64_t *)calloc(n, sizeof(int64_t));
     int64_t *step = (int64_t *)calloc(n, sizeof(int64_t));
     unsigned char *pruned = (unsigned char *)calloc(n, 1);
     double *c = (double *)calloc(m, sizeof(double));
-    /* per level k (state k solves LP(k-1)): two chains, the parent's right-hand side, the real centre, the side of
-     * the node we descended through */
-    Chain (*ch)[2] = (Chain (*)[2])calloc(n + 2, sizeof(Chain[2]));
-    double **cparL = (double **)calloc(n + 2, sizeof(double *));
-    double *xc = (double *)calloc(n + 2, sizeof(double));
-    int *curside = (int *)calloc(n + 2, sizeof(int));
-    for (int k = 0; k <= n + 1; ++k) {
-        cparL[k] = (double *)calloc(m, sizeof(double));
+    /* per level k (state k solves LP(k-1), qd = m-k+1): two chains, the parent's right-hand side in both coordinate
+     * systems, the real centre, the base of this level's own coordinate, the side we descended through */
+    Chain (*ch)[2] = (Chain (*)[2])calloc(n + 3, sizeof(Chain[2]));
+    double **cparL = (double **)calloc(n + 3, sizeof(double *)), **chatL = (double **)calloc(n + 3, sizeof(double *));
+    double *xc = (double *)calloc(n + 3, sizeof(double)), *gbase = (double *)calloc(n + 3, sizeof(double));
+    int *curside = (int *)calloc(n + 3, sizeof(int));
+    for (int k = 0; k <= n + 2; ++k) {
+        cparL[k] = (double *)calloc(m, sizeof(double)); chatL[k] = (double *)calloc(ld, sizeof(double));
         for (int s = 0; s < 2; ++s) {
             ch[k][s].H = (double *)calloc((size_t)ld * ld, sizeof(double));
-            ch[k][s].row = (int *)calloc(ld, sizeof(int)); ch[k][s].sg = (int *)calloc(ld, sizeof(int));
+            ch[k][s].zrow = (int *)calloc(ld, sizeof(int)); ch[k][s].sg = (signed char *)calloc(m, 1);
         }
     }
-    uint64_t counter = 0, nprune = 0, nodes = 0;
-    int rc = BLT_STATUS_OK;
     int k = n;
     double xlast = 0.0, d = 0.0;
-    if (hist) memset(hist, 0, (size_t)(n + 1) * sizeof(uint64_t));
 
     /* initial solve LP(n): closest.cc:206; only x(n-1) is used */
     {
-        memcpy(c, p, (size_t)m * sizeof(double));
-        const int st = lp_cold(lp, n + 1, c);
+        double cmax = 0.0;
+        for (int j = 0; j < m; ++j) if (fabs(p[j]) > cmax) cmax = fabs(p[j]);
         if (hist) hist[n]++;
         nodes++;
-        if (st < 0) { rc = BLT_STATUS_LP_FAIL; goto done; }
-        if (st == 1) xlast = lp->z[n];
-        else if (lp_solve(lp, c, INFINITY, &d, &xlast) != NODE_EXPLORE) { rc = BLT_STATUS_LP_FAIL; goto done; }
+        const int qd = m - n;
+        double vq = 0.0;
+        if (qd > 0) {
+            for (int i = 0; i < qd; ++i) lp->chat[i] = g.QTp[m - 1 - i];
+            int bad = lp_init1(lp);
+            for (int i = 1; i < qd && !bad; ++i) {
+                lp_extend(lp);
+                lp_values(lp);
+                bad = lp_drop_artificial(lp, lp->val[i] > 0.0 ? 1 : -1);
+            }
+            if (bad || lp_solve(lp, INFINITY, cmax, &d) != NODE_EXPLORE) { rc = BLT_STATUS_LP_FAIL; goto done; }
+            vq = lp->v[qd];
+            chain_store(&ch[n + 1][0], lp);
+            memcpy(chatL[n], lp->chat, qd * sizeof(double));
+        }
+        curside[n + 1] = 0;
+        gbase[n] = g.QTp[n - 1];
+        xlast = (gbase[n] - vq) / g.Rm[(size_t)(n - 1) * n + (n - 1)];
     }
     u[n - 1] = (int64_t)round(xlast);          /* set_index, closest.cc:74-82 */
     step[n - 1] = sgn(xlast - (double)u[n - 1]);
@@ -452,33 +562,49 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
     for (;;) {
         if (max_nodes && nodes >= max_nodes) { rc = ORACLE_TRUNCATED; goto done; }
         /* right-hand side of this node: c = cpar - u[k-1] * B[k-1]  (D2) */
+        double cmax = 0.0;
         {
             const double mu = -(double)u[k - 1];
             const double *Bk = B + (size_t)(k - 1) * m, *cp = cparL[k];
-            for (int j = 0; j < m; ++j) c[j] = fma(mu, Bk[j], cp[j]);
+            for (int j = 0; j < m; ++j) { c[j] = fma(mu, Bk[j], cp[j]); if (fabs(c[j]) > cmax) cmax = fabs(c[j]); }
         }
         int status, side = 0;
         nodes++;
         if (hist) hist[k - 1]++;
         if (k == 1) { /* LP(0): plain max-abs */
-            d = 0.0;
-            for (int j = 0; j < m; ++j) if (fabs(c[j]) > d) d = fabs(c[j]);
+            d = cmax;
             status = approximatelyLE(d, radius, DIST_EPS) ? NODE_EXPLORE : NODE_PRUNE;
         } else {
+            const int kk = k - 1, qd = m - kk;
             const int dir = sgn(xc[k] - (double)u[k - 1]);
             side = dir > 0 ? 0 : 1;
+            const double clast = fma(-(double)u[k - 1], g.Rm[(size_t)kk * n + kk], gbase[k]);
             if (!ch[k][side].init) {
-                if (k == n) {
-                    if (lp_cold(lp, k, c) != 0) { rc = BLT_STATUS_LP_FAIL; goto done; }
+                if (qd == 1) {
+                    if (lp_init1(lp)) { rc = BLT_STATUS_LP_FAIL; goto done; }
+                    lp->chat[0] = clast;
                 } else {
-                    chain_load(lp, &ch[k + 1][curside[k + 1]], k + 1);
-                    if (lp_child(lp, dir)) { rc = BLT_STATUS_LP_FAIL; goto done; }
+                    chain_load(lp, &ch[k + 1][curside[k + 1]], qd - 1);
+                    lp_extend(lp);
+                    memcpy(lp->chat, chatL[k], (qd - 1) * sizeof(double));
+                    lp->chat[qd - 1] = clast;
+                    if (lp_drop_artificial(lp, dir)) { rc = BLT_STATUS_LP_FAIL; goto done; }
                 }
                 ch[k][side].init = 1;
-            } else chain_load(lp, &ch[k][side], k);
-            status = lp_solve(lp, c, radius, &d, &xlast);
+            } else {
+                chain_load(lp, &ch[k][side], qd);
+                memcpy(lp->chat, chatL[k], (qd - 1) * sizeof(double));
+                lp->chat[qd - 1] = clast;
+            }
+            status = lp_solve(lp, radius, cmax, &d);
             if (status == NODE_FAIL) { rc = BLT_STATUS_LP_FAIL; goto done; }
             chain_store(&ch[k][side], lp);
+            if (status == NODE_EXPLORE) { /* real centre of the next level: x_{kk-1} of the optimum */
+                double gn = g.QTp[kk - 1];
+                for (int i = kk; i < n; ++i) gn = fma(-(double)u[i], g.Rm[(size_t)(kk - 1) * n + i], gn);
+                gbase[k - 1] = gn;
+                xlast = (gn - lp->v[qd]) / g.Rm[(size_t)(kk - 1) * n + (kk - 1)];
+            }
         }
         if (status == NODE_PRUNE) {
             if (k < n) { /* ascend, closest.cc:110-122 */
@@ -496,6 +622,7 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
         if (k > 1) { /* descend, closest.cc:88-95 */
             curside[k] = side;
             memcpy(cparL[k - 1], c, (size_t)m * sizeof(double));
+            memcpy(chatL[k - 1], lp->chat, (size_t)(m - k + 1) * sizeof(double));
             xc[k - 1] = xlast;
             k--;
             u[k - 1] = (int64_t)round(xlast);
@@ -518,12 +645,12 @@ done:
     if (niter_out) *niter_out = counter;
     if (nprune_out) *nprune_out = nprune;
     if (stats) { stats[0] = lp->pivots; stats[1] = lp->refactors; stats[2] = lp->quick; stats[3] = lp->colds; }
-    for (int kk = 0; kk <= n + 1; ++kk) {
-        free(cparL[kk]);
-        for (int s = 0; s < 2; ++s) { free(ch[kk][s].H); free(ch[kk][s].row); free(ch[kk][s].sg); }
+    for (int kk = 0; kk <= n + 2; ++kk) {
+        free(cparL[kk]); free(chatL[kk]);
+        for (int s = 0; s < 2; ++s) { free(ch[kk][s].H); free(ch[kk][s].zrow); free(ch[kk][s].sg); }
     }
-    free(ch); free(cparL); free(xc); free(curside);
+    free(ch); free(cparL); free(chatL); free(xc); free(gbase); free(curside);
     free(u); free(uhat); free(step); free(pruned); free(c); free(B); free(p);
-    lp_free(lp);
+    lp_free(lp); geo_free(&g);
     return rc;
 }
