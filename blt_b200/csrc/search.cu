@@ -4,17 +4,19 @@
 // Execution model (DESIGN.md sections 3-5):
 //   * ONE persistent kernel per search, one CTA per SM, W warps per CTA.  A warp owns one depth-first search of
 //     one subtree at a time; its 32 lanes cooperate on that subtree's current node.
-//   * A node is a small dense LP  min_x |G x - c|_inf  (G = first kk basis vectors as columns, m rows).  It is
-//     solved by an exchange method on reference sets: K = kk+1 active rows with signs, the K x K inverse H of
-//     [sigma | G_S] in shared memory, dual feasibility kept as the invariant, so t = lambda . c_S is a valid lower
-//     bound at every step and a node is pruned as soon as the bound crosses the radius.
-//   * Warm starts ("side chains"): a node starts from the final basis of the previous sibling on the same side of
-//     the level's real centre, or, for the first node of a side, from its parent's optimal basis with the level's
-//     coefficient fixed.  Both live in a per-warp level store in global memory (L2 resident).
+//   * Geometry once per problem: B^T = Q R (Gram-Schmidt applied twice).  A node with kk free coefficients is the LP
+//         min |r|_inf   s.t.   N^T r = chat,      N = the last q = m - kk columns of Q,  chat = N^T c,
+//     i.e. a dual simplex whose basis is the set Z of the q-1 rows that are strictly inside the box, not the kk+1 rows
+//     on its boundary.  H = A^-1 (q x q) lives in shared memory while q <= 32 and in an L2-resident per-warp buffer
+//     above that.  Row 0 of H is the dual vector y; sg_j (n_j . y) >= 0 is the invariant, so t = y . chat is a valid
+//     lower bound at every step and a node is pruned as soon as the bound crosses the radius.
+//   * Going one level down adds one coordinate: H is bordered with an artificial column which is then pivoted out.
+//   * Warm starts ("side chains"): a node starts from the final vertex of the previous sibling on the same side of
+//     the level's real centre, or, for the first node of a side, from its parent's optimal vertex extended by the
+//     level's coordinate.  Chain heads live in a per-warp level store in global memory (L2 resident).
 //   * Load balance: a global MPMC queue of subtree records.  A warp that explores a child while other warps are
-//     idle writes the child as a record (its optimal basis, right-hand side, path) instead of descending.  Every
-//     node is still solved exactly once, from the same starting basis as in the sequential order, so niter and
-//     nprune do not depend on scheduling.
+//     idle writes the child as a record instead of descending.  Every node is still solved exactly once, from the
+//     same starting vertex as in the sequential order, so niter and nprune do not depend on scheduling.
 //
 // Floating point: every operation below has a twin in oracle/blt_oracle.c with the same operand order; compile
 // with -fmad=false so that only the explicit fma() calls fuse.  FP64 FMA pipe is the roofline (no tensor cores:
@@ -26,10 +28,10 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <chrono>
 #include <mutex>
 #include <vector>
-#include <algorithm>
 
 #include "../../include/bltcu.h"
 
@@ -37,7 +39,9 @@
 #define DIST_EPS 1.0e-4  // libblt/glpk_wrapper.h:13
 #define EPS_OPT 1.0e-9
 #define PIV_TOL 1.0e-11
+#define HARRIS_DELTA 1.0e-10
 #define MAXD BLTCU_MAX_DIM
+#define QS_MAX 32  // largest basis kept in shared memory
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
 enum { REC_ROOT = 1 };
@@ -62,9 +66,12 @@ struct QCtl {
 };
 
 struct Params {
-    int n, m, LD, LDB, KMAX;
+    int n, m, LDQ, QS, LDS, LDG;
     const double *B;        // n x m (double)lat
     const double *p;        // m centre
+    const double *Qrev;     // m x m: Qrev[j*m+i] = q_{m-1-i}[j]
+    const double *Rm;       // n x n upper triangular, Rm[j*n+i] = q_j . b_i
+    const double *QTp;      // m
     double radius;
     const int64_t *lat;     // n x m
     const int64_t *con;     // m x 2
@@ -75,10 +82,14 @@ struct Params {
     unsigned char *pool;    // subtree records
     size_t rec_stride;
     int pool_cap;
-    double *scrD;           // per-warp level store (doubles)
+    double *scrD;           // per-warp level store (doubles): chain matrices, parent right-hand sides
     size_t scrD_stride;
-    int *scrI;              // per-warp level store (ints)
+    int *scrI;              // per-warp level store (ints): basic rows of the chain heads
     size_t scrI_stride;
+    signed char *scrB;      // per-warp level store (bytes): signs of the chain heads
+    size_t scrB_stride;
+    double *bigW;           // per-warp H for q > QS (m x LDG) followed by the refactorisation scratch (m x m)
+    size_t bigW_stride;
     int64_t *sol;           // n, written by the finder
     int64_t *best_u;        // per warp: n (last recorded candidate)
     unsigned char *best_key;// per warp: n
@@ -95,40 +106,48 @@ struct Params {
 
 // record field offsets (bytes), computed identically on host and device
 struct RecLayout {
-    size_t off_u, off_ord, off_cpar, off_row, off_sg, off_H, stride;
+    size_t off_u, off_ord, off_cpar, off_chat, off_sg, off_zrow, off_H, stride;
 };
+__host__ __device__ inline size_t al8(size_t x) { return (x + 7) / 8 * 8; }
 __host__ __device__ inline RecLayout rec_layout(int n, int m) {
     RecLayout L;
-    size_t o = 32;  // header: int k, int flags, double xc, pad
+    size_t o = 32;  // header: int k, int flags, double xc, double gbase, pad
     L.off_u = o; o += (size_t)8 * n;
-    L.off_ord = o; o += ((size_t)n + 7) / 8 * 8;
+    L.off_ord = o; o += al8((size_t)n);
     L.off_cpar = o; o += (size_t)8 * m;
-    L.off_row = o; o += ((size_t)4 * (n + 1) + 7) / 8 * 8;
-    L.off_sg = o; o += ((size_t)4 * (n + 1) + 7) / 8 * 8;
-    L.off_H = o; o += (size_t)8 * (n + 1) * (n + 1);
+    L.off_chat = o; o += (size_t)8 * (m + 1);
+    L.off_sg = o; o += al8((size_t)m);
+    L.off_zrow = o; o += al8((size_t)4 * (m + 1));
+    L.off_H = o; o += (size_t)8 * m * m;
     L.stride = (o + 255) / 256 * 256;
     return L;
 }
-// level store: chains for k = 2..n (K = k), two sides; packed
-__host__ __device__ inline size_t chain_off(int k) {  // doubles before level k: 2 * sum_{j=2}^{k-1} j^2
-    const size_t kk = (size_t)k;
-    return 2 * ((kk - 1) * kk * (2 * kk - 1) / 6 - 1);
+// level store, indexed by the basis size q = 1..m of the level; two chains per q
+__host__ __device__ inline size_t chain_off(int q) {  // doubles before q: 2 * sum_{j<q} j^2
+    const size_t x = (size_t)q;
+    return 2 * ((x - 1) * x * (2 * x - 1) / 6);
 }
-__host__ __device__ inline size_t chain_ioff(int k) {  // ints before level k: 2 sides * (row,sg) * sum j
-    const size_t kk = (size_t)k;
-    return 4 * ((kk - 1) * kk / 2 - 1);
+__host__ __device__ inline size_t chain_ioff(int q) {  // ints before q: 2 * sum_{j<q} j
+    const size_t x = (size_t)q;
+    return (x - 1) * x;
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// Per-warp state (pointers into shared memory) and primitives
+// Per-warp state and primitives
 // ------------------------------------------------------------------------------------------------------------
 struct WS {
-    double *W, *z, *g, *w, *a, *cS, *c, *cpar, *xc;
-    int *row, *sg, *tmpi, *tmps, *step;
+    double *W;  // current home of H (shared memory while qd <= QS, else the per-warp global buffer)
+    int LD;
+    double *Ws, *Wg, *tmpA;
+    int LDS, LDG, QS;
+    double *chat, *val, *w, *a, *v, *r, *c, *cpar, *chatpar, *xc, *gbase;
+    int *zrow, *step;
     long long *u;
-    unsigned char *ord, *flags;  // flags[k]: bit0/1 = chain initialised side 0/1, bit2 = pruned, bit3 = curside
-    const double *Bs;
-    int LD, LDB, n, m, K, lane;
+    unsigned char *pos, *ord, *flags;  // flags[k]: bit0/1 = chain initialised side 0/1, bit2 = pruned, bit3 = curside
+    signed char *sg;
+    const double *Qs;  // Qrev in shared memory, leading dimension LDQ
+    int LDQ, n, m, qd, lane;
+    double al[3], be[3];  // alpha/beta of rows lane, lane+32, lane+64
     unsigned long long pivots, quick, refactors, colds;
 };
 
@@ -153,304 +172,375 @@ __device__ __forceinline__ double dot4(int len, FA fa, FB fb) {
     if (e < len) { a2 = fma(fa(e), fb(e), a2); }
     return (a0 + a1) + (a2 + a3);
 }
+// two dot4 products against the same left operand (one load of it, two fma streams); same bits as two dot4 calls
+template <class FA, class FB, class FC>
+__device__ __forceinline__ void dot4x2(int len, FA fa, FB fb, FC fc, double &r1, double &r2) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+    int e = 0;
+    for (; e + 3 < len; e += 4) {
+        const double x0 = fa(e), x1 = fa(e + 1), x2 = fa(e + 2), x3 = fa(e + 3);
+        a0 = fma(x0, fb(e), a0); b0 = fma(x0, fc(e), b0);
+        a1 = fma(x1, fb(e + 1), a1); b1 = fma(x1, fc(e + 1), b1);
+        a2 = fma(x2, fb(e + 2), a2); b2 = fma(x2, fc(e + 2), b2);
+        a3 = fma(x3, fb(e + 3), a3); b3 = fma(x3, fc(e + 3), b3);
+    }
+    if (e < len) { const double x = fa(e); a0 = fma(x, fb(e), a0); b0 = fma(x, fc(e), b0); ++e; }
+    if (e < len) { const double x = fa(e); a1 = fma(x, fb(e), a1); b1 = fma(x, fc(e), b1); ++e; }
+    if (e < len) { const double x = fa(e); a2 = fma(x, fb(e), a2); b2 = fma(x, fc(e), b2); }
+    r1 = (a0 + a1) + (a2 + a3);
+    r2 = (b0 + b1) + (b2 + b3);
+}
 
 __device__ __forceinline__ double warp_max(double v) {
     for (int off = 16; off >= 1; off >>= 1) { const double o = __shfl_xor_sync(FULLMASK, v, off); v = o > v ? o : v; }
     return v;
 }
-// (largest value, smallest index); idx < 0 never wins
-__device__ __forceinline__ void warp_argmax(double &v, int &idx, double &aux) {
-    for (int off = 16; off >= 1; off >>= 1) {
-        const double ov = __shfl_xor_sync(FULLMASK, v, off);
-        const int oi = __shfl_xor_sync(FULLMASK, idx, off);
-        const double oa = __shfl_xor_sync(FULLMASK, aux, off);
-        const bool take = (oi >= 0) && (idx < 0 || ov > v || (ov == v && oi < idx));
-        if (take) { v = ov; idx = oi; aux = oa; }
-    }
+__device__ __forceinline__ double warp_min(double v) {
+    for (int off = 16; off >= 1; off >>= 1) { const double o = __shfl_xor_sync(FULLMASK, v, off); v = o < v ? o : v; }
+    return v;
 }
-// (smallest value, smallest index); idx < 0 never wins
-__device__ __forceinline__ void warp_argmin(double &v, int &idx) {
+__device__ __forceinline__ double butterfly(double v) {  // the oracle's butterfly32
+    for (int off = 16; off >= 1; off >>= 1) v = v + __shfl_xor_sync(FULLMASK, v, off);
+    return v;
+}
+// (largest value, smallest index); idx < 0 never wins
+__device__ __forceinline__ void warp_argmax(double &v, int &idx) {
     for (int off = 16; off >= 1; off >>= 1) {
         const double ov = __shfl_xor_sync(FULLMASK, v, off);
         const int oi = __shfl_xor_sync(FULLMASK, idx, off);
-        const bool take = (oi >= 0) && (idx < 0 || ov < v || (ov == v && oi < idx));
+        const bool take = (oi >= 0) && (idx < 0 || ov > v || (ov == v && oi < idx));
         if (take) { v = ov; idx = oi; }
     }
 }
 
-__device__ __forceinline__ void lp_gather(WS &s) {
-    for (int e = s.lane; e < s.K; e += 32) s.cS[e] = s.row[e] >= 0 ? s.c[s.row[e]] : 0.0;
-    __syncwarp();
-}
-__device__ __forceinline__ double lp_treedot(WS &s) {  // lambda . cS with the oracle's treedot order
+// ---- geometry: B^T = Q R by Gram-Schmidt applied twice, one warp (twin of geo_build in the oracle) ------------
+__device__ __forceinline__ double treedot_g(const double *a, const double *b, int len, int lane) {
     double acc = 0.0;
-    for (int e = s.lane; e < s.K; e += 32) acc = fma(s.W[e], s.cS[e], acc);
-    for (int off = 16; off >= 1; off >>= 1) acc = acc + __shfl_xor_sync(FULLMASK, acc, off);
-    return acc;
+    for (int e = lane; e < len; e += 32) acc = fma(a[e], b[e], acc);
+    return butterfly(acc);
 }
-__device__ __forceinline__ void lp_point(WS &s) {
-    const int K = s.K;
-    for (int v = s.lane; v < K; v += 32) {
-        const double *Hv = s.W + (size_t)v * s.LD;
-        const double *cS = s.cS;
-        s.z[v] = dot4(K, [&](int e) { return Hv[e]; }, [&](int e) { return cS[e]; });
-    }
+__device__ int geo_build_warp(const double *B, const double *p, int n, int m, double *Q, double *Qrev, double *Rm,
+                              double *QTp, double *v, double *coef, int lane) {
+    for (int e = lane; e < n * n; e += 32) Rm[e] = 0.0;
     __syncwarp();
-}
-__device__ __forceinline__ void lp_row(WS &s, int q, int sq) {
-    if (s.lane == 0) s.a[0] = (double)sq;
-    for (int i = s.lane; i + 1 < s.K; i += 32) s.a[i + 1] = s.Bs[(size_t)i * s.LDB + q];
-    __syncwarp();
-}
-__device__ __forceinline__ void lp_w(WS &s) {
-    const int K = s.K, LD = s.LD;
-    for (int c = s.lane; c < K; c += 32) {
-        const double *a = s.a;
-        const double *Hc = s.W + c;
-        s.w[c] = dot4(K, [&](int e) { return a[e]; }, [&](int e) { return Hc[(size_t)e * LD]; });
-    }
-    __syncwarp();
-}
-// H <- H - g (w - e_l)^T with g = H[:,l] / w_l, for rows v < nrows
-__device__ __forceinline__ void lp_update(WS &s, int l, int nrows, bool set_col) {
-    const int K = s.K, LD = s.LD;
-    const double wl = s.w[l];
-    for (int v = s.lane; v < nrows; v += 32) s.g[v] = s.W[(size_t)v * LD + l] / wl;
-    __syncwarp();
-    for (int c = s.lane; c < K; c += 32) {
-        const double wc = s.w[c];
-        double *Hc = s.W + c;
-        if (c == l) {
-            if (set_col) for (int v = 0; v < nrows; ++v) Hc[(size_t)v * LD] = s.g[v];
-        } else {
-#pragma unroll 4
-            for (int v = 0; v < nrows; ++v) Hc[(size_t)v * LD] = fma(-s.g[v], wc, Hc[(size_t)v * LD]);
+    for (int t = 0; t < m; ++t) {
+        if (t < n) { for (int e = lane; e < m; e += 32) v[e] = B[(size_t)t * m + e]; }
+        else {  // completion: the unit vector with the largest part outside the current span (ties: lowest j)
+            int best = -1; double bv = -1.0;
+            for (int j = lane; j < m; j += 32) {
+                double sres = 1.0;
+                for (int i = 0; i < t; ++i) { const double x = Q[(size_t)i * m + j]; sres = fma(-x, x, sres); }
+                if (sres > bv) { bv = sres; best = j; }
+            }
+            warp_argmax(bv, best);
+            for (int e = lane; e < m; e += 32) v[e] = (e == best) ? 1.0 : 0.0;
         }
+        for (int e = lane; e < m; e += 32) coef[e] = 0.0;
+        __syncwarp();
+        for (int pass = 0; pass < 2; ++pass)
+            for (int j = 0; j < t; ++j) {
+                const double *qj = Q + (size_t)j * m;
+                const double h = treedot_g(qj, v, m, lane);
+                for (int e = lane; e < m; e += 32) v[e] = fma(-h, qj[e], v[e]);
+                if (lane == 0) coef[j] += h;
+                __syncwarp();
+            }
+        const double nrm = sqrt(treedot_g(v, v, m, lane));
+        if (!(nrm > 0.0)) return -1;
+        for (int e = lane; e < m; e += 32) Q[(size_t)t * m + e] = v[e] / nrm;
+        if (t < n) {
+            for (int j = lane; j < t; j += 32) Rm[(size_t)j * n + t] = coef[j];
+            if (lane == 0) Rm[(size_t)t * n + t] = nrm;
+        }
+        __syncwarp();
+    }
+    for (int e = lane; e < m * m; e += 32) { const int j = e / m, i = e - j * m; Qrev[e] = Q[(size_t)(m - 1 - i) * m + j]; }
+    for (int t = 0; t < m; ++t) { const double x = treedot_g(Q + (size_t)t * m, p, m, lane); if (lane == 0) QTp[t] = x; }
+    __syncwarp();
+    return 0;
+}
+
+// ---- LP engine (twin of the oracle's lp_* functions) -----------------------------------------------------------
+__device__ __forceinline__ void lp_home(WS &s, int q) {  // where an H of size q lives
+    if (q <= s.QS) { s.W = s.Ws; s.LD = s.LDS; } else { s.W = s.Wg; s.LD = s.LDG; }
+}
+__device__ __forceinline__ void lp_values(WS &s) {
+    const int qd = s.qd;
+    for (int p = s.lane; p < qd; p += 32) {
+        const double *Hp = s.W + (size_t)p * s.LD, *ch = s.chat;
+        s.val[p] = dot4(qd, [&](int e) { return Hp[e]; }, [&](int e) { return ch[e]; });
+    }
+    __syncwarp();
+}
+__device__ __forceinline__ void lp_flip(WS &s) {
+    for (int c = s.lane; c < s.qd; c += 32) s.W[c] = -s.W[c];
+    for (int j = s.lane; j < s.m; j += 32) s.sg[j] = (signed char)-s.sg[j];
+    if (s.lane == 0) s.val[0] = -s.val[0];
+    __syncwarp();
+}
+__device__ __forceinline__ double lp_alpha_beta(WS &s, int pe) {
+    const int qd = s.qd, m = s.m;
+    const double *y = s.W, *rho = s.W + (size_t)pe * s.LD;
+    double part = 0.0;
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+        const int j = s.lane + 32 * t;
+        s.al[t] = 0.0; s.be[t] = 0.0;
+        if (j < m && !s.pos[j]) {
+            const double *nj = s.Qs + (size_t)j * s.LDQ;
+            dot4x2(qd, [&](int e) { return nj[e]; }, [&](int e) { return y[e]; }, [&](int e) { return rho[e]; }, s.al[t], s.be[t]);
+            part += fabs(s.al[t]);
+        }
+    }
+    return butterfly(part);
+}
+__device__ int lp_ratio(WS &s, int se, int pe) {
+    const int m = s.m, qd = s.qd;
+    const bool artificial = s.zrow[pe] < 0;
+    double scale = 0.0;
+    for (int c = s.lane; c < qd; c += 32) { const double a = fabs(s.W[(size_t)pe * s.LD + c]); scale = a > scale ? a : scale; }
+#pragma unroll
+    for (int t = 0; t < 3; ++t) { const int j = s.lane + 32 * t; if (j < m && !s.pos[j]) { const double a = fabs(s.be[t]); scale = a > scale ? a : scale; } }
+    scale = warp_max(scale);
+    const double tiny = PIV_TOL * scale, dmin = artificial ? tiny : 0.0;
+    double tmax = INFINITY;
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+        const int j = s.lane + 32 * t;
+        if (j >= m || s.pos[j]) continue;
+        const double den = -(double)(se * s.sg[j]) * s.be[t];
+        if (!(den > dmin)) continue;
+        double num = (double)s.sg[j] * s.al[t];
+        if (num < 0.0) num = 0.0;
+        const double rt = (num + HARRIS_DELTA) / den;
+        if (rt < tmax) tmax = rt;
+    }
+    tmax = warp_min(tmax);
+    int best = -1; double bd = 0.0;
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+        const int j = s.lane + 32 * t;
+        if (j >= m || s.pos[j]) continue;
+        const double den = -(double)(se * s.sg[j]) * s.be[t];
+        if (!(den > dmin)) continue;
+        double num = (double)s.sg[j] * s.al[t];
+        if (num < 0.0) num = 0.0;
+        if (num / den <= tmax && den > bd) { bd = den; best = j; }
+    }
+    warp_argmax(bd, best);
+    if (best >= 0 || artificial) return best;
+    double ba = -1.0;
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+        const int j = s.lane + 32 * t;
+        if (j >= m || s.pos[j] || fabs(s.be[t]) > tiny) continue;
+        if (fabs(s.al[t]) > ba) { ba = fabs(s.al[t]); best = j; }
+    }
+    warp_argmax(ba, best);
+    return best;
+}
+__device__ int lp_replace(WS &s, int pe, int l, int se) {
+    const int qd = s.qd, LD = s.LD;
+    double *H = s.W, *Hp = s.W + (size_t)pe * LD;
+    const int e = s.zrow[pe];
+    if (e >= 0) { for (int c = s.lane; c < qd; c += 32) Hp[c] = Hp[c] - (double)se * H[c]; }
+    __syncwarp();
+    const double *nl = s.Qs + (size_t)l * s.LDQ;
+    for (int i = s.lane; i < qd; i += 32) {
+        const double *Hi = H + (size_t)i * LD;
+        s.w[i] = dot4(qd, [&](int c) { return Hi[c]; }, [&](int c) { return nl[c]; });
+    }
+    __syncwarp();
+    const double wp = s.w[pe];
+    if (wp == 0.0) return -1;
+    for (int c = s.lane; c < qd; c += 32) s.v[c] = Hp[c] / wp;
+    __syncwarp();
+    for (int x = s.lane; x < qd * qd; x += 32) {
+        const int i = x / qd, c = x - i * qd;
+        if (i != pe) H[(size_t)i * LD + c] = fma(-s.w[i], s.v[c], H[(size_t)i * LD + c]);
+    }
+    __syncwarp();
+    const double sl = (double)s.sg[l];
+    for (int c = s.lane; c < qd; c += 32) Hp[c] = s.v[c] + sl * H[c];
+    __syncwarp();
+    if (s.lane == 0) {
+        if (e >= 0) { s.sg[e] = (signed char)se; s.pos[e] = 0; }
+        s.zrow[pe] = l; s.pos[l] = (unsigned char)pe;
     }
     __syncwarp();
     s.pivots++;
+    return 0;
 }
-__device__ __forceinline__ void lp_pivot(WS &s, int l) { lp_update(s, l, s.K, true); }
-
-__device__ __forceinline__ int lp_ratio(WS &s, int sq) {
-    const int K = s.K;
-    double wm = 0.0;
-    for (int e = s.lane; e < K; e += 32) { const double a = fabs(s.w[e]); wm = a > wm ? a : wm; }
-    wm = warp_max(wm);
-    const double thr = PIV_TOL * wm;
-    int best = -1;
-    double br = 0.0;
-    for (int e = s.lane; e < K; e += 32) {
-        const double den = (double)(sq * s.sg[e]) * s.w[e];
-        if (!(den > thr)) continue;
-        double num = (double)s.sg[e] * s.W[e];
-        if (num < 0.0) num = 0.0;
-        const double r = num / den;
-        if (best < 0 || r < br) { best = e; br = r; }
+__device__ int lp_init1(WS &s) {
+    const int m = s.m;
+    lp_home(s, 1);
+    double part = 0.0;
+    for (int j = s.lane; j < m; j += 32) {
+        const double x = s.Qs[(size_t)j * s.LDQ];
+        s.sg[j] = x >= 0.0 ? 1 : -1; s.pos[j] = 0;
+        part += fabs(x);
     }
-    warp_argmin(br, best);
-    return best;
+    const double sum = butterfly(part);
+    if (!(sum > 0.0)) return -1;
+    if (s.lane == 0) { s.W[0] = 1.0 / sum; s.zrow[0] = -1; }
+    s.qd = 1; s.colds++;
+    __syncwarp();
+    return 0;
 }
-
-__device__ __forceinline__ void lp_identity(WS &s, int K) {
-    const int LD = s.LD;
-    for (int e = s.lane; e < K * K; e += 32) { const int v = e / K, c = e - v * K; s.W[(size_t)v * LD + c] = (v == c) ? 1.0 : 0.0; }
+// moves H to the home of a basis of size q_home if it is not there already
+__device__ __forceinline__ void lp_rehome(WS &s, int q_home) {
+    double *oldW = s.W; const int oldLD = s.LD, q = s.qd;
+    lp_home(s, q_home);
+    if (s.W == oldW) return;
+    for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * s.LD + c] = oldW[(size_t)i * oldLD + c]; }
     __syncwarp();
 }
-
+// one more coordinate (index qd): border H with an artificial basic column at position qd
+__device__ void lp_extend(WS &s) {
+    lp_rehome(s, s.qd + 1);
+    const int m = s.m, qd = s.qd, LD = s.LD;
+    double part = 0.0;
+    for (int j = s.lane; j < m; j += 32) if (!s.pos[j]) part = fma((double)s.sg[j], s.Qs[(size_t)j * s.LDQ + qd], part);
+    const double a0 = butterfly(part);
+    if (s.lane == 0) s.a[0] = a0;
+    for (int p = 1 + s.lane; p < qd; p += 32) s.a[p] = s.Qs[(size_t)s.zrow[p] * s.LDQ + qd];
+    __syncwarp();
+    for (int c = s.lane; c < qd; c += 32) {
+        const double *a = s.a, *Hc = s.W + c;
+        s.W[(size_t)qd * LD + c] = -dot4(qd, [&](int e) { return a[e]; }, [&](int e) { return Hc[(size_t)e * LD]; });
+    }
+    for (int p = s.lane; p < qd; p += 32) s.W[(size_t)p * LD + qd] = 0.0;
+    if (s.lane == 0) { s.W[(size_t)qd * LD + qd] = 1.0; s.zrow[qd] = -1; }
+    s.qd = qd + 1;
+    __syncwarp();
+}
+__device__ int lp_drop_artificial(WS &s, int sf) {
+    const int pe = s.qd - 1;
+    lp_alpha_beta(s, pe);
+    const int l = lp_ratio(s, sf, pe);
+    if (l < 0) return -1;
+    return lp_replace(s, pe, l, sf);
+}
+// rare path: rebuild H = A^-1 from Z and the signs by Gauss-Jordan with row pivoting, one lane, the oracle's loops
 __device__ int lp_refactor(WS &s) {
-    const int K = s.K;
-    for (int e = s.lane; e < K; e += 32) { s.tmpi[e] = s.row[e]; s.tmps[e] = s.sg[e]; s.row[e] = -1; s.sg[e] = 1; }
+    const int qd = s.qd, LD = s.LD, m = s.m;
+    int rc = 0;
     __syncwarp();
-    lp_identity(s, K);
-    for (int i = 0; i < K; ++i) {
-        lp_row(s, s.tmpi[i], s.tmps[i]);
-        lp_w(s);
-        int l = -1; double bw = 0.0, aux = 0.0;
-        for (int e = s.lane; e < K; e += 32) if (s.row[e] < 0 && fabs(s.w[e]) > bw) { bw = fabs(s.w[e]); l = e; }
-        warp_argmax(bw, l, aux);
-        if (l < 0) return -1;
-        lp_pivot(s, l);
-        if (s.lane == 0) { s.row[l] = s.tmpi[i]; s.sg[l] = s.tmps[i]; }
-        __syncwarp();
+    if (s.lane == 0) {
+        double *A = s.tmpA, *H = s.W;
+        for (int c = 0; c < qd; ++c) {
+            double sum = 0.0;
+            for (int j = 0; j < m; ++j) if (!s.pos[j]) sum = fma((double)s.sg[j], s.Qs[(size_t)j * s.LDQ + c], sum);
+            A[(size_t)c * qd] = sum;
+            for (int p = 1; p < qd; ++p) A[(size_t)c * qd + p] = s.zrow[p] >= 0 ? s.Qs[(size_t)s.zrow[p] * s.LDQ + c] : (c == p ? 1.0 : 0.0);
+        }
+        for (int i = 0; i < qd; ++i) for (int c = 0; c < qd; ++c) H[(size_t)i * LD + c] = (i == c) ? 1.0 : 0.0;
+        for (int col = 0; col < qd; ++col) {
+            int pr = -1; double bv = 0.0;
+            for (int i = col; i < qd; ++i) if (fabs(A[(size_t)i * qd + col]) > bv) { bv = fabs(A[(size_t)i * qd + col]); pr = i; }
+            if (pr < 0) { rc = -1; break; }
+            if (pr != col) {
+                for (int c = 0; c < qd; ++c) {
+                    double t = A[(size_t)pr * qd + c]; A[(size_t)pr * qd + c] = A[(size_t)col * qd + c]; A[(size_t)col * qd + c] = t;
+                    t = H[(size_t)pr * LD + c]; H[(size_t)pr * LD + c] = H[(size_t)col * LD + c]; H[(size_t)col * LD + c] = t;
+                }
+            }
+            const double pv = A[(size_t)col * qd + col];
+            for (int c = 0; c < qd; ++c) { A[(size_t)col * qd + c] /= pv; H[(size_t)col * LD + c] /= pv; }
+            for (int i = 0; i < qd; ++i) {
+                if (i == col) continue;
+                const double f = A[(size_t)i * qd + col];
+                if (f == 0.0) continue;
+                for (int c = 0; c < qd; ++c) {
+                    A[(size_t)i * qd + c] = fma(-f, A[(size_t)col * qd + c], A[(size_t)i * qd + c]);
+                    H[(size_t)i * LD + c] = fma(-f, H[(size_t)col * LD + c], H[(size_t)i * LD + c]);
+                }
+            }
+        }
     }
+    rc = __shfl_sync(FULLMASK, rc, 0);
+    __syncwarp();
     s.refactors++;
-    return 0;
+    return rc;
 }
-
-__device__ __forceinline__ double residual(const WS &s, int j) {
-    const double *Bj = s.Bs + j;
-    const double *z1 = s.z + 1;
-    const int LDB = s.LDB;
-    return s.c[j] - dot4(s.K - 1, [&](int e) { return Bj[(size_t)e * LDB]; }, [&](int e) { return z1[e]; });
-}
-
-// cold start for LP(K-1); returns 0 ok, 1 square system (stage A only), -1 failure.  `used` aliases tmpi.
-__device__ int lp_cold(WS &s, int K) {
-    const int LD = s.LD, m = s.m, kk = K - 1, LDB = s.LDB;
-    s.K = K; s.colds++;
-    for (int e = s.lane; e < K; e += 32) { s.row[e] = -1; s.sg[e] = 1; }
-    unsigned long long used0 = 0, used1 = 0;  // bitmask over m <= 128 rows, replicated in every lane
-    lp_identity(s, K);
-    for (int v = 1; v <= kk; ++v) {
-        int q = -1; double bp = 0.0, aux = 0.0;
-        const double *Hv = s.W + v;
-        for (int j = s.lane; j < m; j += 32) {
-            const bool u = j < 64 ? ((used0 >> j) & 1ull) : ((used1 >> (j - 64)) & 1ull);
-            if (u) continue;
-            const double *Bj = s.Bs + j;
-            const double pv = fabs(dot4(K, [&](int e) { return e == 0 ? 1.0 : Bj[(size_t)(e - 1) * LDB]; },
-                                        [&](int e) { return Hv[(size_t)e * LD]; }));
-            if (pv > bp) { bp = pv; q = j; }
-        }
-        warp_argmax(bp, q, aux);
-        if (q < 0) return -1;
-        lp_row(s, q, 1); lp_w(s); lp_pivot(s, v);
-        if (s.lane == 0) { s.row[v] = q; s.sg[v] = 1; }
-        if (q < 64) used0 |= 1ull << q; else used1 |= 1ull << (q - 64);
-        __syncwarp();
+__device__ __forceinline__ void lp_image(WS &s, int nv) {
+    const int m = s.m;
+    const double t = s.val[0];
+    for (int j = s.lane; j < m; j += 32) s.r[j] = s.pos[j] ? s.val[s.pos[j]] : (double)s.sg[j] * t;
+    __syncwarp();
+    for (int i = s.lane; i < nv; i += 32) {
+        const double *Qi = s.Qs + i, *r = s.r;
+        const int LDQ = s.LDQ;
+        s.v[i] = dot4(m, [&](int e) { return Qi[(size_t)e * LDQ]; }, [&](int e) { return r[e]; });
     }
-    lp_gather(s); lp_point(s);
-    if (kk >= m) return 1;
-    {
-        int q = -1; double br = -1.0, aux = 0.0;
-        for (int j = s.lane; j < m; j += 32) {
-            const bool u = j < 64 ? ((used0 >> j) & 1ull) : ((used1 >> (j - 64)) & 1ull);
-            if (u) continue;
-            const double r = fabs(residual(s, j));
-            if (r > br) { br = r; q = j; }
-        }
-        warp_argmax(br, q, aux);
-        if (q < 0) return -1;
-        const double *Bq = s.Bs + q;
-        const double *H0 = s.W + LD;
-        const double rho = dot4(kk, [&](int e) { return Bq[(size_t)e * LDB]; }, [&](int e) { return H0[(size_t)e * LD]; });
-        const int sq = (rho >= 0.0) ? 1 : -1;
-        lp_row(s, q, sq); lp_w(s);
-        if (s.w[0] == 0.0) return -1;
-        lp_pivot(s, 0);
-        if (s.lane == 0) { s.row[0] = q; s.sg[0] = sq; }
-        __syncwarp();
-    }
-    {   // sign fix (Sherman-Morrison on the sigma column); lam -> a, Delta -> w, sigma' -> cS
-        bool any = false;
-        for (int e = s.lane; e < K; e += 32) {
-            const double l = s.W[e];
-            s.a[e] = l;
-            const int ns = l > 0.0 ? 1 : (l < 0.0 ? -1 : s.sg[e]);
-            s.w[e] = (double)(ns - s.sg[e]);
-            s.cS[e] = (double)ns;
-            s.tmps[e] = ns;
-            if (ns != s.sg[e]) any = true;
-        }
-        __syncwarp();
-        if (__any_sync(FULLMASK, any)) {
-            const double *lam = s.a, *sp = s.cS, *dl = s.w;
-            const double D = dot4(K, [&](int e) { return lam[e]; }, [&](int e) { return sp[e]; });
-            if (!(D > 0.0)) return -1;
-            for (int v = s.lane; v < K; v += 32) {
-                const double *Hv = s.W + (size_t)v * LD;
-                s.g[v] = dot4(K, [&](int e) { return Hv[e]; }, [&](int e) { return dl[e]; }) / D;
-            }
-            __syncwarp();
-            for (int c = s.lane; c < K; c += 32) {
-                const double lc = lam[c];
-                double *Hc = s.W + c;
-                for (int v = 0; v < K; ++v) Hc[(size_t)v * LD] = fma(-s.g[v], lc, Hc[(size_t)v * LD]);
-            }
-            for (int e = s.lane; e < K; e += 32) s.sg[e] = s.tmps[e];
-            __syncwarp();
-        }
-    }
-    return 0;
-}
-
-__device__ __forceinline__ void lp_flip(WS &s) {
-    for (int e = s.lane; e < s.K; e += 32) { s.W[e] = -s.W[e]; s.sg[e] = -s.sg[e]; }
-    if (s.lane == 0) s.z[0] = -s.z[0];
     __syncwarp();
 }
-
-// node solve from the current dual-feasible basis; radius = +inf disables pruning
-__device__ int lp_solve(WS &s, double radius, double &d_out, double &xlast_out) {
-    const int K = s.K, m = s.m;
-    lp_gather(s);
-    {
-        double tq = lp_treedot(s);
-        if (tq < 0.0) tq = -tq;
-        if (!approxLE(tq, radius)) { s.quick++; return NODE_PRUNE; }
-    }
-    lp_point(s);
-    if (s.z[0] < 0.0) lp_flip(s);
-    double cmax = 0.0;
-    for (int j = s.lane; j < m; j += 32) { const double a = fabs(s.c[j]); cmax = a > cmax ? a : cmax; }
-    cmax = warp_max(cmax);
-    const int cap = 100 * K + 1000;
+// solve from the current dual-feasible vertex; radius = +inf disables pruning; on NODE_EXPLORE v[qd] is valid if qd < m
+__device__ int lp_solve(WS &s, double radius, double cmax, double &d_out) {
+    const int qd = s.qd, m = s.m;
+    lp_values(s);
+    if (s.val[0] < 0.0) lp_flip(s);
+    const int cap = 100 * m + 1000;
     bool refactored = false;
     for (int iter = 0;; ++iter) {
-        const double t = s.z[0];
-        if (!approxLE(t, radius)) return NODE_PRUNE;
-        int q = -1; double rmax = -1.0, rq = 0.0;
-        for (int j = s.lane; j < m; j += 32) {
-            const double r = residual(s, j);
-            if (fabs(r) > rmax) { rmax = fabs(r); q = j; rq = r; }
-        }
-        warp_argmax(rmax, q, rq);
+        const double t = s.val[0];
+        if (!approxLE(t, radius)) { if (iter == 0) s.quick++; return NODE_PRUNE; }
+        int pe = -1; double vmax = -1.0;
+        for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
+        warp_argmax(vmax, pe);
         const double tol = EPS_OPT * (cmax + t);
-        if (rmax <= t + tol) { d_out = t; xlast_out = s.z[K - 1]; return NODE_EXPLORE; }
-        if (iter >= cap) return NODE_FAIL;
-        bool dup = false;
-        for (int e = s.lane; e < K; e += 32) if (s.row[e] == q) dup = true;
-        if (__any_sync(FULLMASK, dup)) {
+        if (pe < 0 || vmax <= t + tol) {
+            const int nv = qd < m ? qd + 1 : qd;
+            lp_image(s, nv);
+            double err = 0.0;
+            for (int i = s.lane; i < qd; i += 32) { const double e = fabs(s.v[i] - s.chat[i]); err = e > err ? e : err; }
+            err = warp_max(err);
+            if (err <= 1.0e-8 * ((double)m * cmax + t)) { d_out = t; return NODE_EXPLORE; }
             if (refactored) return NODE_FAIL;
             refactored = true;
             if (lp_refactor(s)) return NODE_FAIL;
-            lp_gather(s); lp_point(s);
-            if (s.z[0] < 0.0) lp_flip(s);
+            lp_values(s);
+            if (s.val[0] < 0.0) lp_flip(s);
             continue;
         }
-        const int sq = rq > 0.0 ? 1 : -1;
-        lp_row(s, q, sq); lp_w(s);
-        const int l = lp_ratio(s, sq);
+        if (iter >= cap) return NODE_FAIL;
+        const int se = s.val[pe] > 0.0 ? 1 : -1;
+        const double nrm1 = lp_alpha_beta(s, pe);
+        if (fabs(nrm1 - 1.0) > 1.0e-6) {
+            if (refactored) return NODE_FAIL;
+            refactored = true;
+            if (lp_refactor(s)) return NODE_FAIL;
+            lp_values(s);
+            if (s.val[0] < 0.0) lp_flip(s);
+            continue;
+        }
+        const int l = lp_ratio(s, se, pe);
         if (l < 0) return NODE_FAIL;
-        lp_pivot(s, l);
-        if (s.lane == 0) { s.row[l] = q; s.sg[l] = sq; }
-        const double delta = (double)sq * (rmax - t);
-        for (int v = s.lane; v < K; v += 32) s.z[v] = fma(s.g[v], delta, s.z[v]);
-        __syncwarp();
+        if (lp_replace(s, pe, l, se)) return NODE_FAIL;
+        lp_values(s);
     }
-}
-
-// child transform: last variable becomes fixed; dir = sgn(x_last - u).  K -> K-1.
-__device__ int lp_child(WS &s, int dir) {
-    const int K = s.K, LD = s.LD;
-    for (int e = s.lane; e < K; e += 32) s.w[e] = s.W[(size_t)(K - 1) * LD + e];
-    __syncwarp();
-    const int l = lp_ratio(s, -dir);
-    if (l < 0) return -1;
-    lp_update(s, l, K - 1, false);
-    if (l != K - 1) {
-        for (int v = s.lane; v < K - 1; v += 32) s.W[(size_t)v * LD + l] = s.W[(size_t)v * LD + K - 1];
-        if (s.lane == 0) { s.row[l] = s.row[K - 1]; s.sg[l] = s.sg[K - 1]; }
-    }
-    __syncwarp();
-    s.K = K - 1;
-    return 0;
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // Level store and records
 // ------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI) {  // W (K x K) -> packed
-    const int K = s.K, LD = s.LD;
-    for (int e = s.lane; e < K * K; e += 32) { const int v = e / K, c = e - v * K; dH[e] = s.W[(size_t)v * LD + c]; }
-    for (int e = s.lane; e < K; e += 32) { dI[e] = s.row[e]; dI[K + e] = s.sg[e]; }
+// chain head: H (q x q packed), basic rows (q ints), signs (m bytes)
+__device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, signed char *dB) {
+    const int q = s.qd, LD = s.LD;
+    for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; dH[x] = s.W[(size_t)i * LD + c]; }
+    for (int p = s.lane; p < q; p += 32) dI[p] = s.zrow[p];
+    for (int j = s.lane; j < s.m; j += 32) dB[j] = s.sg[j];
 }
-__device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *dI, int K) {
+// loads a q x q head into the home of a basis of size q_home (q_home >= q: the caller may be about to extend it)
+__device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *dI, const signed char *dB, int q, int q_home) {
+    lp_home(s, q_home);
     const int LD = s.LD;
-    s.K = K;
-    for (int e = s.lane; e < K * K; e += 32) { const int v = e / K, c = e - v * K; s.W[(size_t)v * LD + c] = dH[e]; }
-    for (int e = s.lane; e < K; e += 32) { s.row[e] = dI[e]; s.sg[e] = dI[K + e]; }
+    s.qd = q;
+    for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
+    for (int j = s.lane; j < s.m; j += 32) { s.sg[j] = dB[j]; s.pos[j] = 0; }
+    for (int p = s.lane; p < q; p += 32) s.zrow[p] = dI[p];
+    __syncwarp();
+    for (int p = 1 + s.lane; p < q; p += 32) if (s.zrow[p] >= 0) s.pos[s.zrow[p]] = (unsigned char)p;
     __syncwarp();
 }
 
@@ -511,6 +601,10 @@ __device__ bool check_soln_dev(const Params &P, const long long *u, int lane) {
 // ------------------------------------------------------------------------------------------------------------
 struct Counters { unsigned long long niter, nprune, nodes, donated; };
 
+__device__ __forceinline__ void fail_search(const Params &P, int lane, int status) {
+    if (lane == 0) { P.q->status = status; P.q->abort = 1; }
+}
+
 __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &cnt, unsigned int *hist) {
     const int n = P.n, m = P.m, lane = s.lane;
     const RecLayout RL = rec_layout(n, m);
@@ -518,51 +612,69 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
     const int k0 = ((int *)R)[0];
     const int rflags = ((int *)R)[1];
     double xc0 = ((double *)R)[1];
+    const double gb0 = ((double *)R)[2];
     const bool is_root = (rflags & REC_ROOT) != 0;
     double *scrD = P.scrD + (size_t)gwarp * P.scrD_stride;
     int *scrI = P.scrI + (size_t)gwarp * P.scrI_stride;
-    double *cparL = scrD + chain_off(n + 1);  // (n+2) x m after the chains
-    auto chainH = [&](int k, int side) { return scrD + chain_off(k) + (size_t)side * k * k; };
-    auto chainI = [&](int k, int side) { return scrI + chain_ioff(k) + (size_t)side * 2 * k; };
+    signed char *scrB = P.scrB + (size_t)gwarp * P.scrB_stride;
+    double *cparL = scrD + chain_off(m + 1);                 // (n+2) x m
+    double *chatL = cparL + (size_t)(n + 2) * m;             // (n+2) x (m+1)
+    auto chainH = [&](int q, int side) { return scrD + chain_off(q) + (size_t)side * q * q; };
+    auto chainI = [&](int q, int side) { return scrI + chain_ioff(q) + (size_t)side * q; };
+    auto chainB = [&](int q, int side) { return scrB + ((size_t)q * 2 + side) * m; };
 
     // ---- load the record ----
     for (int e = lane; e < n; e += 32) { s.u[e] = ((long long *)(R + RL.off_u))[e]; s.ord[e] = (R + RL.off_ord)[e]; s.flags[e + 1] = 0; }
     for (int j = lane; j < m; j += 32) { const double v = ((double *)(R + RL.off_cpar))[j]; s.cpar[j] = v; cparL[(size_t)k0 * m + j] = v; }
-    int wk = -1, wside = -1;  // which chain the working matrix W currently equals
-    if (!is_root) {
-        chain_load(s, (const double *)(R + RL.off_H), (const int *)(R + RL.off_row), k0 + 1);
-        // row and sg are adjacent arrays of (n+1) ints in the record, but chain_load expects sg at dI[K+e]
-        for (int e = lane; e < k0 + 1; e += 32) s.sg[e] = ((const int *)(R + RL.off_sg))[e];
-        __syncwarp();
-        if (k0 + 1 <= n) { chain_store(s, chainH(k0 + 1, 0), chainI(k0 + 1, 0)); wk = k0 + 1; wside = 0; }
+    const int qpar = m - k0;  // basis size of the explored node this subtree hangs under (0: nothing to start from)
+    int wq = -1, wside = -1;  // which chain head the working matrix currently equals
+    if (!is_root && qpar > 0) {
+        chain_load(s, (const double *)(R + RL.off_H), (const int *)(R + RL.off_zrow), (const signed char *)(R + RL.off_sg), qpar, qpar + 1);
+        chain_store(s, chainH(qpar, 0), chainI(qpar, 0), chainB(qpar, 0));
+        for (int e = lane; e < qpar; e += 32) { const double v = ((double *)(R + RL.off_chat))[e]; s.chatpar[e] = v; chatL[(size_t)k0 * (m + 1) + e] = v; }
+        wq = qpar; wside = 0;
     }
     __syncwarp();
     __threadfence();
     if (lane == 0) ring_push(P.q, &P.q->ftail, P.fring, P.ring_mask, rec);  // the record slot is free again
 
-    double d = 0.0, xlast = 0.0;
+    double d = 0.0, xlast = 0.0, gb = gb0;
     if (is_root) {  // initial solve LP(n), closest.cc:206
-        for (int j = lane; j < m; j += 32) s.c[j] = s.cpar[j];
-        __syncwarp();
-        const int st = lp_cold(s, n + 1);
+        double cm = 0.0;
+        for (int j = lane; j < m; j += 32) { const double a = fabs(s.cpar[j]); cm = a > cm ? a : cm; }
+        cm = warp_max(cm);
         cnt.nodes++; if (lane == 0) hist[n]++;
-        int bad = 0;
-        if (st < 0) bad = 1;
-        else if (st == 1) xlast = s.z[n];
-        else if (lp_solve(s, INFINITY, d, xlast) != NODE_EXPLORE) bad = 1;
-        if (bad) { if (lane == 0) { P.q->status = BLTCU_STATUS_LP_FAIL; P.q->abort = 1; } return; }
+        double vq = 0.0;
+        if (qpar > 0) {
+            for (int i = lane; i < qpar; i += 32) s.chat[i] = P.QTp[m - 1 - i];
+            __syncwarp();
+            int bad = lp_init1(s);
+            for (int i = 1; i < qpar && !bad; ++i) {
+                lp_extend(s);
+                lp_values(s);
+                bad = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
+            }
+            if (bad || lp_solve(s, INFINITY, cm, d) != NODE_EXPLORE) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
+            vq = s.v[qpar];
+            chain_store(s, chainH(qpar, 0), chainI(qpar, 0), chainB(qpar, 0));
+            for (int e = lane; e < qpar; e += 32) { const double v = s.chat[e]; s.chatpar[e] = v; chatL[(size_t)k0 * (m + 1) + e] = v; }
+            wq = qpar; wside = 0;
+        }
+        gb = P.QTp[n - 1];
+        xlast = (gb - vq) / P.Rm[(size_t)(n - 1) * n + (n - 1)];
         xc0 = xlast;
+        __syncwarp();
     }
     int k = k0;
     if (lane == 0) {
         const long long un = (long long)round(xc0);
-        s.u[k - 1] = un; s.step[k - 1] = sgn_d(xc0 - (double)un); s.xc[k] = xc0; s.ord[k - 1] = 0; s.flags[k] = 0;
+        s.u[k - 1] = un; s.step[k - 1] = sgn_d(xc0 - (double)un); s.xc[k] = xc0; s.gbase[k] = gb; s.ord[k - 1] = 0; s.flags[k] = 0;
     }
     __syncwarp();
     const int depth0 = n - k0;
     const bool forced = depth0 < P.static_depth;  // static split: emit every explored child of this record
-
     unsigned int wd = 0;
+
     for (;;) {
         {   // one lane reads the stop flag so that the whole warp takes the same branch
             int ab = 0;
@@ -573,42 +685,62 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
             if (__shfl_sync(FULLMASK, ab, 0)) return;
         }
         // c = cpar - u[k-1] * B[k-1]
+        double cmax = 0.0;
         {
             const double mu = -(double)s.u[k - 1];
-            const double *Bk = s.Bs + (size_t)(k - 1) * s.LDB;
-            for (int j = lane; j < m; j += 32) s.c[j] = fma(mu, Bk[j], s.cpar[j]);
+            const double *Bk = P.B + (size_t)(k - 1) * m;
+            for (int j = lane; j < m; j += 32) { const double cj = fma(mu, Bk[j], s.cpar[j]); s.c[j] = cj; const double a = fabs(cj); cmax = a > cmax ? a : cmax; }
+            cmax = warp_max(cmax);
             __syncwarp();
         }
         cnt.nodes++; if (lane == 0) hist[k - 1]++;
         int status, side = 0;
-        const bool second_prune_possible = (s.flags[k] & 4) != 0;
+        const bool leaving_prune = (s.flags[k] & 4) != 0;
+        double gnext = 0.0;
         if (k == 1) {
-            double dm = 0.0;
-            for (int j = lane; j < m; j += 32) { const double a = fabs(s.c[j]); dm = a > dm ? a : dm; }
-            d = warp_max(dm);
+            d = cmax;
             status = approxLE(d, P.radius) ? NODE_EXPLORE : NODE_PRUNE;
         } else {
+            const int kk = k - 1, qd = m - kk;
             const int dir = sgn_d(s.xc[k] - (double)s.u[k - 1]);
             side = dir > 0 ? 0 : 1;
+            const double clast = fma(-(double)s.u[k - 1], P.Rm[(size_t)kk * n + kk], s.gbase[k]);
             const bool inited = (s.flags[k] >> side) & 1;
             if (!inited) {
-                if (is_root && k == n) {
-                    if (lp_cold(s, k) != 0) { if (lane == 0) { P.q->status = BLTCU_STATUS_LP_FAIL; P.q->abort = 1; } return; }
+                if (qd == 1) {
+                    if (lp_init1(s)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
                 } else {
-                    const int ps = (s.flags[k + 1] >> 3) & 1;
-                    if (!(wk == k + 1 && wside == ps)) chain_load(s, chainH(k + 1, ps), chainI(k + 1, ps), k + 1);
-                    if (lp_child(s, dir)) { if (lane == 0) { P.q->status = BLTCU_STATUS_LP_FAIL; P.q->abort = 1; } return; }
+                    const int ps = (k == k0) ? 0 : ((s.flags[k + 1] >> 3) & 1);
+                    if (!(wq == qd - 1 && wside == ps)) chain_load(s, chainH(qd - 1, ps), chainI(qd - 1, ps), chainB(qd - 1, ps), qd - 1, qd);
+                    lp_extend(s);
                 }
-                if (lane == 0) s.flags[k] |= (unsigned char)(1 << side);
+                for (int e = lane; e < qd - 1; e += 32) s.chat[e] = s.chatpar[e];
+                if (lane == 0) { s.chat[qd - 1] = clast; s.flags[k] |= (unsigned char)(1 << side); }
                 __syncwarp();
-            } else if (!(wk == k && wside == side)) chain_load(s, chainH(k, side), chainI(k, side), k);
-            status = lp_solve(s, P.radius, d, xlast);
-            if (status == NODE_FAIL) { if (lane == 0) { P.q->status = BLTCU_STATUS_LP_FAIL; P.q->abort = 1; } return; }
-            wk = k; wside = side;
+                if (qd > 1 && lp_drop_artificial(s, dir)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
+            } else {
+                if (!(wq == qd && wside == side)) chain_load(s, chainH(qd, side), chainI(qd, side), chainB(qd, side), qd, qd);
+                for (int e = lane; e < qd - 1; e += 32) s.chat[e] = s.chatpar[e];
+                if (lane == 0) s.chat[qd - 1] = clast;
+                __syncwarp();
+            }
+            status = lp_solve(s, P.radius, cmax, d);
+            if (status == NODE_FAIL) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
+            wq = qd; wside = side;
             // keep the chain head unless this is the prune that leaves the level
-            if (!(status == NODE_PRUNE && (second_prune_possible || (is_root && k == k0)))) {
-                chain_store(s, chainH(k, side), chainI(k, side));
+            if (!(status == NODE_PRUNE && (leaving_prune || (is_root && k == k0)))) {
+                chain_store(s, chainH(qd, side), chainI(qd, side), chainB(qd, side));
                 __syncwarp();
+            }
+            if (status == NODE_EXPLORE) {  // real centre of the next level: x_{kk-1} of the optimum
+                double gn = 0.0;
+                if (lane == 0) {
+                    gn = P.QTp[kk - 1];
+                    const double *Rr = P.Rm + (size_t)(kk - 1) * n;
+                    for (int i = kk; i < n; ++i) gn = fma(-(double)s.u[i], Rr[i], gn);
+                }
+                gnext = __shfl_sync(FULLMASK, gn, 0);
+                xlast = (gnext - s.v[qd]) / P.Rm[(size_t)(kk - 1) * n + (kk - 1)];
             }
         }
         if (status == NODE_PRUNE) {
@@ -617,7 +749,9 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
             if (s.flags[k] & 4) {  // second prune at this level: leave it
                 if (k == k0) return;
                 k++;
+                const int qp = m - k;  // entries of the parent right-hand side in complement coordinates
                 for (int j = lane; j < m; j += 32) s.cpar[j] = cparL[(size_t)k * m + j];
+                for (int e = lane; e < qp; e += 32) s.chatpar[e] = chatL[(size_t)k * (m + 1) + e];
             } else if (lane == 0) s.flags[k] |= 4;
             __syncwarp();
             if (lane == 0) {
@@ -630,6 +764,7 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
         }
         // explore
         if (k > 1) {
+            const int qd = m - k + 1;
             // hand the child to the queue instead of descending?
             bool emit = false;
             int slot = -1;
@@ -647,21 +782,17 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
                 if (lane == 0) slot = ring_pop(P.q, &P.q->fhead, &P.q->ftail, P.fring, P.ring_mask);
                 slot = __shfl_sync(FULLMASK, slot, 0);
                 if (slot < 0) {
-                    if (forced && k == k0) { if (lane == 0) { P.q->status = BLTCU_STATUS_ERROR; P.q->abort = 1; } return; }
+                    if (forced && k == k0) { fail_search(P, lane, BLTCU_STATUS_ERROR); return; }
                     emit = false;
                 }
             }
             if (emit) {
                 unsigned char *C = P.pool + (size_t)slot * RL.stride;
-                if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; }
+                if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gnext; }
                 for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
                 for (int j = lane; j < m; j += 32) ((double *)(C + RL.off_cpar))[j] = s.c[j];
-                {
-                    const int K = s.K, LD = s.LD;
-                    double *dH = (double *)(C + RL.off_H);
-                    for (int e = lane; e < K * K; e += 32) { const int v = e / K, c2 = e - v * K; dH[e] = s.W[(size_t)v * LD + c2]; }
-                    for (int e = lane; e < K; e += 32) { ((int *)(C + RL.off_row))[e] = s.row[e]; ((int *)(C + RL.off_sg))[e] = s.sg[e]; }
-                }
+                for (int e = lane; e < qd; e += 32) ((double *)(C + RL.off_chat))[e] = s.chat[e];
+                chain_store(s, (double *)(C + RL.off_H), (int *)(C + RL.off_zrow), (signed char *)(C + RL.off_sg));
                 __syncwarp();
                 __threadfence();
                 if (lane == 0) {
@@ -684,9 +815,10 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
             }
             // descend, closest.cc:88-95
             for (int j = lane; j < m; j += 32) { const double v = s.c[j]; cparL[(size_t)(k - 1) * m + j] = v; s.cpar[j] = v; }
+            for (int e = lane; e < qd; e += 32) { const double v = s.chat[e]; chatL[(size_t)(k - 1) * (m + 1) + e] = v; s.chatpar[e] = v; }
             if (lane == 0) {
                 s.flags[k] = (unsigned char)((s.flags[k] & ~8) | (side << 3));
-                s.xc[k - 1] = xlast;
+                s.xc[k - 1] = xlast; s.gbase[k - 1] = gnext;
                 const long long un = (long long)round(xlast);
                 s.u[k - 2] = un; s.step[k - 2] = sgn_d(xlast - (double)un);
                 s.flags[k - 1] = 0; s.ord[k - 2] = 0;
@@ -727,6 +859,7 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
             // explore(), closest.cc:99-104
             k = 2;
             for (int j = lane; j < m; j += 32) s.cpar[j] = cparL[(size_t)2 * m + j];
+            for (int e = lane; e < m - 2; e += 32) s.chatpar[e] = chatL[(size_t)2 * (m + 1) + e];
             if (lane == 0) {
                 const int st = s.step[1];
                 s.u[1] += st; s.step[1] = -st - (st > 0 ? 1 : -1);
@@ -738,32 +871,50 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
     }
 }
 
+// carves the per-warp shared-memory block
+__device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, int m, int QS, int LDS) {
+    const int M1 = m + 1;
+    s.Ws = base; base += (size_t)QS * LDS;
+    s.chat = base; base += M1; s.val = base; base += M1; s.w = base; base += M1; s.a = base; base += M1; s.v = base; base += M1;
+    s.chatpar = base; base += M1;
+    s.r = base; base += m; s.c = base; base += m; s.cpar = base; base += m;
+    s.xc = base; base += n + 2; s.gbase = base; base += n + 2;
+    s.u = (long long *)base; base += n;
+    int *ib = (int *)base;
+    s.zrow = ib; ib += M1; s.step = ib; ib += n + 1;
+    unsigned int *hist = (unsigned int *)ib; ib += n + 1;
+    unsigned char *bb = (unsigned char *)ib;
+    const int nb = ((n > m ? n : m) + 8) / 8 * 8;
+    s.pos = bb; bb += nb; s.sg = (signed char *)bb; bb += nb; s.ord = bb; bb += nb; s.flags = bb;
+    return hist;
+}
+__host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS) {
+    const size_t M1 = (size_t)m + 1;
+    const size_t d = (size_t)QS * LDS + 6 * M1 + 3 * (size_t)m + 2 * (size_t)(n + 2) + n;
+    const size_t i = M1 + 2 * (size_t)(n + 1);
+    const size_t nb = (size_t)((n > m ? n : m) + 8) / 8 * 8;
+    return (d * 8 + i * 4 + 4 * nb + 15) / 16 * 16;
+}
+
 // ------------------------------------------------------------------------------------------------------------
 // The persistent kernel
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
+__global__ void __launch_bounds__(512, 1) bltcu_search_kernel(const Params P) {
     extern __shared__ __align__(16) double smem[];
     const int n = P.n, m = P.m;
-    double *Bs = smem;
-    for (int e = threadIdx.x; e < n * P.LDB; e += blockDim.x) {
-        const int i = e / P.LDB, j = e - i * P.LDB;
-        Bs[e] = j < m ? P.B[(size_t)i * m + j] : 0.0;
+    double *Qs = smem;
+    for (int e = threadIdx.x; e < m * P.LDQ; e += blockDim.x) {
+        const int j = e / P.LDQ, i = e - j * P.LDQ;
+        Qs[e] = i < m ? P.Qrev[(size_t)j * m + i] : 0.0;
     }
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int gwarp = blockIdx.x * P.warps_per_cta + warp;
-    double *base = smem + (size_t)n * P.LDB + (size_t)warp * P.warp_smem_doubles;
     WS s;
-    const int KM = P.KMAX;
-    s.W = base; base += (size_t)KM * P.LD;
-    s.z = base; base += KM; s.g = base; base += KM; s.w = base; base += KM; s.a = base; base += KM; s.cS = base; base += KM;
-    s.c = base; base += m; s.cpar = base; base += m; s.xc = base; base += n + 2;
-    s.u = (long long *)base; base += n;
-    int *ib = (int *)base;
-    s.row = ib; ib += KM; s.sg = ib; ib += KM; s.tmpi = ib; ib += KM; s.tmps = ib; ib += KM; s.step = ib; ib += n + 1;
-    unsigned int *hist = (unsigned int *)ib; ib += n + 1;
-    s.ord = (unsigned char *)ib; s.flags = s.ord + ((n + 8) / 8 * 8);
-    s.Bs = Bs; s.LD = P.LD; s.LDB = P.LDB; s.n = n; s.m = m; s.K = 0; s.lane = lane;
+    unsigned int *hist = carve_warp(s, smem + (size_t)m * P.LDQ + (size_t)warp * P.warp_smem_doubles, n, m, P.QS, P.LDS);
+    s.Wg = P.bigW + (size_t)gwarp * P.bigW_stride; s.tmpA = s.Wg + (size_t)m * P.LDG;
+    s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS; s.W = s.Ws; s.LD = s.LDS;
+    s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0;
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     __syncwarp();
@@ -806,59 +957,81 @@ __global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
 }
 
 // small helper kernels ---------------------------------------------------------------------------------------
-__global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p,
-                                   unsigned long long *now) {
-    const int tid = blockIdx.x * blockDim.x + threadIdx.x;
-    if (tid == 0) *now = gtimer();
-    if (tid < n * m) B[tid] = (double)lat[tid];                                   // closest.cc:203
-    if (tid < m) p[tid] = (double)(con[2 * tid + 1] + con[2 * tid]) / 2.0;        // closest.cc:180-185
+// fp64 basis, centre and the geometry of the problem; one warp
+__global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p, double *Q,
+                                   double *Qrev, double *Rm, double *QTp, double *tmp, unsigned long long *now, int *rc) {
+    const int lane = threadIdx.x;
+    if (lane == 0) *now = gtimer();
+    for (int e = lane; e < n * m; e += 32) B[e] = (double)lat[e];                                 // closest.cc:203
+    for (int j = lane; j < m; j += 32) p[j] = (double)(con[2 * j + 1] + con[2 * j]) / 2.0;        // closest.cc:180-185
+    __syncwarp();
+    const int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
+    if (lane == 0) *rc = r;
 }
 __global__ void bltcu_check_kernel(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok) {
     Params P; P.n = n; P.m = m; P.lat = lat; P.con = con;
     const bool r = check_soln_dev(P, (const long long *)u, threadIdx.x & 31);
     if (threadIdx.x == 0) *ok = r ? 1 : 0;
 }
-// one cold layer-distance solve (test seam): c computed as glpk_wrapper.cc:156-166 does
-__global__ void bltcu_infdist_kernel(const double *B, int n, int m, int LD, int LDB, const int64_t *u, int k,
-                                     const double *p, double *x, double *dist, int *rc) {
+// one cold layer-distance solve (test seam): c computed as glpk_wrapper.cc:156-166 does.  Everything but the small
+// vectors lives in global memory here (QS = 0): this kernel is a test seam, not a hot path.
+__global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_t *u, int k, const double *p, double *x,
+                                     double *dist, int *rc, double *Q, double *Qrev, double *Rm, double *QTp, double *Wg,
+                                     double *tmp) {
     extern __shared__ __align__(16) double smem[];
-    double *Bs = smem;
     const int lane = threadIdx.x;
-    for (int e = lane; e < n * LDB; e += 32) { const int i = e / LDB, j = e - i * LDB; Bs[e] = j < m ? B[(size_t)i * m + j] : 0.0; }
-    __syncwarp();
-    const int KM = n + 1;
-    double *base = smem + (size_t)n * LDB;
     WS s;
-    s.W = base; base += (size_t)KM * LD;
-    s.z = base; base += KM; s.g = base; base += KM; s.w = base; base += KM; s.a = base; base += KM; s.cS = base; base += KM;
-    s.c = base; base += m; s.cpar = base; base += m; s.xc = base; base += n + 2;
-    s.u = (long long *)base; base += n;
-    int *ib = (int *)base;
-    s.row = ib; ib += KM; s.sg = ib; ib += KM; s.tmpi = ib; ib += KM; s.tmps = ib; ib += KM; s.step = ib;
-    s.Bs = Bs; s.LD = LD; s.LDB = LDB; s.n = n; s.m = m; s.K = 0; s.lane = lane;
+    (void)carve_warp(s, smem, n, m, 0, 1);
+    s.Wg = Wg; s.tmpA = Wg + (size_t)m * (m | 1);
+    s.LDS = 1; s.LDG = m | 1; s.QS = 0; s.W = s.Wg; s.LD = s.LDG;
+    s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0;
+    int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
+    double cm = 0.0;
     for (int i = lane; i < m; i += 32) {
         double rhs1 = 0.0;
         for (int j = k; j < n; ++j) rhs1 += (double)(-u[j]) * B[(size_t)j * m + i];
         rhs1 += p[i];
-        s.c[i] = rhs1;
+        s.c[i] = rhs1; s.r[i] = 0.0;
+        cm = fabs(rhs1) > cm ? fabs(rhs1) : cm;
     }
+    cm = warp_max(cm);
     __syncwarp();
-    int r = 0;
-    double d = 0.0, xl = 0.0;
-    if (k == 0) {
-        double dm = 0.0;
-        for (int j = lane; j < m; j += 32) { const double a = fabs(s.c[j]); dm = a > dm ? a : dm; }
-        d = warp_max(dm);
-    } else {
-        const int st = lp_cold(s, k + 1);
-        if (st < 0) r = -1;
-        else if (st == 1) {
-            double dm = 0.0;
-            for (int j = lane; j < m; j += 32) { const double a = fabs(residual(s, j)); dm = a > dm ? a : dm; }
-            d = warp_max(dm);
-        } else if (lp_solve(s, INFINITY, d, xl) != NODE_EXPLORE) r = -1;
-        if (r == 0) for (int i = lane; i < k; i += 32) x[i] = s.z[i + 1];
+    double d = 0.0;
+    const int qd = m - k;
+    if (k == 0) d = cm;
+    else if (r == 0) {
+        if (qd > 0) {
+            for (int i = lane; i < qd; i += 32) {
+                const double *Qi = Qrev + i, *c = s.c;
+                s.chat[i] = dot4(m, [&](int e) { return Qi[(size_t)e * m]; }, [&](int e) { return c[e]; });
+            }
+            __syncwarp();
+            r = lp_init1(s);
+            for (int i = 1; i < qd && r == 0; ++i) {
+                lp_extend(s);
+                lp_values(s);
+                r = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
+            }
+            if (r == 0 && lp_solve(s, INFINITY, cm, d) != NODE_EXPLORE) r = -1;
+            if (r == 0) {
+                const double t = s.val[0];
+                for (int j = lane; j < m; j += 32) s.r[j] = s.pos[j] ? s.val[s.pos[j]] : (double)s.sg[j] * t;
+                __syncwarp();
+            }
+        }
+        if (r == 0 && lane == 0) {  // x = R_k^-1 Q_k^T (c - r), one lane, the oracle's loops
+            for (int i = 0; i < k; ++i) {
+                double acc = 0.0;
+                for (int j = 0; j < m; ++j) acc = fma(Q[(size_t)i * m + j], s.c[j] - s.r[j], acc);
+                s.w[i] = acc;
+            }
+            for (int i = k - 1; i >= 0; --i) {
+                double acc = s.w[i];
+                for (int t = i + 1; t < k; ++t) acc = fma(-Rm[(size_t)i * n + t], x[t], acc);
+                x[i] = acc / Rm[(size_t)i * n + i];
+            }
+        }
     }
     if (lane == 0) { *dist = d; *rc = r; }
 }
@@ -913,6 +1086,80 @@ int ws_reserve(DevWs *w, size_t bytes) {
     return 0;
 }
 size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// Layout of one search's global workspace, shared by the cached-workspace path and the fixed-array path.
+struct Layout {
+    int KQS, LDS, LDG, LDQ, wpc, ctas, nwarps, pool_cap;
+    size_t warp_bytes, smem_bytes, scrD_stride, scrI_stride, scrB_stride, bigW_stride;
+    size_t o_q, o_in, o_B, o_p, o_Q, o_Qrev, o_Rm, o_QTp, o_tmp, o_rc, o_ring, o_fring, o_out, o_sol, o_bu, o_bk, o_bv, o_pool,
+        o_scrD, o_scrI, o_scrB, o_bigW, total;
+    RecLayout RL;
+};
+int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap) {
+    L.KQS = std::min(m, QS_MAX); L.LDS = L.KQS | 1; L.LDG = m | 1; L.LDQ = m | 1;
+    L.warp_bytes = warp_smem_bytes(n, m, L.KQS, L.LDS);
+    const size_t q_bytes = (size_t)m * L.LDQ * 8;
+    int wpc = (int)((smem_budget > q_bytes ? smem_budget - q_bytes : 0) / L.warp_bytes);
+    if (wpc > max_wpc) wpc = max_wpc;
+    if (want_wpc > 0 && want_wpc < wpc) wpc = want_wpc;
+    if (wpc < 1) return -1;
+    L.wpc = wpc;
+    L.ctas = want_ctas > 0 ? want_ctas : sms;
+    L.nwarps = L.ctas * wpc;
+    L.smem_bytes = q_bytes + (size_t)wpc * L.warp_bytes;
+    L.RL = rec_layout(n, m);
+    L.pool_cap = pool_cap;
+    while ((size_t)L.pool_cap * L.RL.stride > ((size_t)3 << 30) && L.pool_cap > 256) L.pool_cap >>= 1;
+    L.scrD_stride = align_up(chain_off(m + 1) + (size_t)(n + 2) * m + (size_t)(n + 2) * (m + 1), 32);
+    L.scrI_stride = align_up(chain_ioff(m + 1) + 8, 32);
+    L.scrB_stride = align_up((size_t)(m + 2) * 2 * m, 32);
+    L.bigW_stride = align_up((size_t)m * L.LDG + (size_t)m * m, 32);
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
+    L.o_q = carve(sizeof(QCtl));
+    L.o_in = carve(((size_t)n * m + 2 * (size_t)m) * 8);
+    L.o_B = carve((size_t)n * m * 8);
+    L.o_p = carve((size_t)m * 8);
+    L.o_Q = carve((size_t)m * m * 8);
+    L.o_Qrev = carve((size_t)m * m * 8);
+    L.o_Rm = carve((size_t)n * n * 8);
+    L.o_QTp = carve((size_t)m * 8);
+    L.o_tmp = carve((size_t)2 * m * 8);
+    L.o_rc = carve(16);
+    L.o_ring = carve((size_t)L.pool_cap * 4);
+    L.o_fring = carve((size_t)L.pool_cap * 4);
+    L.o_out = carve((size_t)L.pool_cap * 4);
+    L.o_sol = carve((size_t)n * 8 + 8);
+    L.o_bu = carve((size_t)L.nwarps * n * 8);
+    L.o_bk = carve((size_t)L.nwarps * n);
+    L.o_bv = carve((size_t)L.nwarps * 4);
+    L.o_pool = carve((size_t)L.pool_cap * L.RL.stride);
+    L.o_scrD = carve((size_t)L.nwarps * L.scrD_stride * 8);
+    L.o_scrI = carve((size_t)L.nwarps * L.scrI_stride * 4);
+    L.o_scrB = carve((size_t)L.nwarps * L.scrB_stride);
+    L.o_bigW = carve((size_t)L.nwarps * L.bigW_stride * 8);
+    L.total = off;
+    return 0;
+}
+void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) {
+    memset(&P, 0, sizeof P);
+    P.n = n; P.m = m; P.LDQ = L.LDQ; P.QS = L.KQS; P.LDS = L.LDS; P.LDG = L.LDG;
+    P.B = (double *)(base + L.o_B); P.p = (double *)(base + L.o_p);
+    P.Qrev = (double *)(base + L.o_Qrev); P.Rm = (double *)(base + L.o_Rm); P.QTp = (double *)(base + L.o_QTp);
+    P.q = (QCtl *)(base + L.o_q);
+    P.ring = (int *)(base + L.o_ring); P.fring = (int *)(base + L.o_fring); P.ring_mask = (unsigned int)L.pool_cap - 1;
+    P.pool = base + L.o_pool; P.rec_stride = L.RL.stride; P.pool_cap = L.pool_cap;
+    P.scrD = (double *)(base + L.o_scrD); P.scrD_stride = L.scrD_stride;
+    P.scrI = (int *)(base + L.o_scrI); P.scrI_stride = L.scrI_stride;
+    P.scrB = (signed char *)(base + L.o_scrB); P.scrB_stride = L.scrB_stride;
+    P.bigW = (double *)(base + L.o_bigW); P.bigW_stride = L.bigW_stride;
+    P.sol = (int64_t *)(base + L.o_sol);
+    P.best_u = (int64_t *)(base + L.o_bu); P.best_key = base + L.o_bk; P.best_valid = (int *)(base + L.o_bv);
+    P.out_list = (int *)(base + L.o_out);
+    P.warps_per_cta = L.wpc;
+    P.warp_smem_doubles = L.warp_bytes / 8;
+    P.lowwater = std::min(L.nwarps, L.pool_cap / 4);
+}
 }  // namespace
 
 static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
@@ -926,106 +1173,61 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (world > 1 && o.split_depth <= 0) o.split_depth = std::min(6, std::max(1, n - 3));
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
-    // ---- launch shape from the shared-memory budget ----
-    const int KMAX = n + 1;
-    const int LD = KMAX | 1, LDB = m | 1;
-    size_t wd = (size_t)KMAX * LD + 5 * (size_t)KMAX + 2 * (size_t)m + (n + 2) + n;           // doubles
-    size_t wi = 4 * (size_t)KMAX + (n + 1) + (n + 1);                                         // ints
-    size_t wb = 2 * (size_t)((n + 8) / 8 * 8) + 16;                                            // bytes
-    size_t warp_bytes = align_up(wd * 8 + wi * 4 + wb, 16);
-    const size_t b_bytes = (size_t)n * LDB * 8;
-    const size_t budget = w->smem_optin;
-    int wpc = (int)((budget > b_bytes ? budget - b_bytes : 0) / warp_bytes);
-    if (wpc > 8) wpc = 8;
-    if (o.warps_per_cta > 0 && o.warps_per_cta < wpc) wpc = o.warps_per_cta;
-    if (wpc < 1) {
-        fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, budget);
+    Layout L;
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 16, 4096)) {
+        fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }
-    int ctas = o.ctas > 0 ? o.ctas : w->sms;
-    const int nwarps = ctas * wpc;
-    const size_t smem_bytes = b_bytes + (size_t)wpc * warp_bytes;
-
-    // ---- carve the global workspace ----
-    const RecLayout RL = rec_layout(n, m);
-    int pool_cap = 4096;
-    while ((size_t)pool_cap * RL.stride > ((size_t)3 << 30) && pool_cap > 256) pool_cap >>= 1;
-    const unsigned int ring_cap = (unsigned int)pool_cap;  // power of two
-    const size_t scrD_stride = align_up(chain_off(n + 1) + (size_t)(n + 2) * m, 32);
-    const size_t scrI_stride = align_up(chain_ioff(n + 1) + 8, 32);
-    size_t off = 0;
-    auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
-    const size_t o_q = carve(sizeof(QCtl));
-    const size_t o_B = carve((size_t)n * m * 8);
-    const size_t o_p = carve((size_t)m * 8);
-    const size_t o_ring = carve((size_t)ring_cap * 4);
-    const size_t o_fring = carve((size_t)ring_cap * 4);
-    const size_t o_out = carve((size_t)pool_cap * 4);
-    const size_t o_sol = carve((size_t)n * 8);
-    const size_t o_bu = carve((size_t)nwarps * n * 8);
-    const size_t o_bk = carve((size_t)nwarps * n);
-    const size_t o_bv = carve((size_t)nwarps * 4);
-    const size_t o_pool = carve((size_t)pool_cap * RL.stride);
-    const size_t o_scrD = carve((size_t)nwarps * scrD_stride * 8);
-    const size_t o_scrI = carve((size_t)nwarps * scrI_stride * 4);
-    if (ws_reserve(w, off)) return BLTCU_STATUS_ERROR;
+    if (ws_reserve(w, L.total)) return BLTCU_STATUS_ERROR;
     unsigned char *base = (unsigned char *)w->buf;
     cudaStream_t st = w->stream;
+    const int ctas = L.ctas, wpc = L.wpc, nwarps = L.nwarps, pool_cap = L.pool_cap;
+    const unsigned int ring_cap = (unsigned int)pool_cap;
+    const RecLayout RL = L.RL;
+    const size_t smem_bytes = L.smem_bytes;
 
     Params P;
-    memset(&P, 0, sizeof P);
-    P.n = n; P.m = m; P.LD = LD; P.LDB = LDB; P.KMAX = KMAX;
-    P.B = (double *)(base + o_B); P.p = (double *)(base + o_p);
+    fill_params(P, L, base, n, m);
     P.lat = d_lat; P.con = d_con;
-    P.q = (QCtl *)(base + o_q);
-    P.ring = (int *)(base + o_ring); P.fring = (int *)(base + o_fring); P.ring_mask = ring_cap - 1;
-    P.pool = base + o_pool; P.rec_stride = RL.stride; P.pool_cap = pool_cap;
-    P.scrD = (double *)(base + o_scrD); P.scrD_stride = scrD_stride;
-    P.scrI = (int *)(base + o_scrI); P.scrI_stride = scrI_stride;
-    P.sol = (int64_t *)(base + o_sol);
-    P.best_u = (int64_t *)(base + o_bu); P.best_key = base + o_bk; P.best_valid = (int *)(base + o_bv);
-    P.out_list = (int *)(base + o_out);
     P.donate_min_level = o.donate_min_level > 0 ? std::max(2, o.donate_min_level) : std::min(6, std::max(2, n / 3));
-    P.lowwater = std::min(nwarps, pool_cap / 4);
     P.no_early_exit = o.no_early_exit;
-    P.warps_per_cta = wpc;
-    P.warp_smem_doubles = warp_bytes / 8;
 
     CK(cudaFuncSetAttribute(bltcu_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     int launches = 0;
-    bltcu_setup_kernel<<<(n * m + 255) / 256, 256, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p,
-                                                          (unsigned long long *)P.sol);
+    bltcu_setup_kernel<<<1, 32, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q),
+                                        (double *)P.Qrev, (double *)P.Rm, (double *)P.QTp, (double *)(base + L.o_tmp),
+                                        (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8));
     CK(cudaGetLastError());
     launches++;
-    // radius: closest.cc:193-194 uses row 0 only; device clock for the watchdog deadline
+    // radius: closest.cc:193-194 uses row 0 only; device clock for the watchdog deadline; status of the geometry
     int64_t con0[2];
-    unsigned long long now_ns = 0, deadline_ns = 0;
+    unsigned long long now_rc[2] = {0, 0};
+    unsigned long long deadline_ns = 0;
     CK(cudaMemcpyAsync(con0, d_con, 16, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(&now_ns, P.sol, 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(now_rc, base + L.o_rc, 16, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    if ((int)(now_rc[1] & 0xffffffffu) != 0) return BLTCU_STATUS_LP_FAIL;  // dependent basis rows
     P.radius = (double)(con0[1] - con0[0]) / 2.0;
     {
         long long tmo = o.timeout_ms;
         if (tmo <= 0) { const char *e = getenv("BLTCU_TIMEOUT_MS"); if (e) tmo = atoll(e); }
-        if (tmo > 0) deadline_ns = now_ns + (unsigned long long)tmo * 1000000ull;
+        if (tmo > 0) deadline_ns = now_rc[0] + (unsigned long long)tmo * 1000000ull;
     }
 
     // host images of the control block and rings
     std::vector<int> ring(ring_cap, -1), fring(ring_cap);
     QCtl hq;
-    auto reset_ctl = [&](const std::vector<int> &initial, int first_free) -> int {
+    auto reset_ctl = [&](const std::vector<int> &initial) -> int {
         memset(&hq, 0, sizeof hq);
         std::fill(ring.begin(), ring.end(), -1);
         for (size_t i = 0; i < initial.size(); ++i) ring[i] = initial[i];
         hq.tail = (unsigned int)initial.size();
         hq.pending = (int)initial.size();
-        // free ring: slots not in use
         std::fill(fring.begin(), fring.end(), -1);
         unsigned int nf = 0;
         std::vector<char> used(pool_cap, 0);
         for (int r : initial) used[r] = 1;
-        for (int i = 0; i < pool_cap; ++i) if (!used[i] && i >= first_free) fring[nf++] = i;
-        for (int i = 0; i < std::min(first_free, pool_cap); ++i) if (!used[i]) fring[nf++] = i;
+        for (int i = 0; i < pool_cap; ++i) if (!used[i]) fring[nf++] = i;
         hq.ftail = nf;
         hq.deadline_ns = deadline_ns;
         CK(cudaMemcpyAsync(P.q, &hq, sizeof hq, cudaMemcpyHostToDevice, st));
@@ -1043,7 +1245,6 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         ((int *)rec.data())[1] = REC_ROOT;
         CK(cudaMemcpyAsync(P.pool, rec.data(), RL.stride, cudaMemcpyHostToDevice, st));
         CK(cudaStreamSynchronize(st));
-        // cpar = p lives on the device: copy it there
         CK(cudaMemcpyAsync(P.pool + RL.off_cpar, P.p, (size_t)m * 8, cudaMemcpyDeviceToDevice, st));
     }
 
@@ -1077,7 +1278,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > 0) {
         // phase A: deterministic static split of the top levels (every rank computes the same list)
         initial.assign(1, 0);
-        if (reset_ctl(initial, 1)) return BLTCU_STATUS_ERROR;
+        if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
         P.static_depth = o.split_depth; P.dynamic = 0;
         if (launch()) return BLTCU_STATUS_ERROR;
         status = hq.status; found = hq.found;
@@ -1097,8 +1298,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         for (size_t i = 0; i < idx.size(); ++i) if ((int)(i % world) == rank) initial.push_back(out[idx[i]]);
         const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0));
         if (!stop && !initial.empty()) {
-            // phase B keeps every record of phase A alive only if it is in this rank's hand; the rest is free
-            if (reset_ctl(initial, 0)) return BLTCU_STATUS_ERROR;
+            if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
             if (found) { hq.found = 1; CK(cudaMemcpyAsync(P.q, &hq, sizeof hq, cudaMemcpyHostToDevice, st)); }
             P.static_depth = 0; P.dynamic = 1;
             if (launch()) return BLTCU_STATUS_ERROR;
@@ -1108,7 +1308,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         }
     } else {
         initial.assign(1, 0);
-        if (reset_ctl(initial, 1)) return BLTCU_STATUS_ERROR;
+        if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
         P.static_depth = 0; P.dynamic = 1;
         if (launch()) return BLTCU_STATUS_ERROR;
         status = hq.status; found = hq.found;
@@ -1143,7 +1343,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         stats->found = found;
         stats->launches = launches;
         stats->warps = nwarps; stats->ctas = ctas;
-        stats->scratch_bytes = off;
+        stats->scratch_bytes = L.total;
         stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
     }
     return status;
@@ -1228,20 +1428,21 @@ extern "C" int bltcu_infdist(const double *B, int n, int m, const int64_t *u, in
     std::lock_guard<std::mutex> lk(g_mu);
     DevWs *w = nullptr;
     if (get_ws(0, &w)) return BLTCU_STATUS_ERROR;
-    const int KMAX = n + 1, LD = KMAX | 1, LDB = m | 1;
-    const size_t smem = ((size_t)n * LDB + (size_t)KMAX * LD + 5 * (size_t)KMAX + 2 * (size_t)m + (n + 2) + n) * 8 +
-                        (5 * (size_t)KMAX + 8) * 4;
-    if (smem > w->smem_optin) return BLTCU_STATUS_ERROR;
-    const size_t nb = (size_t)n * m * 8, nu = (size_t)n * 8, np = (size_t)m * 8;
+    const size_t smem = warp_smem_bytes(n, m, 0, 1);
+    const size_t nb = (size_t)n * m, mm = (size_t)m * m;
+    // doubles: B, p, x, dist+rc, Q, Qrev, Rm, QTp, Wg (m*LDG + m*m), tmp (2m); then u
+    const size_t nd = nb + m + n + 2 + mm + mm + (size_t)n * n + m + ((size_t)m * (m | 1) + mm) + 2 * (size_t)m;
     unsigned char *d = nullptr;
-    CK(cudaMalloc((void **)&d, nb + nu + np + nu + 16));
-    double *dB = (double *)d; int64_t *du = (int64_t *)(d + nb); double *dp = (double *)(d + nb + nu);
-    double *dx = (double *)(d + nb + nu + np); double *dd = (double *)(d + nb + nu + np + nu); int *drc = (int *)(dd + 1);
-    CK(cudaMemcpy(dB, B, nb, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(du, u, nu, cudaMemcpyHostToDevice));
-    CK(cudaMemcpy(dp, p, np, cudaMemcpyHostToDevice));
+    CK(cudaMalloc((void **)&d, nd * 8 + (size_t)n * 8));
+    double *dB = (double *)d, *dp = dB + nb, *dx = dp + m, *dd = dx + n, *dQ = dd + 2, *dQrev = dQ + mm, *dRm = dQrev + mm;
+    double *dQTp = dRm + (size_t)n * n, *dWg = dQTp + m, *dtmp = dWg + ((size_t)m * (m | 1) + mm);
+    int64_t *du = (int64_t *)(dtmp + 2 * (size_t)m);
+    int *drc = (int *)(dd + 1);
+    CK(cudaMemcpy(dB, B, nb * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(du, u, (size_t)n * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dp, p, (size_t)m * 8, cudaMemcpyHostToDevice));
     CK(cudaFuncSetAttribute(bltcu_infdist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    bltcu_infdist_kernel<<<1, 32, smem, w->stream>>>(dB, n, m, LD, LDB, du, k, dp, dx, dd, drc);
+    bltcu_infdist_kernel<<<1, 32, smem, w->stream>>>(dB, n, m, du, k, dp, dx, dd, drc, dQ, dQrev, dRm, dQTp, dWg, dtmp);
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(w->stream));
     int rc = 0;
@@ -1266,7 +1467,7 @@ extern "C" void bltcu_release(void) {
     g_ws.clear();
 }
 
-extern "C" const char *bltcu_version(void) { return "blt-b200 0.1 (sm_100a)"; }
+extern "C" const char *bltcu_version(void) { return "blt-b200 0.2 (sm_100a)"; }
 
 // ------------------------------------------------------------------------------------------------------------
 // Allocation-free variant of the search
@@ -1352,78 +1553,41 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
         g_noalloc_dev[device] = ptr;
     }
     unsigned char *base = g_noalloc_dev[device];
-    const int wpc = BLTCU_NOALLOC_WPC;
-    const int ctas = std::min(g_noalloc_sms[device], BLTCU_NOALLOC_CTAS);
-    const int nwarps = ctas * wpc;
-
-    // same shared-memory and workspace carving as search_impl(), but inside the fixed array
-    const int KMAX = n + 1, LD = KMAX | 1, LDB = m | 1;
-    const size_t wd = (size_t)KMAX * LD + 5 * (size_t)KMAX + 2 * (size_t)m + (n + 2) + n;
-    const size_t wi = 4 * (size_t)KMAX + (n + 1) + (n + 1);
-    const size_t wb = 2 * (size_t)((n + 8) / 8 * 8) + 16;
-    const size_t warp_bytes = align_up(wd * 8 + wi * 4 + wb, 16);
-    const size_t smem_bytes = (size_t)n * LDB * 8 + (size_t)wpc * warp_bytes;
-    if (smem_bytes > g_noalloc_smem[device]) return BLTCU_STATUS_ERROR;
-    const RecLayout RL = rec_layout(n, m);
-    const size_t scrD_stride = align_up(chain_off(n + 1) + (size_t)(n + 2) * m, 32);
-    const size_t scrI_stride = align_up(chain_ioff(n + 1) + 8, 32);
-    size_t off = 0;
-    auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
-    const size_t o_q = carve(sizeof(QCtl));
-    const size_t o_in = carve(((size_t)n * m + 2 * (size_t)m) * 8);
-    const size_t o_B = carve((size_t)n * m * 8);
-    const size_t o_p = carve((size_t)m * 8);
-    const size_t o_ring = carve((size_t)BLTCU_NOALLOC_POOL * 4);
-    const size_t o_fring = carve((size_t)BLTCU_NOALLOC_POOL * 4);
-    const size_t o_out = carve((size_t)BLTCU_NOALLOC_POOL * 4);
-    const size_t o_sol = carve((size_t)n * 8);
-    const size_t o_bu = carve((size_t)nwarps * n * 8);
-    const size_t o_bk = carve((size_t)nwarps * n);
-    const size_t o_bv = carve((size_t)nwarps * 4);
-    const size_t o_pool = carve((size_t)BLTCU_NOALLOC_POOL * RL.stride);
-    const size_t o_scrD = carve((size_t)nwarps * scrD_stride * 8);
-    const size_t o_scrI = carve((size_t)nwarps * scrI_stride * 4);
-    if (off > (size_t)BLTCU_NOALLOC_BYTES) {
-        fprintf(stderr, "bltcu_closest_noalloc: internal layout (%zu bytes) exceeds the scratch array\n", off);
+    // same shared-memory and workspace layout as search_impl(), but inside the fixed array
+    Layout L;
+    if (make_layout(L, n, m, g_noalloc_smem[device], std::min(g_noalloc_sms[device], BLTCU_NOALLOC_CTAS), BLTCU_NOALLOC_WPC, 0,
+                    BLTCU_NOALLOC_WPC, BLTCU_NOALLOC_POOL))
+        return BLTCU_STATUS_ERROR;
+    if (L.total > (size_t)BLTCU_NOALLOC_BYTES) {
+        fprintf(stderr, "bltcu_closest_noalloc: internal layout (%zu bytes) exceeds the scratch array\n", L.total);
         return BLTCU_STATUS_ERROR;
     }
-    int64_t *d_lat = (int64_t *)(base + o_in), *d_con = d_lat + (size_t)n * m;
+    const int wpc = L.wpc, ctas = L.ctas, nwarps = L.nwarps;
+    const size_t smem_bytes = L.smem_bytes;
+    int64_t *d_lat = (int64_t *)(base + L.o_in), *d_con = d_lat + (size_t)n * m;
     Params P;
-    memset(&P, 0, sizeof P);
-    P.n = n; P.m = m; P.LD = LD; P.LDB = LDB; P.KMAX = KMAX;
-    P.B = (double *)(base + o_B); P.p = (double *)(base + o_p);
+    fill_params(P, L, base, n, m);
     P.lat = d_lat; P.con = d_con;
-    P.q = (QCtl *)(base + o_q);
-    P.ring = (int *)(base + o_ring); P.fring = (int *)(base + o_fring); P.ring_mask = BLTCU_NOALLOC_POOL - 1;
-    P.pool = base + o_pool; P.rec_stride = RL.stride; P.pool_cap = BLTCU_NOALLOC_POOL;
-    P.scrD = (double *)(base + o_scrD); P.scrD_stride = scrD_stride;
-    P.scrI = (int *)(base + o_scrI); P.scrI_stride = scrI_stride;
-    P.sol = (int64_t *)(base + o_sol);
-    P.best_u = (int64_t *)(base + o_bu); P.best_key = base + o_bk; P.best_valid = (int *)(base + o_bv);
-    P.out_list = (int *)(base + o_out);
     P.static_depth = 0; P.dynamic = 1;
     P.donate_min_level = std::min(6, std::max(2, n / 3));
-    P.lowwater = std::min(nwarps, BLTCU_NOALLOC_POOL / 4);
     P.no_early_exit = 0;
-    P.warps_per_cta = wpc;
-    P.warp_smem_doubles = warp_bytes / 8;
     P.radius = (double)(con[1] - con[0]) / 2.0;  // closest.cc:193-194: row 0 only
 
     cudaStream_t st = 0;  // legacy default stream: creating a stream would be an allocation
     CK(cudaMemcpyAsync(d_lat, lat, (size_t)n * m * 8, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(d_con, con, (size_t)2 * m * 8, cudaMemcpyHostToDevice, st));
-    bltcu_setup_kernel<<<(n * m + 255) / 256, 256, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p,
-                                                          (unsigned long long *)P.sol);
+    bltcu_setup_kernel<<<1, 32, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q),
+                                        (double *)P.Qrev, (double *)P.Rm, (double *)P.QTp, (double *)(base + L.o_tmp),
+                                        (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8));
     CK(cudaGetLastError());
+    unsigned long long now_rc[2] = {0, 0};
+    CK(cudaMemcpyAsync(now_rc, base + L.o_rc, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    if ((int)(now_rc[1] & 0xffffffffu) != 0) return BLTCU_STATUS_LP_FAIL;
     unsigned long long deadline_ns = 0;
     if (const char *e = getenv("BLTCU_TIMEOUT_MS")) {
         const long long tmo = atoll(e);
-        if (tmo > 0) {
-            unsigned long long now_ns = 0;
-            CK(cudaMemcpyAsync(&now_ns, P.sol, 8, cudaMemcpyDeviceToHost, st));
-            CK(cudaStreamSynchronize(st));
-            deadline_ns = now_ns + (unsigned long long)tmo * 1000000ull;
-        }
+        if (tmo > 0) deadline_ns = now_rc[0] + (unsigned long long)tmo * 1000000ull;
     }
     bltcu_noalloc_init_kernel<<<1, 256, 0, st>>>(P, deadline_ns, nwarps);  // one block: its barrier orders the clears
     CK(cudaGetLastError());

@@ -600,8 +600,13 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
             if (status == NODE_FAIL) { rc = BLT_STATUS_LP_FAIL; goto done; }
             chain_store(&ch[k][side], lp);
             if (status == NODE_EXPLORE) { /* real centre of the next level: x_{kk-1} of the optimum */
-                double gn = g.QTp[kk - 1];
-                for (int i = kk; i < n; ++i) gn = fma(-(double)u[i], g.Rm[(size_t)(kk - 1) * n + i], gn);
+                /* next coordinate of the rotated right-hand side: the part fixed by the levels above (32-lane order),
+                 * then this level's own coefficient */
+                double part[32];
+                for (int l = 0; l < 32; ++l) part[l] = 0.0;
+                for (int i = kk + 1; i < n; ++i) part[(i - kk - 1) & 31] = fma(-(double)u[i], g.Rm[(size_t)(kk - 1) * n + i], part[(i - kk - 1) & 31]);
+                const double g2 = g.QTp[kk - 1] + butterfly32(part);
+                const double gn = fma(-(double)u[kk], g.Rm[(size_t)(kk - 1) * n + kk], g2);
                 gbase[k - 1] = gn;
                 xlast = (gn - lp->v[qd]) / g.Rm[(size_t)(kk - 1) * n + (kk - 1)];
             }
