@@ -13,10 +13,13 @@
 //   * Going one level down adds one coordinate: H is bordered with an artificial column which is then pivoted out.
 //   * Warm starts ("side chains"): a node starts from the final vertex of the previous sibling on the same side of
 //     the level's real centre, or, for the first node of a side, from its parent's optimal vertex extended by the
-//     level's coordinate.  Chain heads live in a per-warp level store in global memory (L2 resident).
-//   * Load balance: a global MPMC queue of subtree records.  A warp that explores a child while other warps are
-//     idle writes the child as a record instead of descending.  Every node is still solved exactly once, from the
-//     same starting vertex as in the sequential order, so niter and nprune do not depend on scheduling.
+//     level's coordinate.  Both chains of the level being expanded live in shared memory.
+//   * A task is ONE sibling loop: all children of an explored node are solved back to back (the set of siblings
+//     visited depends only on their own LP outcomes, closest.cc:110-122), every explored child becomes a record: the
+//     first one is expanded next by the same warp, the others go on the warp's private stack in global memory.
+//   * Load balance: a global MPMC queue of records.  A warp whose stack is non-empty while other warps are idle
+//     moves its OLDEST record (the largest subtree) to the queue.  Every node is solved exactly once, from the same
+//     starting vertex as in the sequential order, so niter and nprune do not depend on scheduling.
 //
 // Floating point: every operation below has a twin in oracle/blt_oracle.c with the same operand order; compile
 // with -fmad=false so that only the explicit fma() calls fuse.  FP64 FMA pipe is the roofline (no tensor cores:
@@ -44,7 +47,7 @@
 #define QS_MAX 32  // largest basis kept in shared memory
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
-enum { REC_ROOT = 1 };
+enum { REC_TOP = 1 };  // record flag: its children are the top level (first prune ends the search, closest.cc:280-286)
 
 // ------------------------------------------------------------------------------------------------------------
 // Global control block (one per search, zeroed by the host before launch)
@@ -62,6 +65,7 @@ struct QCtl {
     int pad1;
     unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
     unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated;
+    unsigned long long idle_ns, busy_ns;  // summed over warps: time spent waiting for work / expanding records
     unsigned long long hist[MAXD + 1];
 };
 
@@ -82,14 +86,13 @@ struct Params {
     unsigned char *pool;    // subtree records
     size_t rec_stride;
     int pool_cap;
-    double *scrD;           // per-warp level store (doubles): chain matrices, parent right-hand sides
-    size_t scrD_stride;
-    int *scrI;              // per-warp level store (ints): basic rows of the chain heads
-    size_t scrI_stride;
-    signed char *scrB;      // per-warp level store (bytes): signs of the chain heads
-    size_t scrB_stride;
-    double *bigW;           // per-warp H for q > QS (m x LDG) followed by the refactorisation scratch (m x m)
-    size_t bigW_stride;
+    double *wbuf;           // per-warp doubles: parent H (m x m), two side matrices for q > QS (m x LDG each), m x m scratch
+    size_t wbuf_stride;
+    unsigned char *nextrec; // per-warp: two record buffers for the child the warp expands next
+    unsigned char *arena;   // per-warp private stack of pending records, followed by its table of offsets
+    size_t arena_stride;    // bytes per warp (stack + table)
+    size_t arena_bytes;     // bytes of the stack part
+    int arena_slots;        // entries of the offset table
     int64_t *sol;           // n, written by the finder
     int64_t *best_u;        // per warp: n (last recorded candidate)
     unsigned char *best_key;// per warp: n
@@ -122,7 +125,12 @@ __host__ __device__ inline RecLayout rec_layout(int n, int m) {
     L.stride = (o + 255) / 256 * 256;
     return L;
 }
-// level store, indexed by the basis size q = 1..m of the level; two chains per q
+// bytes a record for children level k really uses (its basis has size m - k; leaf-level records carry no basis)
+__host__ __device__ inline size_t rec_bytes(const RecLayout &L, int m, int k) {
+    const size_t q = (size_t)(m - k);
+    return k <= 1 ? L.off_sg : (L.off_H + 8 * q * q + 15) / 16 * 16;
+}
+// (unused by the kernel since the level store was replaced by per-warp stacks; kept for the layout helpers)
 __host__ __device__ inline size_t chain_off(int q) {  // doubles before q: 2 * sum_{j<q} j^2
     const size_t x = (size_t)q;
     return 2 * ((x - 1) * x * (2 * x - 1) / 6);
@@ -138,17 +146,25 @@ __host__ __device__ inline size_t chain_ioff(int q) {  // ints before q: 2 * sum
 struct WS {
     double *W;  // current home of H (shared memory while qd <= QS, else the per-warp global buffer)
     int LD;
-    double *Ws, *Wg, *tmpA;
+    double *Ws, *Wg, *tmpA;  // homes of the side being worked on
     int LDS, LDG, QS;
-    double *chat, *val, *w, *a, *v, *r, *c, *cpar, *chatpar, *xc, *gbase;
-    int *zrow, *step;
+    double *chat, *val, *w, *a, *v, *r, *c, *cpar, *chatpar, *brow;
+    int *zrow;
     long long *u;
-    unsigned char *pos, *ord, *flags;  // flags[k]: bit0/1 = chain initialised side 0/1, bit2 = pruned, bit3 = curside
+    unsigned char *pos, *ord;
     signed char *sg;
     const double *Qs;  // Qrev in shared memory, leading dimension LDQ
     int LDQ, n, m, qd, lane;
-    double al[3], be[3];  // alpha/beta of rows lane, lane+32, lane+64
+    double *al, *be;  // alpha_j = n_j . y, beta_j = n_j . H[pe] (shared memory, m each)
     unsigned long long pivots, quick, refactors, colds;
+    // the two sides of the level being expanded, and the parent's vertex
+    double *Ws_a, *Ws_b, *Wg_a, *Wg_b;
+    int *zrow_a, *zrow_b;
+    unsigned char *pos_a, *pos_b;
+    signed char *sg_a, *sg_b;
+    double *Wpar;
+    int *pzrow;
+    signed char *psg;
 };
 
 __device__ __forceinline__ bool approxLE(double a, double b) {  // libblt/util.cc:17-31
@@ -161,6 +177,7 @@ template <class FA, class FB>
 __device__ __forceinline__ double dot4(int len, FA fa, FB fb) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
     int e = 0;
+#pragma unroll 1
     for (; e + 3 < len; e += 4) {
         a0 = fma(fa(e), fb(e), a0);
         a1 = fma(fa(e + 1), fb(e + 1), a1);
@@ -177,6 +194,7 @@ template <class FA, class FB, class FC>
 __device__ __forceinline__ void dot4x2(int len, FA fa, FB fb, FC fc, double &r1, double &r2) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
     int e = 0;
+#pragma unroll 1
     for (; e + 3 < len; e += 4) {
         const double x0 = fa(e), x1 = fa(e + 1), x2 = fa(e + 2), x3 = fa(e + 3);
         a0 = fma(x0, fb(e), a0); b0 = fma(x0, fc(e), b0);
@@ -261,9 +279,6 @@ __device__ int geo_build_warp(const double *B, const double *p, int n, int m, do
 }
 
 // ---- LP engine (twin of the oracle's lp_* functions) -----------------------------------------------------------
-__device__ __forceinline__ void lp_home(WS &s, int q) {  // where an H of size q lives
-    if (q <= s.QS) { s.W = s.Ws; s.LD = s.LDS; } else { s.W = s.Wg; s.LD = s.LDG; }
-}
 __device__ __forceinline__ void lp_values(WS &s) {
     const int qd = s.qd;
     for (int p = s.lane; p < qd; p += 32) {
@@ -282,64 +297,62 @@ __device__ __forceinline__ double lp_alpha_beta(WS &s, int pe) {
     const int qd = s.qd, m = s.m;
     const double *y = s.W, *rho = s.W + (size_t)pe * s.LD;
     double part = 0.0;
-#pragma unroll
-    for (int t = 0; t < 3; ++t) {
-        const int j = s.lane + 32 * t;
-        s.al[t] = 0.0; s.be[t] = 0.0;
-        if (j < m && !s.pos[j]) {
+#pragma unroll 1
+    for (int j = s.lane; j < m; j += 32) {
+        double a = 0.0, b = 0.0;
+        if (!s.pos[j]) {
             const double *nj = s.Qs + (size_t)j * s.LDQ;
-            dot4x2(qd, [&](int e) { return nj[e]; }, [&](int e) { return y[e]; }, [&](int e) { return rho[e]; }, s.al[t], s.be[t]);
-            part += fabs(s.al[t]);
+            dot4x2(qd, [&](int e) { return nj[e]; }, [&](int e) { return y[e]; }, [&](int e) { return rho[e]; }, a, b);
+            part += fabs(a);
         }
+        s.al[j] = a; s.be[j] = b;
     }
     return butterfly(part);
 }
-__device__ int lp_ratio(WS &s, int se, int pe) {
+__device__ __forceinline__ int lp_ratio(WS &s, int se, int pe) {
     const int m = s.m, qd = s.qd;
     const bool artificial = s.zrow[pe] < 0;
     double scale = 0.0;
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) { const double a = fabs(s.W[(size_t)pe * s.LD + c]); scale = a > scale ? a : scale; }
-#pragma unroll
-    for (int t = 0; t < 3; ++t) { const int j = s.lane + 32 * t; if (j < m && !s.pos[j]) { const double a = fabs(s.be[t]); scale = a > scale ? a : scale; } }
+#pragma unroll 1
+    for (int j = s.lane; j < m; j += 32) if (!s.pos[j]) { const double a = fabs(s.be[j]); scale = a > scale ? a : scale; }
     scale = warp_max(scale);
     const double tiny = PIV_TOL * scale, dmin = artificial ? tiny : 0.0;
     double tmax = INFINITY;
-#pragma unroll
-    for (int t = 0; t < 3; ++t) {
-        const int j = s.lane + 32 * t;
-        if (j >= m || s.pos[j]) continue;
-        const double den = -(double)(se * s.sg[j]) * s.be[t];
+#pragma unroll 1
+    for (int j = s.lane; j < m; j += 32) {
+        if (s.pos[j]) continue;
+        const double den = -(double)(se * s.sg[j]) * s.be[j];
         if (!(den > dmin)) continue;
-        double num = (double)s.sg[j] * s.al[t];
+        double num = (double)s.sg[j] * s.al[j];
         if (num < 0.0) num = 0.0;
         const double rt = (num + HARRIS_DELTA) / den;
         if (rt < tmax) tmax = rt;
     }
     tmax = warp_min(tmax);
     int best = -1; double bd = 0.0;
-#pragma unroll
-    for (int t = 0; t < 3; ++t) {
-        const int j = s.lane + 32 * t;
-        if (j >= m || s.pos[j]) continue;
-        const double den = -(double)(se * s.sg[j]) * s.be[t];
+#pragma unroll 1
+    for (int j = s.lane; j < m; j += 32) {
+        if (s.pos[j]) continue;
+        const double den = -(double)(se * s.sg[j]) * s.be[j];
         if (!(den > dmin)) continue;
-        double num = (double)s.sg[j] * s.al[t];
+        double num = (double)s.sg[j] * s.al[j];
         if (num < 0.0) num = 0.0;
         if (num / den <= tmax && den > bd) { bd = den; best = j; }
     }
     warp_argmax(bd, best);
     if (best >= 0 || artificial) return best;
     double ba = -1.0;
-#pragma unroll
-    for (int t = 0; t < 3; ++t) {
-        const int j = s.lane + 32 * t;
-        if (j >= m || s.pos[j] || fabs(s.be[t]) > tiny) continue;
-        if (fabs(s.al[t]) > ba) { ba = fabs(s.al[t]); best = j; }
+#pragma unroll 1
+    for (int j = s.lane; j < m; j += 32) {
+        if (s.pos[j] || fabs(s.be[j]) > tiny) continue;
+        if (fabs(s.al[j]) > ba) { ba = fabs(s.al[j]); best = j; }
     }
     warp_argmax(ba, best);
     return best;
 }
-__device__ int lp_replace(WS &s, int pe, int l, int se) {
+__device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
     const int qd = s.qd, LD = s.LD;
     double *H = s.W, *Hp = s.W + (size_t)pe * LD;
     const int e = s.zrow[pe];
@@ -355,9 +368,17 @@ __device__ int lp_replace(WS &s, int pe, int l, int se) {
     if (wp == 0.0) return -1;
     for (int c = s.lane; c < qd; c += 32) s.v[c] = Hp[c] / wp;
     __syncwarp();
-    for (int x = s.lane; x < qd * qd; x += 32) {
-        const int i = x / qd, c = x - i * qd;
-        if (i != pe) H[(size_t)i * LD + c] = fma(-s.w[i], s.v[c], H[(size_t)i * LD + c]);
+    if (qd <= 32) {  // one lane per column, rows in a loop: same arithmetic, no index division
+        if (s.lane < qd) {
+            const double vc = s.v[s.lane];
+            double *Hc = H + s.lane;
+            for (int i = 0; i < qd; ++i) if (i != pe) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
+        }
+    } else {
+        for (int x = s.lane; x < qd * qd; x += 32) {
+            const int i = x / qd, c = x - i * qd;
+            if (i != pe) H[(size_t)i * LD + c] = fma(-s.w[i], s.v[c], H[(size_t)i * LD + c]);
+        }
     }
     __syncwarp();
     const double sl = (double)s.sg[l];
@@ -371,9 +392,8 @@ __device__ int lp_replace(WS &s, int pe, int l, int se) {
     s.pivots++;
     return 0;
 }
-__device__ int lp_init1(WS &s) {
+__device__ __forceinline__ int lp_init1(WS &s) {
     const int m = s.m;
-    lp_home(s, 1);
     double part = 0.0;
     for (int j = s.lane; j < m; j += 32) {
         const double x = s.Qs[(size_t)j * s.LDQ];
@@ -387,17 +407,8 @@ __device__ int lp_init1(WS &s) {
     __syncwarp();
     return 0;
 }
-// moves H to the home of a basis of size q_home if it is not there already
-__device__ __forceinline__ void lp_rehome(WS &s, int q_home) {
-    double *oldW = s.W; const int oldLD = s.LD, q = s.qd;
-    lp_home(s, q_home);
-    if (s.W == oldW) return;
-    for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * s.LD + c] = oldW[(size_t)i * oldLD + c]; }
-    __syncwarp();
-}
 // one more coordinate (index qd): border H with an artificial basic column at position qd
-__device__ void lp_extend(WS &s) {
-    lp_rehome(s, s.qd + 1);
+__device__ __forceinline__ void lp_extend(WS &s) {
     const int m = s.m, qd = s.qd, LD = s.LD;
     double part = 0.0;
     for (int j = s.lane; j < m; j += 32) if (!s.pos[j]) part = fma((double)s.sg[j], s.Qs[(size_t)j * s.LDQ + qd], part);
@@ -414,25 +425,26 @@ __device__ void lp_extend(WS &s) {
     s.qd = qd + 1;
     __syncwarp();
 }
-__device__ int lp_drop_artificial(WS &s, int sf) {
+// cold builds only (root solve, test seam): pivot the artificial at the last position out
+__device__ __forceinline__ int lp_drop_artificial(WS &s, int sf) {
     const int pe = s.qd - 1;
     lp_alpha_beta(s, pe);
     const int l = lp_ratio(s, sf, pe);
     if (l < 0) return -1;
     return lp_replace(s, pe, l, sf);
 }
-// rare path: rebuild H = A^-1 from Z and the signs by Gauss-Jordan with row pivoting, one lane, the oracle's loops
-__device__ int lp_refactor(WS &s) {
-    const int qd = s.qd, LD = s.LD, m = s.m;
+// rare path: rebuild H = A^-1 from Z and the signs by Gauss-Jordan with row pivoting, one lane, the oracle's loops.
+// Takes plain pointers so that the caller's state can stay in registers.
+__device__ __noinline__ int lp_refactor_impl(double *H, int LD, double *A, const double *Qs, int LDQ, int qd, int m,
+                                             const unsigned char *pos, const signed char *sg, const int *zrow, int lane) {
     int rc = 0;
     __syncwarp();
-    if (s.lane == 0) {
-        double *A = s.tmpA, *H = s.W;
+    if (lane == 0) {
         for (int c = 0; c < qd; ++c) {
             double sum = 0.0;
-            for (int j = 0; j < m; ++j) if (!s.pos[j]) sum = fma((double)s.sg[j], s.Qs[(size_t)j * s.LDQ + c], sum);
+            for (int j = 0; j < m; ++j) if (!pos[j]) sum = fma((double)sg[j], Qs[(size_t)j * LDQ + c], sum);
             A[(size_t)c * qd] = sum;
-            for (int p = 1; p < qd; ++p) A[(size_t)c * qd + p] = s.zrow[p] >= 0 ? s.Qs[(size_t)s.zrow[p] * s.LDQ + c] : (c == p ? 1.0 : 0.0);
+            for (int p = 1; p < qd; ++p) A[(size_t)c * qd + p] = zrow[p] >= 0 ? Qs[(size_t)zrow[p] * LDQ + c] : (c == p ? 1.0 : 0.0);
         }
         for (int i = 0; i < qd; ++i) for (int c = 0; c < qd; ++c) H[(size_t)i * LD + c] = (i == c) ? 1.0 : 0.0;
         for (int col = 0; col < qd; ++col) {
@@ -460,8 +472,11 @@ __device__ int lp_refactor(WS &s) {
     }
     rc = __shfl_sync(FULLMASK, rc, 0);
     __syncwarp();
-    s.refactors++;
     return rc;
+}
+__device__ __forceinline__ int lp_refactor(WS &s) {
+    s.refactors++;
+    return lp_refactor_impl(s.W, s.LD, s.tmpA, s.Qs, s.LDQ, s.qd, s.m, s.pos, s.sg, s.zrow, s.lane);
 }
 __device__ __forceinline__ void lp_image(WS &s, int nv) {
     const int m = s.m;
@@ -475,49 +490,64 @@ __device__ __forceinline__ void lp_image(WS &s, int nv) {
     }
     __syncwarp();
 }
-// solve from the current dual-feasible vertex; radius = +inf disables pruning; on NODE_EXPLORE v[qd] is valid if qd < m
-__device__ int lp_solve(WS &s, double radius, double cmax, double &d_out) {
+// Solve from the current dual-feasible vertex; radius = +inf disables pruning; on NODE_EXPLORE v[qd] is valid if
+// qd < m.  art != 0: the basis still holds the artificial column of a fresh coordinate at position qd-1; it is pivoted
+// out first with sign `art` (the oracle's lp_drop_artificial followed by lp_solve; merged so that the pivot code
+// exists once in the instruction stream).
+__device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, double &d_out, int art) {
     const int qd = s.qd, m = s.m;
-    lp_values(s);
-    if (s.val[0] < 0.0) lp_flip(s);
+    if (!art) {
+        lp_values(s);
+        if (s.val[0] < 0.0) lp_flip(s);
+    }
     const int cap = 100 * m + 1000;
     bool refactored = false;
-    for (int iter = 0;; ++iter) {
-        const double t = s.val[0];
-        if (!approxLE(t, radius)) { if (iter == 0) s.quick++; return NODE_PRUNE; }
-        int pe = -1; double vmax = -1.0;
-        for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
-        warp_argmax(vmax, pe);
-        const double tol = EPS_OPT * (cmax + t);
-        if (pe < 0 || vmax <= t + tol) {
-            const int nv = qd < m ? qd + 1 : qd;
-            lp_image(s, nv);
-            double err = 0.0;
-            for (int i = s.lane; i < qd; i += 32) { const double e = fabs(s.v[i] - s.chat[i]); err = e > err ? e : err; }
-            err = warp_max(err);
-            if (err <= 1.0e-8 * ((double)m * cmax + t)) { d_out = t; return NODE_EXPLORE; }
-            if (refactored) return NODE_FAIL;
-            refactored = true;
-            if (lp_refactor(s)) return NODE_FAIL;
-            lp_values(s);
-            if (s.val[0] < 0.0) lp_flip(s);
-            continue;
+    int iter = 0;
+#pragma unroll 1
+    for (;;) {
+        int pe, se;
+        if (art) { pe = qd - 1; se = art; }
+        else {
+            const double t = s.val[0];
+            if (!approxLE(t, radius)) { if (iter == 0) s.quick++; return NODE_PRUNE; }
+            pe = -1; double vmax = -1.0;
+            for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
+            warp_argmax(vmax, pe);
+            const double tol = EPS_OPT * (cmax + t);
+            if (pe < 0 || vmax <= t + tol) {
+                const int nv = qd < m ? qd + 1 : qd;
+                lp_image(s, nv);
+                double err = 0.0;
+                for (int i = s.lane; i < qd; i += 32) { const double e = fabs(s.v[i] - s.chat[i]); err = e > err ? e : err; }
+                err = warp_max(err);
+                if (err <= 1.0e-8 * ((double)m * cmax + t)) { d_out = t; return NODE_EXPLORE; }
+                if (refactored) return NODE_FAIL;
+                refactored = true;
+                if (lp_refactor(s)) return NODE_FAIL;
+                lp_values(s);
+                if (s.val[0] < 0.0) lp_flip(s);
+                ++iter;
+                continue;
+            }
+            if (iter >= cap) return NODE_FAIL;
+            se = s.val[pe] > 0.0 ? 1 : -1;
         }
-        if (iter >= cap) return NODE_FAIL;
-        const int se = s.val[pe] > 0.0 ? 1 : -1;
         const double nrm1 = lp_alpha_beta(s, pe);
-        if (fabs(nrm1 - 1.0) > 1.0e-6) {
+        if (!art && fabs(nrm1 - 1.0) > 1.0e-6) {
             if (refactored) return NODE_FAIL;
             refactored = true;
             if (lp_refactor(s)) return NODE_FAIL;
             lp_values(s);
             if (s.val[0] < 0.0) lp_flip(s);
+            ++iter;
             continue;
         }
         const int l = lp_ratio(s, se, pe);
         if (l < 0) return NODE_FAIL;
         if (lp_replace(s, pe, l, se)) return NODE_FAIL;
         lp_values(s);
+        if (art) { art = 0; if (s.val[0] < 0.0) lp_flip(s); }
+        else ++iter;
     }
 }
 
@@ -531,9 +561,8 @@ __device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, si
     for (int p = s.lane; p < q; p += 32) dI[p] = s.zrow[p];
     for (int j = s.lane; j < s.m; j += 32) dB[j] = s.sg[j];
 }
-// loads a q x q head into the home of a basis of size q_home (q_home >= q: the caller may be about to extend it)
-__device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *dI, const signed char *dB, int q, int q_home) {
-    lp_home(s, q_home);
+// loads a q x q head into the working matrix
+__device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *dI, const signed char *dB, int q) {
     const int LD = s.LD;
     s.qd = q;
     for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
@@ -597,82 +626,94 @@ __device__ bool check_soln_dev(const Params &P, const long long *u, int lane) {
 }
 
 // ------------------------------------------------------------------------------------------------------------
-// One subtree
+// One task = the sibling loop below one explored node
 // ------------------------------------------------------------------------------------------------------------
 struct Counters { unsigned long long niter, nprune, nodes, donated; };
+
+// per-warp private stack of pending records (global memory): [abot, acount) entries of the offset table are live
+struct Arena {
+    unsigned char *base;
+    int *offs;       // offs[i] = byte offset of entry i; offs[acount] = top of the stack
+    int acount, abot;
+    size_t cap;
+    int slots;
+};
 
 __device__ __forceinline__ void fail_search(const Params &P, int lane, int status) {
     if (lane == 0) { P.q->status = status; P.q->abort = 1; }
 }
+// BIG = the basis of this task is larger than the shared-memory matrices: H lives in the per-warp global buffers.
+// The choice is a template parameter so that in the common case every access to H compiles to LDS/STS.
+template <bool BIG>
+__device__ __forceinline__ void use_side(WS &s, int side) {
+    if (BIG) { s.W = side ? s.Wg_b : s.Wg_a; s.LD = s.LDG; } else { s.W = side ? s.Ws_b : s.Ws_a; s.LD = s.LDS; }
+    s.zrow = side ? s.zrow_b : s.zrow_a; s.pos = side ? s.pos_b : s.pos_a; s.sg = side ? s.sg_b : s.sg_a;
+}
+__device__ __forceinline__ void copy_words(void *dst, const void *src, size_t bytes, int lane) {  // bytes % 8 == 0
+    unsigned long long *d = (unsigned long long *)dst;
+    const unsigned long long *s = (const unsigned long long *)src;
+    for (size_t i = lane; i < bytes / 8; i += 32) d[i] = s[i];
+}
+// writes the record of an explored child (children level k-1) whose vertex is the current working state
+__device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL, WS &s, unsigned char *C, int k, double xlast,
+                                            double gn) {
+    const int n = P.n, m = P.m, lane = s.lane, qd = s.qd;
+    if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gn; }
+    for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
+    for (int j = lane; j < m; j += 32) ((double *)(C + RL.off_cpar))[j] = s.c[j];
+    for (int e = lane; e < qd; e += 32) ((double *)(C + RL.off_chat))[e] = s.chat[e];
+    if (k - 1 > 1) chain_store(s, (double *)(C + RL.off_H), (int *)(C + RL.off_zrow), (signed char *)(C + RL.off_sg));
+    __syncwarp();
+}
 
-__device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &cnt, unsigned int *hist) {
+// Expands record R.  Returns the number of children left for this warp in `next` (0 or 1); others went to the arena,
+// the queue or the static-split output.
+template <bool BIG>
+__device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
+                      int gwarp, Counters &cnt, unsigned int *hist) {
     const int n = P.n, m = P.m, lane = s.lane;
     const RecLayout RL = rec_layout(n, m);
-    unsigned char *R = P.pool + (size_t)rec * RL.stride;
-    const int k0 = ((int *)R)[0];
-    const int rflags = ((int *)R)[1];
-    double xc0 = ((double *)R)[1];
-    const double gb0 = ((double *)R)[2];
-    const bool is_root = (rflags & REC_ROOT) != 0;
-    double *scrD = P.scrD + (size_t)gwarp * P.scrD_stride;
-    int *scrI = P.scrI + (size_t)gwarp * P.scrI_stride;
-    signed char *scrB = P.scrB + (size_t)gwarp * P.scrB_stride;
-    double *cparL = scrD + chain_off(m + 1);                 // (n+2) x m
-    double *chatL = cparL + (size_t)(n + 2) * m;             // (n+2) x (m+1)
-    auto chainH = [&](int q, int side) { return scrD + chain_off(q) + (size_t)side * q * q; };
-    auto chainI = [&](int q, int side) { return scrI + chain_ioff(q) + (size_t)side * q; };
-    auto chainB = [&](int q, int side) { return scrB + ((size_t)q * 2 + side) * m; };
+    const int k0 = ((const int *)R)[0];
+    const int rflags = ((const int *)R)[1];
+    double xc0 = ((const double *)R)[1];
+    double gb = ((const double *)R)[2];
+    const bool is_top = (rflags & REC_TOP) != 0;
+    const int kk = k0 - 1, qd0 = m - kk, qpar = m - k0;
 
-    // ---- load the record ----
-    for (int e = lane; e < n; e += 32) { s.u[e] = ((long long *)(R + RL.off_u))[e]; s.ord[e] = (R + RL.off_ord)[e]; s.flags[e + 1] = 0; }
-    for (int j = lane; j < m; j += 32) { const double v = ((double *)(R + RL.off_cpar))[j]; s.cpar[j] = v; cparL[(size_t)k0 * m + j] = v; }
-    const int qpar = m - k0;  // basis size of the explored node this subtree hangs under (0: nothing to start from)
-    int wq = -1, wside = -1;  // which chain head the working matrix currently equals
-    if (!is_root && qpar > 0) {
-        chain_load(s, (const double *)(R + RL.off_H), (const int *)(R + RL.off_zrow), (const signed char *)(R + RL.off_sg), qpar, qpar + 1);
-        chain_store(s, chainH(qpar, 0), chainI(qpar, 0), chainB(qpar, 0));
-        for (int e = lane; e < qpar; e += 32) { const double v = ((double *)(R + RL.off_chat))[e]; s.chatpar[e] = v; chatL[(size_t)k0 * (m + 1) + e] = v; }
-        wq = qpar; wside = 0;
+    // ---- take what is needed out of the record; afterwards the record is dead ----
+    for (int e = lane; e < n; e += 32) { s.u[e] = ((const long long *)(R + RL.off_u))[e]; s.ord[e] = (R + RL.off_ord)[e]; }
+    for (int j = lane; j < m; j += 32) s.cpar[j] = ((const double *)(R + RL.off_cpar))[j];
+    if (qpar > 0 && k0 > 1) {
+        copy_words(s.Wpar, R + RL.off_H, (size_t)qpar * qpar * 8, lane);
+        for (int p = lane; p < qpar; p += 32) s.pzrow[p] = ((const int *)(R + RL.off_zrow))[p];
+        for (int j = lane; j < m; j += 32) s.psg[j] = ((const signed char *)(R + RL.off_sg))[j];
+        for (int e = lane; e < qpar; e += 32) s.chat[e] = ((const double *)(R + RL.off_chat))[e];
     }
     __syncwarp();
-    __threadfence();
-    if (lane == 0) ring_push(P.q, &P.q->ftail, P.fring, P.ring_mask, rec);  // the record slot is free again
+    if (pool_slot >= 0) {
+        __threadfence();
+        if (lane == 0) ring_push(P.q, &P.q->ftail, P.fring, P.ring_mask, pool_slot);  // the record slot is free again
+    }
 
-    double d = 0.0, xlast = 0.0, gb = gb0;
-    if (is_root) {  // initial solve LP(n), closest.cc:206
-        double cm = 0.0;
-        for (int j = lane; j < m; j += 32) { const double a = fabs(s.cpar[j]); cm = a > cm ? a : cm; }
-        cm = warp_max(cm);
-        cnt.nodes++; if (lane == 0) hist[n]++;
-        double vq = 0.0;
-        if (qpar > 0) {
-            for (int i = lane; i < qpar; i += 32) s.chat[i] = P.QTp[m - 1 - i];
-            __syncwarp();
-            int bad = lp_init1(s);
-            for (int i = 1; i < qpar && !bad; ++i) {
-                lp_extend(s);
-                lp_values(s);
-                bad = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
-            }
-            if (bad || lp_solve(s, INFINITY, cm, d) != NODE_EXPLORE) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
-            vq = s.v[qpar];
-            chain_store(s, chainH(qpar, 0), chainI(qpar, 0), chainB(qpar, 0));
-            for (int e = lane; e < qpar; e += 32) { const double v = s.chat[e]; s.chatpar[e] = v; chatL[(size_t)k0 * (m + 1) + e] = v; }
-            wq = qpar; wside = 0;
-        }
-        gb = P.QTp[n - 1];
-        xlast = (gb - vq) / P.Rm[(size_t)(n - 1) * n + (n - 1)];
-        xc0 = xlast;
-        __syncwarp();
+    double d = 0.0, xlast = 0.0;
+    // ---- constants of this level ----
+    for (int j = lane; j < m; j += 32) s.brow[j] = P.B[(size_t)kk * m + j];
+    const double Rkk = P.Rm[(size_t)kk * n + kk];
+    double Rk1 = 1.0, Rk1k = 0.0, g2 = 0.0;
+    if (kk >= 1) {
+        const double *Rr = P.Rm + (size_t)(kk - 1) * n;
+        Rk1 = Rr[kk - 1]; Rk1k = Rr[kk];
+        double part = 0.0;
+        for (int i = kk + 1 + lane; i < n; i += 32) part = fma(-(double)s.u[i], Rr[i], part);
+        g2 = P.QTp[kk - 1] + butterfly(part);
     }
-    int k = k0;
-    if (lane == 0) {
-        const long long un = (long long)round(xc0);
-        s.u[k - 1] = un; s.step[k - 1] = sgn_d(xc0 - (double)un); s.xc[k] = xc0; s.gbase[k] = gb; s.ord[k - 1] = 0; s.flags[k] = 0;
-    }
+    long long ucur = (long long)round(xc0);
+    int step = sgn_d(xc0 - (double)ucur);
+    bool pruned = false;
+    int inited = 0, nkept = 0;
+    if (lane == 0) { s.u[kk] = ucur; s.ord[kk] = 0; }
     __syncwarp();
-    const int depth0 = n - k0;
-    const bool forced = depth0 < P.static_depth;  // static split: emit every explored child of this record
+    const bool forced = (n - k0) < P.static_depth;  // static split: every explored child of this record is published
     unsigned int wd = 0;
 
     for (;;) {
@@ -680,151 +721,93 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
             int ab = 0;
             if (lane == 0) {
                 ab = *(volatile int *)&P.q->abort;
-                if (!ab && (++wd & 255u) == 0) ab = overdue(P.q, 1) ? 1 : 0;
+                if (!ab && (++wd & 63u) == 0) ab = overdue(P.q, 1) ? 1 : 0;
             }
-            if (__shfl_sync(FULLMASK, ab, 0)) return;
+            if (__shfl_sync(FULLMASK, ab, 0)) return nkept;
         }
-        // c = cpar - u[k-1] * B[k-1]
+        // c = cpar - u * B[kk]
         double cmax = 0.0;
         {
-            const double mu = -(double)s.u[k - 1];
-            const double *Bk = P.B + (size_t)(k - 1) * m;
-            for (int j = lane; j < m; j += 32) { const double cj = fma(mu, Bk[j], s.cpar[j]); s.c[j] = cj; const double a = fabs(cj); cmax = a > cmax ? a : cmax; }
+            const double mu = -(double)ucur;
+            for (int j = lane; j < m; j += 32) { const double cj = fma(mu, s.brow[j], s.cpar[j]); s.c[j] = cj; const double a = fabs(cj); cmax = a > cmax ? a : cmax; }
             cmax = warp_max(cmax);
             __syncwarp();
         }
-        cnt.nodes++; if (lane == 0) hist[k - 1]++;
-        int status, side = 0;
-        const bool leaving_prune = (s.flags[k] & 4) != 0;
-        double gnext = 0.0;
-        if (k == 1) {
+        cnt.nodes++; if (lane == 0) hist[kk]++;
+        int status;
+        double gn = 0.0;
+        if (k0 == 1) {
             d = cmax;
             status = approxLE(d, P.radius) ? NODE_EXPLORE : NODE_PRUNE;
         } else {
-            const int kk = k - 1, qd = m - kk;
-            const int dir = sgn_d(s.xc[k] - (double)s.u[k - 1]);
-            side = dir > 0 ? 0 : 1;
-            const double clast = fma(-(double)s.u[k - 1], P.Rm[(size_t)kk * n + kk], s.gbase[k]);
-            const bool inited = (s.flags[k] >> side) & 1;
-            if (!inited) {
-                if (qd == 1) {
-                    if (lp_init1(s)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
+            const int dir = sgn_d(xc0 - (double)ucur);
+            const int side = dir > 0 ? 0 : 1;
+            use_side<BIG>(s, side);
+            const double clast = fma(-(double)ucur, Rkk, gb);
+            int art = 0;
+            if (!((inited >> side) & 1)) {
+                if (qd0 == 1) {
+                    if (lp_init1(s)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return nkept; }
                 } else {
-                    const int ps = (k == k0) ? 0 : ((s.flags[k + 1] >> 3) & 1);
-                    if (!(wq == qd - 1 && wside == ps)) chain_load(s, chainH(qd - 1, ps), chainI(qd - 1, ps), chainB(qd - 1, ps), qd - 1, qd);
+                    chain_load(s, s.Wpar, s.pzrow, s.psg, qpar);
                     lp_extend(s);
                 }
-                for (int e = lane; e < qd - 1; e += 32) s.chat[e] = s.chatpar[e];
-                if (lane == 0) { s.chat[qd - 1] = clast; s.flags[k] |= (unsigned char)(1 << side); }
+                inited |= 1 << side;
+                if (qd0 > 1) art = dir;
+                if (lane == 0) s.chat[qd0 - 1] = clast;
                 __syncwarp();
-                if (qd > 1 && lp_drop_artificial(s, dir)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
             } else {
-                if (!(wq == qd && wside == side)) chain_load(s, chainH(qd, side), chainI(qd, side), chainB(qd, side), qd, qd);
-                for (int e = lane; e < qd - 1; e += 32) s.chat[e] = s.chatpar[e];
-                if (lane == 0) s.chat[qd - 1] = clast;
+                s.qd = qd0;
+                if (lane == 0) s.chat[qd0 - 1] = clast;
                 __syncwarp();
             }
-            status = lp_solve(s, P.radius, cmax, d);
-            if (status == NODE_FAIL) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return; }
-            wq = qd; wside = side;
-            // keep the chain head unless this is the prune that leaves the level
-            if (!(status == NODE_PRUNE && (leaving_prune || (is_root && k == k0)))) {
-                chain_store(s, chainH(qd, side), chainI(qd, side), chainB(qd, side));
-                __syncwarp();
-            }
+            status = lp_solve(s, P.radius, cmax, d, art);
+            if (status == NODE_FAIL) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return nkept; }
             if (status == NODE_EXPLORE) {  // real centre of the next level: x_{kk-1} of the optimum
-                double gn = 0.0;
-                if (lane == 0) {
-                    gn = P.QTp[kk - 1];
-                    const double *Rr = P.Rm + (size_t)(kk - 1) * n;
-                    for (int i = kk; i < n; ++i) gn = fma(-(double)s.u[i], Rr[i], gn);
-                }
-                gnext = __shfl_sync(FULLMASK, gn, 0);
-                xlast = (gnext - s.v[qd]) / P.Rm[(size_t)(kk - 1) * n + (kk - 1)];
+                gn = fma(-(double)ucur, Rk1k, g2);
+                xlast = (gn - s.v[qd0]) / Rk1;
             }
         }
         if (status == NODE_PRUNE) {
-            if (is_root && k == k0) return;  // closest.cc:280-286: first prune at the top level ends the search
+            if (is_top) return nkept;  // closest.cc:280-286: first prune at the top level ends the search
             cnt.nprune++;
-            if (s.flags[k] & 4) {  // second prune at this level: leave it
-                if (k == k0) return;
-                k++;
-                const int qp = m - k;  // entries of the parent right-hand side in complement coordinates
-                for (int j = lane; j < m; j += 32) s.cpar[j] = cparL[(size_t)k * m + j];
-                for (int e = lane; e < qp; e += 32) s.chatpar[e] = chatL[(size_t)k * (m + 1) + e];
-            } else if (lane == 0) s.flags[k] |= 4;
-            __syncwarp();
-            if (lane == 0) {
-                const int st = s.step[k - 1];
-                s.u[k - 1] += st; s.step[k - 1] = -st - (st > 0 ? 1 : -1);
-                if (s.ord[k - 1] < 255) s.ord[k - 1]++;
-            }
-            __syncwarp();
-            continue;
-        }
-        // explore
-        if (k > 1) {
-            const int qd = m - k + 1;
-            // hand the child to the queue instead of descending?
-            bool emit = false;
-            int slot = -1;
-            if (forced && k == k0) emit = true;
-            else if (P.dynamic && (k - 1) >= P.donate_min_level && s.ord[k - 1] > 0) {  // keep the first (nearest) child
-                int want = 0;
-                if (lane == 0) {
-                    const int idle = *(volatile int *)&P.q->idle;
-                    const int qlen = (int)(*(volatile unsigned int *)&P.q->tail - *(volatile unsigned int *)&P.q->head);
-                    want = (idle > 0 && qlen < idle + P.lowwater) ? 1 : 0;
-                }
-                emit = __shfl_sync(FULLMASK, want, 0) != 0;
-            }
-            if (emit) {
+            if (pruned) return nkept;  // second prune: the level is left
+            pruned = true;
+        } else if (k0 > 1) {
+            // explored inner node: its children are one more task
+            cnt.niter++;
+            unsigned char *C = nullptr;
+            int slot = -1, dest = 0;  // dest: 0 next, 1 arena, 2 queue, 3 static-split output
+            const size_t need = rec_bytes(RL, m, k0 - 1);
+            if (forced) {
                 if (lane == 0) slot = ring_pop(P.q, &P.q->fhead, &P.q->ftail, P.fring, P.ring_mask);
                 slot = __shfl_sync(FULLMASK, slot, 0);
-                if (slot < 0) {
-                    if (forced && k == k0) { fail_search(P, lane, BLTCU_STATUS_ERROR); return; }
-                    emit = false;
+                if (slot < 0) { fail_search(P, lane, BLTCU_STATUS_ERROR); return nkept; }
+                C = P.pool + (size_t)slot * RL.stride;
+                dest = ((n - (k0 - 1)) >= P.static_depth) ? 3 : 2;
+            } else if (nkept == 0) { C = next; dest = 0; }
+            else {
+                const size_t top = (size_t)A.offs[A.acount];
+                if (A.acount + 1 < A.slots && top + need <= A.cap) { C = A.base + top; dest = 1; }
+                else {  // private stack full: publish instead
+                    if (lane == 0) slot = ring_pop(P.q, &P.q->fhead, &P.q->ftail, P.fring, P.ring_mask);
+                    slot = __shfl_sync(FULLMASK, slot, 0);
+                    if (slot < 0) { fail_search(P, lane, BLTCU_STATUS_ERROR); return nkept; }
+                    C = P.pool + (size_t)slot * RL.stride;
+                    dest = 2;
                 }
             }
-            if (emit) {
-                unsigned char *C = P.pool + (size_t)slot * RL.stride;
-                if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gnext; }
-                for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
-                for (int j = lane; j < m; j += 32) ((double *)(C + RL.off_cpar))[j] = s.c[j];
-                for (int e = lane; e < qd; e += 32) ((double *)(C + RL.off_chat))[e] = s.chat[e];
-                chain_store(s, (double *)(C + RL.off_H), (int *)(C + RL.off_zrow), (signed char *)(C + RL.off_sg));
-                __syncwarp();
+            write_child(P, RL, s, C, k0, xlast, gn);
+            if (dest == 0) nkept = 1;
+            else if (dest == 1) { if (lane == 0) A.offs[A.acount + 1] = (int)(A.offs[A.acount] + need); A.acount++; __syncwarp(); }
+            else {
                 __threadfence();
                 if (lane == 0) {
-                    if (forced && (n - (k - 1)) >= P.static_depth) {
-                        const unsigned int o = atomicAdd(&P.q->out_count, 1u);
-                        P.out_list[o] = slot;
-                    } else {
-                        atomicAdd(&P.q->pending, 1);
-                        ring_push(P.q, &P.q->tail, P.ring, P.ring_mask, slot);
-                    }
-                    // continue with the next sibling as if the subtree had returned
-                    const int st = s.step[k - 1];
-                    s.u[k - 1] += st; s.step[k - 1] = -st - (st > 0 ? 1 : -1);
-                    if (s.ord[k - 1] < 255) s.ord[k - 1]++;
+                    if (dest == 3) { const unsigned int o = atomicAdd(&P.q->out_count, 1u); P.out_list[o] = slot; }
+                    else { atomicAdd(&P.q->pending, 1); ring_push(P.q, &P.q->tail, P.ring, P.ring_mask, slot); }
                 }
                 cnt.donated++;
-                cnt.niter++;
-                __syncwarp();
-                continue;
             }
-            // descend, closest.cc:88-95
-            for (int j = lane; j < m; j += 32) { const double v = s.c[j]; cparL[(size_t)(k - 1) * m + j] = v; s.cpar[j] = v; }
-            for (int e = lane; e < qd; e += 32) { const double v = s.chat[e]; chatL[(size_t)(k - 1) * (m + 1) + e] = v; s.chatpar[e] = v; }
-            if (lane == 0) {
-                s.flags[k] = (unsigned char)((s.flags[k] & ~8) | (side << 3));
-                s.xc[k - 1] = xlast; s.gbase[k - 1] = gnext;
-                const long long un = (long long)round(xlast);
-                s.u[k - 2] = un; s.step[k - 2] = sgn_d(xlast - (double)un);
-                s.flags[k - 1] = 0; s.ord[k - 2] = 0;
-            }
-            k--;
-            __syncwarp();
         } else {
             // leaf: record, closest.cc:300-312
             {
@@ -853,53 +836,61 @@ __device__ void run_task(const Params &P, WS &s, int rec, int gwarp, Counters &c
                     for (int e = lane; e < n; e += 32) P.sol[e] = s.u[e];
                     __threadfence();
                 }
-                if (!P.no_early_exit) { if (lane == 0) P.q->abort = 1; return; }
+                if (!P.no_early_exit) { if (lane == 0) P.q->abort = 1; return nkept; }
             }
-            if (n == 1) return;  // D4 of oracle/blt_oracle.c
-            // explore(), closest.cc:99-104
-            k = 2;
-            for (int j = lane; j < m; j += 32) s.cpar[j] = cparL[(size_t)2 * m + j];
-            for (int e = lane; e < m - 2; e += 32) s.chatpar[e] = chatL[(size_t)2 * (m + 1) + e];
-            if (lane == 0) {
-                const int st = s.step[1];
-                s.u[1] += st; s.step[1] = -st - (st > 0 ? 1 : -1);
-                if (s.ord[1] < 255) s.ord[1]++;
-            }
-            __syncwarp();
+            if (n == 1) return nkept;  // D4 of oracle/blt_oracle.c
+            // explore(), closest.cc:99-104: the leaf level is abandoned and the parent level moves on (its loop has
+            // already run here), so this task simply ends
+            cnt.niter++;
+            return nkept;
         }
-        cnt.niter++;
+        // next sibling, closest.cc:118-121
+        ucur += step; step = -step - (step > 0 ? 1 : -1);
+        if (lane == 0) { s.u[kk] = ucur; if (s.ord[kk] < 255) s.ord[kk]++; }
+        __syncwarp();
     }
 }
 
-// carves the per-warp shared-memory block
+__device__ __forceinline__ int expand(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
+                                      int gwarp, Counters &cnt, unsigned int *hist) {
+    const int k0 = ((const int *)R)[0];
+    if (P.m - k0 + 1 <= P.QS) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
+    return expand_impl<true>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
+}
+
+// carves the per-warp shared-memory block; returns the node histogram
 __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, int m, int QS, int LDS) {
     const int M1 = m + 1;
-    s.Ws = base; base += (size_t)QS * LDS;
+    s.Ws_a = base; base += (size_t)QS * LDS;
+    s.Ws_b = base; base += (size_t)QS * LDS;
     s.chat = base; base += M1; s.val = base; base += M1; s.w = base; base += M1; s.a = base; base += M1; s.v = base; base += M1;
-    s.chatpar = base; base += M1;
-    s.r = base; base += m; s.c = base; base += m; s.cpar = base; base += m;
-    s.xc = base; base += n + 2; s.gbase = base; base += n + 2;
+    s.r = base; base += m; s.c = base; base += m; s.cpar = base; base += m; s.brow = base; base += m;
+    s.al = base; base += m; s.be = base; base += m;
     s.u = (long long *)base; base += n;
     int *ib = (int *)base;
-    s.zrow = ib; ib += M1; s.step = ib; ib += n + 1;
+    s.zrow_a = ib; ib += M1; s.zrow_b = ib; ib += M1; s.pzrow = ib; ib += M1;
     unsigned int *hist = (unsigned int *)ib; ib += n + 1;
     unsigned char *bb = (unsigned char *)ib;
     const int nb = ((n > m ? n : m) + 8) / 8 * 8;
-    s.pos = bb; bb += nb; s.sg = (signed char *)bb; bb += nb; s.ord = bb; bb += nb; s.flags = bb;
+    s.pos_a = bb; bb += nb; s.pos_b = bb; bb += nb;
+    s.sg_a = (signed char *)bb; bb += nb; s.sg_b = (signed char *)bb; bb += nb;
+    s.psg = (signed char *)bb; bb += nb;
+    s.ord = bb;
+    s.chatpar = nullptr;
     return hist;
 }
 __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS) {
     const size_t M1 = (size_t)m + 1;
-    const size_t d = (size_t)QS * LDS + 6 * M1 + 3 * (size_t)m + 2 * (size_t)(n + 2) + n;
-    const size_t i = M1 + 2 * (size_t)(n + 1);
+    const size_t d = 2 * (size_t)QS * LDS + 5 * M1 + 6 * (size_t)m + n;
+    const size_t i = 3 * M1 + (size_t)(n + 1);
     const size_t nb = (size_t)((n > m ? n : m) + 8) / 8 * 8;
-    return (d * 8 + i * 4 + 4 * nb + 15) / 16 * 16;
+    return (d * 8 + i * 4 + 6 * nb + 15) / 16 * 16;
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // The persistent kernel
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(512, 1) bltcu_search_kernel(const Params P) {
+__global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
     extern __shared__ __align__(16) double smem[];
     const int n = P.n, m = P.m;
     double *Qs = smem;
@@ -910,47 +901,112 @@ __global__ void __launch_bounds__(512, 1) bltcu_search_kernel(const Params P) {
     __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int gwarp = blockIdx.x * P.warps_per_cta + warp;
+    const RecLayout RL = rec_layout(n, m);
     WS s;
     unsigned int *hist = carve_warp(s, smem + (size_t)m * P.LDQ + (size_t)warp * P.warp_smem_doubles, n, m, P.QS, P.LDS);
-    s.Wg = P.bigW + (size_t)gwarp * P.bigW_stride; s.tmpA = s.Wg + (size_t)m * P.LDG;
-    s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS; s.W = s.Ws; s.LD = s.LDS;
+    {
+        double *wb = P.wbuf + (size_t)gwarp * P.wbuf_stride;
+        s.Wpar = wb; wb += (size_t)m * m;
+        s.Wg_a = wb; wb += (size_t)m * P.LDG;
+        s.Wg_b = wb; wb += (size_t)m * P.LDG;
+        s.tmpA = wb;
+    }
+    s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
     s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0;
+    use_side<false>(s, 0);
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
+    Arena A;
+    A.base = P.arena + (size_t)gwarp * P.arena_stride;
+    A.offs = (int *)(A.base + P.arena_bytes);
+    A.cap = P.arena_bytes; A.slots = P.arena_slots; A.acount = 0; A.abot = 0;
+    if (lane == 0) A.offs[0] = 0;
     __syncwarp();
+    unsigned char *nextbuf = P.nextrec + (size_t)gwarp * 2 * RL.stride;
+    int nextsel = 0, have_next = 0;
     Counters cnt = {0, 0, 0, 0};
     QCtl *q = P.q;
-    bool am_idle = false;
+    bool am_idle = false, have_token = false;
+    unsigned long long t_idle = 0, t_busy = 0, t_mark = gtimer();
     for (;;) {
-        int rec = -1, stop = 0;
-        if (lane == 0) {
-            if (*(volatile int *)&q->abort) stop = 1;
-            else {
-                rec = ring_pop(q, &q->head, &q->tail, P.ring, P.ring_mask);
-                if (rec < 0) {
-                    if (*(volatile int *)&q->pending == 0) stop = 1;
-                    else {
-                        if (!am_idle) { atomicAdd(&q->idle, 1); am_idle = true; }
-                        __nanosleep(200);
-                        if (overdue(q, 2)) stop = 1;
-                    }
-                } else if (am_idle) { atomicSub(&q->idle, 1); am_idle = false; }
+        const unsigned char *R = nullptr;
+        int slot = -1;
+        if (have_next) {
+            R = nextbuf + (size_t)nextsel * RL.stride;
+            nextsel ^= 1; have_next = 0;
+            int ab = 0;
+            if (lane == 0) ab = *(volatile int *)&q->abort;
+            if (__shfl_sync(FULLMASK, ab, 0)) break;
+        } else if (A.acount > A.abot) {
+            A.acount--;
+            R = A.base + A.offs[A.acount];
+            if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; __syncwarp(); }
+            int ab = 0;
+            if (lane == 0) ab = *(volatile int *)&q->abort;
+            if (__shfl_sync(FULLMASK, ab, 0)) break;
+        } else {
+            int stop = 0;
+            if (lane == 0) {
+                if (have_token) { __threadfence(); atomicSub(&q->pending, 1); }
+                if (*(volatile int *)&q->abort) stop = 1;
+                else {
+                    slot = ring_pop(q, &q->head, &q->tail, P.ring, P.ring_mask);
+                    if (slot < 0) {
+                        if (*(volatile int *)&q->pending == 0) stop = 1;
+                        else {
+                            if (!am_idle) { atomicAdd(&q->idle, 1); am_idle = true; }
+                            __nanosleep(500);
+                            if (overdue(q, 2)) stop = 1;
+                        }
+                    } else if (am_idle) { atomicSub(&q->idle, 1); am_idle = false; }
+                }
+            }
+            have_token = false;
+            stop = __shfl_sync(FULLMASK, stop, 0);
+            slot = __shfl_sync(FULLMASK, slot, 0);
+            if (stop) break;
+            if (slot < 0) continue;
+            have_token = true;  // the record's count in `pending` now stands for this busy warp
+            R = P.pool + (size_t)slot * RL.stride;
+        }
+        // a popped stack record sits where new children would be pushed: expand() copies what it needs first, and the
+        // stack top was lowered above, so the children overwrite it only after it is dead
+        { const unsigned long long t = gtimer(); t_idle += t - t_mark; t_mark = t; }
+        have_next = expand(P, s, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, cnt, hist);
+        __syncwarp();
+        { const unsigned long long t = gtimer(); t_busy += t - t_mark; t_mark = t; }
+        // hand the oldest pending record to an idle warp
+        if (P.dynamic && A.acount > A.abot) {
+            int want = 0, dslot = -1;
+            if (lane == 0) {
+                const int idle = *(volatile int *)&q->idle;
+                const int qlen = (int)(*(volatile unsigned int *)&q->tail - *(volatile unsigned int *)&q->head);
+                want = (idle > 0 && qlen < idle + P.lowwater) ? 1 : 0;
+                if (want) dslot = ring_pop(q, &q->fhead, &q->ftail, P.fring, P.ring_mask);
+            }
+            dslot = __shfl_sync(FULLMASK, dslot, 0);
+            if (dslot >= 0) {
+                const unsigned char *src = A.base + A.offs[A.abot];
+                const size_t bytes = (size_t)(A.offs[A.abot + 1] - A.offs[A.abot]);
+                copy_words(P.pool + (size_t)dslot * RL.stride, src, bytes, lane);
+                __syncwarp();
+                __threadfence();
+                if (lane == 0) { atomicAdd(&q->pending, 1); ring_push(q, &q->tail, P.ring, P.ring_mask, dslot); }
+                A.abot++;
+                cnt.donated++;
+                if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; __syncwarp(); }
             }
         }
-        stop = __shfl_sync(FULLMASK, stop, 0);
-        rec = __shfl_sync(FULLMASK, rec, 0);
-        if (stop) break;
-        if (rec < 0) continue;
-        run_task(P, s, rec, gwarp, cnt, hist);
-        __syncwarp();
-        if (lane == 0) { __threadfence(); atomicSub(&q->pending, 1); }
     }
     if (lane == 0) {
+        if (have_token) { __threadfence(); atomicSub(&q->pending, 1); }
         if (am_idle) atomicSub(&q->idle, 1);
         atomicAdd(&q->niter, cnt.niter); atomicAdd(&q->nprune, cnt.nprune); atomicAdd(&q->nodes, cnt.nodes);
         atomicAdd(&q->donated, cnt.donated);
         atomicAdd(&q->pivots, s.pivots); atomicAdd(&q->quick, s.quick); atomicAdd(&q->refactors, s.refactors);
         atomicAdd(&q->colds, s.colds);
+        t_idle += gtimer() - t_mark;
+        atomicAdd(&q->idle_ns, t_idle); atomicAdd(&q->busy_ns, t_busy);
     }
     __syncwarp();
     for (int e = lane; e <= n; e += 32) if (hist[e]) atomicAdd(&q->hist[e], (unsigned long long)hist[e]);
@@ -958,14 +1014,59 @@ __global__ void __launch_bounds__(512, 1) bltcu_search_kernel(const Params P) {
 
 // small helper kernels ---------------------------------------------------------------------------------------
 // fp64 basis, centre and the geometry of the problem; one warp
+// One warp: fp64 basis, centre, the geometry of the problem, then the initial solve LP(n) (closest.cc:206) whose
+// optimum is the parent vertex of the top level.  Writes the top-level record into `rec` (pool slot 0).  The basis
+// of this one solve lives in global memory (Wg); it is a cold path.
 __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p, double *Q,
-                                   double *Qrev, double *Rm, double *QTp, double *tmp, unsigned long long *now, int *rc) {
+                                   double *Qrev, double *Rm, double *QTp, double *tmp, unsigned long long *now, int *rc,
+                                   double *Wg, unsigned char *rec) {
+    extern __shared__ __align__(16) double smem[];
     const int lane = threadIdx.x;
     if (lane == 0) *now = gtimer();
     for (int e = lane; e < n * m; e += 32) B[e] = (double)lat[e];                                 // closest.cc:203
     for (int j = lane; j < m; j += 32) p[j] = (double)(con[2 * j + 1] + con[2 * j]) / 2.0;        // closest.cc:180-185
     __syncwarp();
-    const int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
+    int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
+    if (r == 0) {
+        WS s;
+        (void)carve_warp(s, smem, n, m, 0, 1);
+        s.Wg_a = Wg; s.Wg_b = Wg; s.tmpA = Wg + (size_t)m * (m | 1); s.Wpar = nullptr;
+        s.LDS = 1; s.LDG = m | 1; s.QS = 0;
+        use_side<true>(s, 0);
+        s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
+        s.pivots = s.quick = s.refactors = s.colds = 0;
+        const RecLayout RL = rec_layout(n, m);
+        const int qpar = m - n;
+        unsigned long long *cnt_out = now + 2;  // pivots, cold starts, refactorisations, quick prunes of this solve
+        double cm = 0.0, d = 0.0, vq = 0.0;
+        for (int j = lane; j < m; j += 32) { const double a = fabs(p[j]); cm = a > cm ? a : cm; }
+        cm = warp_max(cm);
+        for (size_t i = lane; i < RL.stride / 8; i += 32) ((unsigned long long *)rec)[i] = 0ull;
+        __syncwarp();
+        if (qpar > 0) {
+            for (int i = lane; i < qpar; i += 32) s.chat[i] = QTp[m - 1 - i];
+            __syncwarp();
+            r = lp_init1(s);
+            for (int i = 1; i < qpar && r == 0; ++i) {
+                lp_extend(s);
+                lp_values(s);
+                r = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
+            }
+            if (r == 0 && lp_solve(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
+            if (r == 0) {
+                vq = s.v[qpar];
+                for (int e = lane; e < qpar; e += 32) ((double *)(rec + RL.off_chat))[e] = s.chat[e];
+                chain_store(s, (double *)(rec + RL.off_H), (int *)(rec + RL.off_zrow), (signed char *)(rec + RL.off_sg));
+            }
+        }
+        if (r == 0) {
+            const double gb = QTp[n - 1];
+            const double xlast = (gb - vq) / Rm[(size_t)(n - 1) * n + (n - 1)];
+            if (lane == 0) { ((int *)rec)[0] = n; ((int *)rec)[1] = REC_TOP; ((double *)rec)[1] = xlast; ((double *)rec)[2] = gb; }
+            for (int j = lane; j < m; j += 32) ((double *)(rec + RL.off_cpar))[j] = p[j];
+        }
+        if (lane == 0) { cnt_out[0] = s.pivots; cnt_out[1] = s.colds; cnt_out[2] = s.refactors; cnt_out[3] = s.quick; }
+    }
     if (lane == 0) *rc = r;
 }
 __global__ void bltcu_check_kernel(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok) {
@@ -982,8 +1083,9 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
     const int lane = threadIdx.x;
     WS s;
     (void)carve_warp(s, smem, n, m, 0, 1);
-    s.Wg = Wg; s.tmpA = Wg + (size_t)m * (m | 1);
-    s.LDS = 1; s.LDG = m | 1; s.QS = 0; s.W = s.Wg; s.LD = s.LDG;
+    s.Wg_a = Wg; s.Wg_b = Wg; s.tmpA = Wg + (size_t)m * (m | 1); s.Wpar = nullptr;
+    s.LDS = 1; s.LDG = m | 1; s.QS = 0;
+    use_side<true>(s, 0);
     s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0;
     int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
@@ -1013,7 +1115,7 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
                 lp_values(s);
                 r = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
             }
-            if (r == 0 && lp_solve(s, INFINITY, cm, d) != NODE_EXPLORE) r = -1;
+            if (r == 0 && lp_solve(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
             if (r == 0) {
                 const double t = s.val[0];
                 for (int j = lane; j < m; j += 32) s.r[j] = s.pos[j] ? s.val[s.pos[j]] : (double)s.sg[j] * t;
@@ -1089,13 +1191,15 @@ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // Layout of one search's global workspace, shared by the cached-workspace path and the fixed-array path.
 struct Layout {
-    int KQS, LDS, LDG, LDQ, wpc, ctas, nwarps, pool_cap;
-    size_t warp_bytes, smem_bytes, scrD_stride, scrI_stride, scrB_stride, bigW_stride;
+    int KQS, LDS, LDG, LDQ, wpc, ctas, nwarps, pool_cap, arena_slots;
+    size_t warp_bytes, smem_bytes, wbuf_stride, arena_bytes, arena_stride;
     size_t o_q, o_in, o_B, o_p, o_Q, o_Qrev, o_Rm, o_QTp, o_tmp, o_rc, o_ring, o_fring, o_out, o_sol, o_bu, o_bk, o_bv, o_pool,
-        o_scrD, o_scrI, o_scrB, o_bigW, total;
+        o_wbuf, o_next, o_arena, total;
     RecLayout RL;
 };
-int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap) {
+// arena_recs: size of each warp's private stack in units of the largest record
+int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap,
+                int arena_recs) {
     L.KQS = std::min(m, QS_MAX); L.LDS = L.KQS | 1; L.LDG = m | 1; L.LDQ = m | 1;
     L.warp_bytes = warp_smem_bytes(n, m, L.KQS, L.LDS);
     const size_t q_bytes = (size_t)m * L.LDQ * 8;
@@ -1110,10 +1214,10 @@ int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_w
     L.RL = rec_layout(n, m);
     L.pool_cap = pool_cap;
     while ((size_t)L.pool_cap * L.RL.stride > ((size_t)3 << 30) && L.pool_cap > 256) L.pool_cap >>= 1;
-    L.scrD_stride = align_up(chain_off(m + 1) + (size_t)(n + 2) * m + (size_t)(n + 2) * (m + 1), 32);
-    L.scrI_stride = align_up(chain_ioff(m + 1) + 8, 32);
-    L.scrB_stride = align_up((size_t)(m + 2) * 2 * m, 32);
-    L.bigW_stride = align_up((size_t)m * L.LDG + (size_t)m * m, 32);
+    L.wbuf_stride = align_up((size_t)2 * m * m + (size_t)2 * m * L.LDG, 32);
+    L.arena_slots = 1024;
+    L.arena_bytes = align_up((size_t)arena_recs * L.RL.stride, 256);
+    L.arena_stride = align_up(L.arena_bytes + (size_t)L.arena_slots * 4, 256);
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
     L.o_q = carve(sizeof(QCtl));
@@ -1125,7 +1229,7 @@ int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_w
     L.o_Rm = carve((size_t)n * n * 8);
     L.o_QTp = carve((size_t)m * 8);
     L.o_tmp = carve((size_t)2 * m * 8);
-    L.o_rc = carve(16);
+    L.o_rc = carve(64);
     L.o_ring = carve((size_t)L.pool_cap * 4);
     L.o_fring = carve((size_t)L.pool_cap * 4);
     L.o_out = carve((size_t)L.pool_cap * 4);
@@ -1134,10 +1238,9 @@ int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_w
     L.o_bk = carve((size_t)L.nwarps * n);
     L.o_bv = carve((size_t)L.nwarps * 4);
     L.o_pool = carve((size_t)L.pool_cap * L.RL.stride);
-    L.o_scrD = carve((size_t)L.nwarps * L.scrD_stride * 8);
-    L.o_scrI = carve((size_t)L.nwarps * L.scrI_stride * 4);
-    L.o_scrB = carve((size_t)L.nwarps * L.scrB_stride);
-    L.o_bigW = carve((size_t)L.nwarps * L.bigW_stride * 8);
+    L.o_wbuf = carve((size_t)L.nwarps * L.wbuf_stride * 8);
+    L.o_next = carve((size_t)L.nwarps * 2 * L.RL.stride);
+    L.o_arena = carve((size_t)L.nwarps * L.arena_stride);
     L.total = off;
     return 0;
 }
@@ -1149,10 +1252,9 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
     P.q = (QCtl *)(base + L.o_q);
     P.ring = (int *)(base + L.o_ring); P.fring = (int *)(base + L.o_fring); P.ring_mask = (unsigned int)L.pool_cap - 1;
     P.pool = base + L.o_pool; P.rec_stride = L.RL.stride; P.pool_cap = L.pool_cap;
-    P.scrD = (double *)(base + L.o_scrD); P.scrD_stride = L.scrD_stride;
-    P.scrI = (int *)(base + L.o_scrI); P.scrI_stride = L.scrI_stride;
-    P.scrB = (signed char *)(base + L.o_scrB); P.scrB_stride = L.scrB_stride;
-    P.bigW = (double *)(base + L.o_bigW); P.bigW_stride = L.bigW_stride;
+    P.wbuf = (double *)(base + L.o_wbuf); P.wbuf_stride = L.wbuf_stride;
+    P.nextrec = base + L.o_next;
+    P.arena = base + L.o_arena; P.arena_stride = L.arena_stride; P.arena_bytes = L.arena_bytes; P.arena_slots = L.arena_slots;
     P.sol = (int64_t *)(base + L.o_sol);
     P.best_u = (int64_t *)(base + L.o_bu); P.best_key = base + L.o_bk; P.best_valid = (int *)(base + L.o_bv);
     P.out_list = (int *)(base + L.o_out);
@@ -1174,7 +1276,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
     Layout L;
-    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 16, 4096)) {
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 8, 4096, 24)) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }
@@ -1194,17 +1296,20 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
 
     CK(cudaFuncSetAttribute(bltcu_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     int launches = 0;
-    bltcu_setup_kernel<<<1, 32, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q),
-                                        (double *)P.Qrev, (double *)P.Rm, (double *)P.QTp, (double *)(base + L.o_tmp),
-                                        (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8));
+    const size_t setup_smem = warp_smem_bytes(n, m, 0, 1);
+    CK(cudaFuncSetAttribute(bltcu_setup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)setup_smem));
+    bltcu_setup_kernel<<<1, 32, setup_smem, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q),
+                                                 (double *)P.Qrev, (double *)P.Rm, (double *)P.QTp, (double *)(base + L.o_tmp),
+                                                 (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8), P.wbuf,
+                                                 P.pool);
     CK(cudaGetLastError());
     launches++;
     // radius: closest.cc:193-194 uses row 0 only; device clock for the watchdog deadline; status of the geometry
     int64_t con0[2];
-    unsigned long long now_rc[2] = {0, 0};
+    unsigned long long now_rc[6] = {0, 0, 0, 0, 0, 0};
     unsigned long long deadline_ns = 0;
     CK(cudaMemcpyAsync(con0, d_con, 16, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(now_rc, base + L.o_rc, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(now_rc, base + L.o_rc, 48, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if ((int)(now_rc[1] & 0xffffffffu) != 0) return BLTCU_STATUS_LP_FAIL;  // dependent basis rows
     P.radius = (double)(con0[1] - con0[0]) / 2.0;
@@ -1238,22 +1343,12 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     CK(cudaMemsetAsync(P.best_valid, 0, (size_t)nwarps * 4, st));
     CK(cudaMemsetAsync(P.sol, 0, (size_t)n * 8, st));
 
-    // root record in slot 0: k = n, flags ROOT, cpar = p
-    {
-        std::vector<unsigned char> rec(RL.stride, 0);
-        ((int *)rec.data())[0] = n;
-        ((int *)rec.data())[1] = REC_ROOT;
-        CK(cudaMemcpyAsync(P.pool, rec.data(), RL.stride, cudaMemcpyHostToDevice, st));
-        CK(cudaStreamSynchronize(st));
-        CK(cudaMemcpyAsync(P.pool + RL.off_cpar, P.p, (size_t)m * 8, cudaMemcpyDeviceToDevice, st));
-    }
-
     float kernel_ms = 0.f;
     QCtl acc;  // totals
     memset(&acc, 0, sizeof acc);
     auto add_counts = [&](const QCtl &x) {
         acc.niter += x.niter; acc.nprune += x.nprune; acc.nodes += x.nodes; acc.pivots += x.pivots; acc.quick += x.quick;
-        acc.refactors += x.refactors; acc.colds += x.colds; acc.donated += x.donated;
+        acc.refactors += x.refactors; acc.colds += x.colds; acc.donated += x.donated; acc.idle_ns += x.idle_ns; acc.busy_ns += x.busy_ns;
         for (int i = 0; i <= n; ++i) acc.hist[i] += x.hist[i];
     };
     auto launch = [&]() -> int {
@@ -1275,6 +1370,10 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
 
     int status = BLTCU_STATUS_OK, found = 0;
     std::vector<int> initial;
+    if (rank == 0) {  // the initial solve LP(n) done by the setup kernel
+        acc.nodes += 1; acc.hist[n] += 1;
+        acc.pivots += now_rc[2]; acc.colds += now_rc[3]; acc.refactors += now_rc[4]; acc.quick += now_rc[5];
+    }
     if (o.split_depth > 0) {
         // phase A: deterministic static split of the top levels (every rank computes the same list)
         initial.assign(1, 0);
@@ -1338,6 +1437,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         stats->niter = acc.niter; stats->nprune = acc.nprune; stats->nodes = acc.nodes; stats->pivots = acc.pivots;
         stats->quick_prunes = acc.quick; stats->refactors = acc.refactors; stats->cold_starts = acc.colds;
         stats->donated = acc.donated;
+        stats->busy_frac = (acc.idle_ns + acc.busy_ns) ? (double)acc.busy_ns / (double)(acc.idle_ns + acc.busy_ns) : 0.0;
         for (int i = 0; i <= n; ++i) stats->hist[i] = acc.hist[i];
         stats->kernel_ms = kernel_ms;
         stats->found = found;
@@ -1484,6 +1584,7 @@ extern "C" const char *bltcu_version(void) { return "blt-b200 0.2 (sm_100a)"; }
 #define BLTCU_NOALLOC_WPC 2       // warps per CTA of this variant (fixed so that the level store has a fixed size)
 #define BLTCU_NOALLOC_CTAS 148    // at most this many CTAs
 #define BLTCU_NOALLOC_POOL 512    // subtree records (power of two)
+#define BLTCU_NOALLOC_ARENA_RECS 6 // private stack of each warp, in units of the largest record
 #define BLTCU_NOALLOC_MAXDEV 64
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[BLTCU_NOALLOC_BYTES];
@@ -1506,7 +1607,6 @@ __global__ void bltcu_noalloc_init_kernel(Params P, unsigned long long deadline_
         P.ring[i] = (i == 0) ? 0 : -1;                      // the root record sits in slot 0
         P.fring[i] = (i + 1 <= (int)P.ring_mask) ? i + 1 : -1;  // slots 1..cap-1 are free
     }
-    for (size_t i = tid; i < RL.stride; i += nth) P.pool[i] = 0;
     for (int i = tid; i < P.n; i += nth) P.sol[i] = 0;
     for (int i = tid; i < nwarps; i += nth) P.best_valid[i] = 0;
     __threadfence();
@@ -1514,10 +1614,7 @@ __global__ void bltcu_noalloc_init_kernel(Params P, unsigned long long deadline_
     if (blockIdx.x == 0) {
         if (threadIdx.x == 0) {
             P.q->tail = 1; P.q->pending = 1; P.q->ftail = P.ring_mask; P.q->deadline_ns = deadline_ns;
-            ((int *)P.pool)[0] = P.n;
-            ((int *)P.pool)[1] = REC_ROOT;
         }
-        for (int j = threadIdx.x; j < P.m; j += blockDim.x) ((double *)(P.pool + RL.off_cpar))[j] = P.p[j];
     }
 }
 
@@ -1556,7 +1653,7 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     // same shared-memory and workspace layout as search_impl(), but inside the fixed array
     Layout L;
     if (make_layout(L, n, m, g_noalloc_smem[device], std::min(g_noalloc_sms[device], BLTCU_NOALLOC_CTAS), BLTCU_NOALLOC_WPC, 0,
-                    BLTCU_NOALLOC_WPC, BLTCU_NOALLOC_POOL))
+                    BLTCU_NOALLOC_WPC, BLTCU_NOALLOC_POOL, BLTCU_NOALLOC_ARENA_RECS))
         return BLTCU_STATUS_ERROR;
     if (L.total > (size_t)BLTCU_NOALLOC_BYTES) {
         fprintf(stderr, "bltcu_closest_noalloc: internal layout (%zu bytes) exceeds the scratch array\n", L.total);
@@ -1576,9 +1673,11 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     cudaStream_t st = 0;  // legacy default stream: creating a stream would be an allocation
     CK(cudaMemcpyAsync(d_lat, lat, (size_t)n * m * 8, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(d_con, con, (size_t)2 * m * 8, cudaMemcpyHostToDevice, st));
-    bltcu_setup_kernel<<<1, 32, 0, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q),
-                                        (double *)P.Qrev, (double *)P.Rm, (double *)P.QTp, (double *)(base + L.o_tmp),
-                                        (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8));
+    // also writes the top-level record into pool slot 0 (the root record of the search)
+    bltcu_setup_kernel<<<1, 32, warp_smem_bytes(n, m, 0, 1), st>>>(
+        d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q), (double *)P.Qrev, (double *)P.Rm,
+        (double *)P.QTp, (double *)(base + L.o_tmp), (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8),
+        P.wbuf, P.pool);
     CK(cudaGetLastError());
     unsigned long long now_rc[2] = {0, 0};
     CK(cudaMemcpyAsync(now_rc, base + L.o_rc, 16, cudaMemcpyDeviceToHost, st));

@@ -52,7 +52,8 @@ typedef struct bltcu_stats {
     int found;             /* 1 = a lattice point inside the box was found */
     int launches;          /* kernels launched by this call */
     int warps, ctas;       /* launch shape */
-    uint64_t scratch_bytes;/* global scratch used (level store + subtree pool) */
+    uint64_t scratch_bytes;/* global scratch used (per-warp stacks + subtree pool) */
+    double busy_frac;      /* share of warp time spent expanding records (the rest waits for work) */
 } bltcu_stats;
 
 /* closest(): libblt/closest.h:50-54, libblt/closest.cc:166-327.
