@@ -43,11 +43,15 @@
 #define EPS_OPT 1.0e-9
 #define PIV_TOL 1.0e-11
 #define HARRIS_DELTA 1.0e-10
+#define PIV_REL 1.0e-9
+#define STALL_MAX 40
 #define MAXD BLTCU_MAX_DIM
 #define QS_MAX 32  // largest basis kept in shared memory
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
-enum { REC_TOP = 1 };  // record flag: its children are the top level (first prune ends the search, closest.cc:280-286)
+enum { REC_TOP = 1, REC_CONT = 2 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
+#define EAGER_MAX 4  // explored children a sibling loop produces before it is suspended in favour of its first child
+// REC_TOP: the record's children are the top level (first prune ends the search, closest.cc:280-286)
 
 // ------------------------------------------------------------------------------------------------------------
 // Global control block (one per search, zeroed by the host before launch)
@@ -62,11 +66,12 @@ struct QCtl {
     int found;                  // a solution has been written to sol
     unsigned int out_count;     // static split: number of collected subtrees
     int timed_out;              // watchdog fired: 1 node loop, 2 idle loop, 3 pop spin, 4 push spin
-    int pad1;
+    int fail_info;              // failcode | level << 8 of the first LP failure (diagnostics)
     unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
     unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated;
     unsigned long long idle_ns, busy_ns;  // summed over warps: time spent waiting for work / expanding records
     unsigned long long hist[MAXD + 1];
+    long long fail_u[MAXD];     // coefficients of the node whose LP failed first (diagnostics)
 };
 
 struct Params {
@@ -114,14 +119,16 @@ struct RecLayout {
 __host__ __device__ inline size_t al8(size_t x) { return (x + 7) / 8 * 8; }
 __host__ __device__ inline RecLayout rec_layout(int n, int m) {
     RecLayout L;
-    size_t o = 32;  // header: int k, int flags, double xc, double gbase, pad
+    size_t o = 48;  // header: int k, int flags, double xc, double gbase, int step, int state, int bytes, pad
     L.off_u = o; o += (size_t)8 * n;
     L.off_ord = o; o += al8((size_t)n);
     L.off_cpar = o; o += (size_t)8 * m;
     L.off_chat = o; o += (size_t)8 * (m + 1);
     L.off_sg = o; o += al8((size_t)m);
     L.off_zrow = o; o += al8((size_t)4 * (m + 1));
-    L.off_H = o; o += (size_t)8 * m * m;
+    L.off_H = o;
+    // the largest record is a suspended sibling loop: parent vertex + two side vertices + their rows and signs
+    o += (size_t)8 * 3 * m * m + 2 * (al8((size_t)m) + al8((size_t)4 * (m + 1)));
     L.stride = (o + 255) / 256 * 256;
     return L;
 }
@@ -130,14 +137,20 @@ __host__ __device__ inline size_t rec_bytes(const RecLayout &L, int m, int k) {
     const size_t q = (size_t)(m - k);
     return k <= 1 ? L.off_sg : (L.off_H + 8 * q * q + 15) / 16 * 16;
 }
-// (unused by the kernel since the level store was replaced by per-warp stacks; kept for the layout helpers)
-__host__ __device__ inline size_t chain_off(int q) {  // doubles before q: 2 * sum_{j<q} j^2
-    const size_t x = (size_t)q;
-    return 2 * ((x - 1) * x * (2 * x - 1) / 6);
-}
-__host__ __device__ inline size_t chain_ioff(int q) {  // ints before q: 2 * sum_{j<q} j
-    const size_t x = (size_t)q;
-    return (x - 1) * x;
+// a suspended sibling loop at children level k: the record it was started from, then both sides
+struct ContLayout { size_t off_HA, off_HB, off_zA, off_zB, off_sA, off_sB, bytes; };
+__host__ __device__ inline ContLayout cont_layout(const RecLayout &L, int m, int k) {
+    const size_t qpar = (size_t)(m - k), qd = qpar + 1;
+    ContLayout C;
+    size_t o = L.off_H + 8 * qpar * qpar;
+    C.off_HA = o; o += 8 * qd * qd;
+    C.off_HB = o; o += 8 * qd * qd;
+    C.off_zA = o; o += al8(4 * (size_t)(m + 1));
+    C.off_zB = o; o += al8(4 * (size_t)(m + 1));
+    C.off_sA = o; o += al8((size_t)m);
+    C.off_sB = o; o += al8((size_t)m);
+    C.bytes = (o + 15) / 16 * 16;
+    return C;
 }
 
 // ------------------------------------------------------------------------------------------------------------
@@ -157,6 +170,8 @@ struct WS {
     int LDQ, n, m, qd, lane;
     double *al, *be;  // alpha_j = n_j . y, beta_j = n_j . H[pe] (shared memory, m each)
     unsigned long long pivots, quick, refactors, colds;
+    int failcode;  // why the last NODE_FAIL happened (diagnostics)
+    unsigned int repairs;
     // the two sides of the level being expanded, and the parent's vertex
     double *Ws_a, *Ws_b, *Wg_a, *Wg_b;
     int *zrow_a, *zrow_b;
@@ -309,7 +324,44 @@ __device__ __forceinline__ double lp_alpha_beta(WS &s, int pe) {
     }
     return butterfly(part);
 }
-__device__ __forceinline__ int lp_ratio(WS &s, int se, int pe) {
+// sign repair (twin of the oracle's lp_repair): rows whose sg_j*alpha_j fell below -HARRIS_DELTA go to the other bound;
+// column 0 of A changes by Delta = sum -2 sg_j n_j, a rank-one correction of H.  Returns 1 if anything was flipped.
+__device__ __forceinline__ int lp_repair(WS &s) {
+    const int m = s.m, qd = s.qd, LD = s.LD;
+    bool any = false;
+#pragma unroll 1
+    for (int j = s.lane; j < m; j += 32) {
+        double rj = 0.0;
+        if (!s.pos[j] && (double)s.sg[j] * s.al[j] < -HARRIS_DELTA) { rj = -2.0 * (double)s.sg[j]; any = true; }
+        s.r[j] = rj;
+    }
+    if (!__any_sync(FULLMASK, any)) return 0;
+    __syncwarp();
+    for (int c = s.lane; c < qd; c += 32) {
+        const double *r = s.r, *Qc = s.Qs + c;
+        const int LDQ = s.LDQ;
+        s.a[c] = dot4(m, [&](int e) { return r[e]; }, [&](int e) { return Qc[(size_t)e * LDQ]; });
+    }
+    __syncwarp();
+    for (int i = s.lane; i < qd; i += 32) {
+        const double *Hi = s.W + (size_t)i * LD, *a = s.a;
+        s.w[i] = dot4(qd, [&](int e) { return Hi[e]; }, [&](int e) { return a[e]; });
+    }
+    for (int c = s.lane; c < qd; c += 32) s.v[c] = s.W[c];
+    __syncwarp();
+    const double den = 1.0 + s.w[0];
+    for (int c = s.lane; c < qd; c += 32) {
+        const double vc = s.v[c];
+        double *Hc = s.W + c;
+#pragma unroll 1
+        for (int i = 0; i < qd; ++i) { const double f = s.w[i] / den; Hc[(size_t)i * LD] = fma(-f, vc, Hc[(size_t)i * LD]); }
+    }
+    for (int j = s.lane; j < m; j += 32) if (s.r[j] != 0.0) s.sg[j] = (signed char)-s.sg[j];
+    __syncwarp();
+    s.repairs++;
+    return 1;
+}
+__device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland) {
     const int m = s.m, qd = s.qd;
     const bool artificial = s.zrow[pe] < 0;
     double scale = 0.0;
@@ -318,31 +370,39 @@ __device__ __forceinline__ int lp_ratio(WS &s, int se, int pe) {
 #pragma unroll 1
     for (int j = s.lane; j < m; j += 32) if (!s.pos[j]) { const double a = fabs(s.be[j]); scale = a > scale ? a : scale; }
     scale = warp_max(scale);
-    const double tiny = PIV_TOL * scale, dmin = artificial ? tiny : 0.0;
-    double tmax = INFINITY;
-#pragma unroll 1
-    for (int j = s.lane; j < m; j += 32) {
-        if (s.pos[j]) continue;
-        const double den = -(double)(se * s.sg[j]) * s.be[j];
-        if (!(den > dmin)) continue;
-        double num = (double)s.sg[j] * s.al[j];
-        if (num < 0.0) num = 0.0;
-        const double rt = (num + HARRIS_DELTA) / den;
-        if (rt < tmax) tmax = rt;
-    }
-    tmax = warp_min(tmax);
+    const double tiny = PIV_TOL * scale;
     int best = -1; double bd = 0.0;
+    // tier 0 only accepts pivots that are not tiny next to the row's scale; tier 1 accepts any positive pivot
 #pragma unroll 1
-    for (int j = s.lane; j < m; j += 32) {
-        if (s.pos[j]) continue;
-        const double den = -(double)(se * s.sg[j]) * s.be[j];
-        if (!(den > dmin)) continue;
-        double num = (double)s.sg[j] * s.al[j];
-        if (num < 0.0) num = 0.0;
-        if (num / den <= tmax && den > bd) { bd = den; best = j; }
+    for (int tier = 0; tier < 2 && best < 0; ++tier) {
+        const double dmin = tier == 0 ? PIV_REL * scale : 0.0;
+        double tmax = INFINITY;
+#pragma unroll 1
+        for (int j = s.lane; j < m; j += 32) {
+            if (s.pos[j]) continue;
+            const double den = -(double)(se * s.sg[j]) * s.be[j];
+            if (!(den > dmin)) continue;
+            double num = (double)s.sg[j] * s.al[j] + HARRIS_DELTA;  // rows already below zero get less room, not more
+            if (num < 0.0) num = 0.0;
+            const double rt = num / den;
+            if (rt < tmax) tmax = rt;
+        }
+        tmax = warp_min(tmax);
+        bd = 0.0; best = -1;
+#pragma unroll 1
+        for (int j = s.lane; j < m; j += 32) {
+            if (s.pos[j]) continue;
+            const double den = -(double)(se * s.sg[j]) * s.be[j];
+            if (!(den > dmin)) continue;
+            double num = (double)s.sg[j] * s.al[j];
+            if (num < 0.0) num = 0.0;
+            if (num / den <= tmax && (bland ? best < 0 : den > bd)) { bd = den; best = j; }
+        }
+        if (bland) { double key = best >= 0 ? -(double)best : 0.0; warp_argmax(key, best); bd = __shfl_sync(FULLMASK, bd, 0); }  // lowest row index
+        else warp_argmax(bd, best);
     }
-    warp_argmax(bd, best);
-    if (best >= 0 || artificial) return best;
+    if (artificial) return (best >= 0 && bd > 1.0e-3 * tiny) ? best : -1;  // its pivot is den itself: refuse a vanishing one
+    if (best >= 0) return best;
     double ba = -1.0;
 #pragma unroll 1
     for (int j = s.lane; j < m; j += 32) {
@@ -429,7 +489,8 @@ __device__ __forceinline__ void lp_extend(WS &s) {
 __device__ __forceinline__ int lp_drop_artificial(WS &s, int sf) {
     const int pe = s.qd - 1;
     lp_alpha_beta(s, pe);
-    const int l = lp_ratio(s, sf, pe);
+    if (lp_repair(s)) lp_alpha_beta(s, pe);
+    const int l = lp_ratio(s, sf, pe, false);
     if (l < 0) return -1;
     return lp_replace(s, pe, l, sf);
 }
@@ -501,8 +562,9 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
         if (s.val[0] < 0.0) lp_flip(s);
     }
     const int cap = 100 * m + 1000;
-    bool refactored = false;
-    int iter = 0;
+    bool refactored = false, bland = false;
+    int iter = 0, stall = 0;
+    double tbest = -1.0;
 #pragma unroll 1
     for (;;) {
         int pe, se;
@@ -510,10 +572,19 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
         else {
             const double t = s.val[0];
             if (!approxLE(t, radius)) { if (iter == 0) s.quick++; return NODE_PRUNE; }
+            // degenerate stalling: after STALL_MAX steps without progress switch to lowest-index (Bland) choices
+            if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= STALL_MAX) bland = true;
+            const double tol = EPS_OPT * (cmax + t);
             pe = -1; double vmax = -1.0;
             for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
             warp_argmax(vmax, pe);
-            const double tol = EPS_OPT * (cmax + t);
+            if (bland && pe >= 0 && vmax > t + tol) {  // the violated basic row with the lowest row index
+                int bp = -1; double key = 0.0;
+                for (int p = 1 + s.lane; p < qd; p += 32)
+                    if (fabs(s.val[p]) > t + tol && (bp < 0 || -(double)s.zrow[p] > key)) { key = -(double)s.zrow[p]; bp = p; }
+                warp_argmax(key, bp);
+                pe = bp;
+            }
             if (pe < 0 || vmax <= t + tol) {
                 const int nv = qd < m ? qd + 1 : qd;
                 lp_image(s, nv);
@@ -521,30 +592,39 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
                 for (int i = s.lane; i < qd; i += 32) { const double e = fabs(s.v[i] - s.chat[i]); err = e > err ? e : err; }
                 err = warp_max(err);
                 if (err <= 1.0e-8 * ((double)m * cmax + t)) { d_out = t; return NODE_EXPLORE; }
-                if (refactored) return NODE_FAIL;
+                if (refactored) { s.failcode = 1; return NODE_FAIL; }
                 refactored = true;
-                if (lp_refactor(s)) return NODE_FAIL;
+                if (lp_refactor(s)) { s.failcode = 2; return NODE_FAIL; }
                 lp_values(s);
                 if (s.val[0] < 0.0) lp_flip(s);
                 ++iter;
                 continue;
             }
-            if (iter >= cap) return NODE_FAIL;
+            if (iter >= cap) { s.failcode = 3; return NODE_FAIL; }
             se = s.val[pe] > 0.0 ? 1 : -1;
         }
-        const double nrm1 = lp_alpha_beta(s, pe);
-        if (!art && fabs(nrm1 - 1.0) > 1.0e-6) {
-            if (refactored) return NODE_FAIL;
+        double nrm1 = lp_alpha_beta(s, pe);
+        if (lp_repair(s)) {
+            if (art) nrm1 = lp_alpha_beta(s, pe);
+            else {  // the vertex moved a little: price again
+                lp_values(s);
+                if (s.val[0] < 0.0) lp_flip(s);
+                ++iter;
+                continue;
+            }
+        }
+        if (!art && fabs(nrm1 - 1.0) > 1.0e-5) {
+            if (refactored) { s.failcode = 4; return NODE_FAIL; }
             refactored = true;
-            if (lp_refactor(s)) return NODE_FAIL;
+            if (lp_refactor(s)) { s.failcode = 5; return NODE_FAIL; }
             lp_values(s);
             if (s.val[0] < 0.0) lp_flip(s);
             ++iter;
             continue;
         }
-        const int l = lp_ratio(s, se, pe);
-        if (l < 0) return NODE_FAIL;
-        if (lp_replace(s, pe, l, se)) return NODE_FAIL;
+        const int l = lp_ratio(s, se, pe, bland);
+        if (l < 0) { s.failcode = art ? 6 : 7; return NODE_FAIL; }
+        if (lp_replace(s, pe, l, se)) { s.failcode = 8; return NODE_FAIL; }
         lp_values(s);
         if (art) { art = 0; if (s.val[0] < 0.0) lp_flip(s); }
         else ++iter;
@@ -658,7 +738,7 @@ __device__ __forceinline__ void copy_words(void *dst, const void *src, size_t by
 __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL, WS &s, unsigned char *C, int k, double xlast,
                                             double gn) {
     const int n = P.n, m = P.m, lane = s.lane, qd = s.qd;
-    if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gn; }
+    if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gn; ((int *)C)[6] = 0; ((int *)C)[7] = 0; }
     for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
     for (int j = lane; j < m; j += 32) ((double *)(C + RL.off_cpar))[j] = s.c[j];
     for (int e = lane; e < qd; e += 32) ((double *)(C + RL.off_chat))[e] = s.chat[e];
@@ -677,7 +757,8 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     const int rflags = ((const int *)R)[1];
     double xc0 = ((const double *)R)[1];
     double gb = ((const double *)R)[2];
-    const bool is_top = (rflags & REC_TOP) != 0;
+    const bool is_top = (rflags & REC_TOP) != 0, is_cont = (rflags & REC_CONT) != 0;
+    const int c_step = ((const int *)R)[6], c_state = ((const int *)R)[7];
     const int kk = k0 - 1, qd0 = m - kk, qpar = m - k0;
 
     // ---- take what is needed out of the record; afterwards the record is dead ----
@@ -688,6 +769,16 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         for (int p = lane; p < qpar; p += 32) s.pzrow[p] = ((const int *)(R + RL.off_zrow))[p];
         for (int j = lane; j < m; j += 32) s.psg[j] = ((const signed char *)(R + RL.off_sg))[j];
         for (int e = lane; e < qpar; e += 32) s.chat[e] = ((const double *)(R + RL.off_chat))[e];
+    }
+    if (is_cont) {
+        const ContLayout CL = cont_layout(RL, m, k0);
+        const int st = c_state;
+        for (int side = 0; side < 2; ++side) {
+            if (!((st >> (1 + side)) & 1)) continue;
+            use_side<BIG>(s, side);
+            chain_load(s, (const double *)(R + (side ? CL.off_HB : CL.off_HA)), (const int *)(R + (side ? CL.off_zB : CL.off_zA)),
+                       (const signed char *)(R + (side ? CL.off_sB : CL.off_sA)), qd0);
+        }
     }
     __syncwarp();
     if (pool_slot >= 0) {
@@ -710,8 +801,11 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     long long ucur = (long long)round(xc0);
     int step = sgn_d(xc0 - (double)ucur);
     bool pruned = false;
-    int inited = 0, nkept = 0;
-    if (lane == 0) { s.u[kk] = ucur; s.ord[kk] = 0; }
+    int inited = 0, nkept = 0, nexp = 0;
+    if (is_cont) {  // resume a suspended loop: the next sibling, the zig-zag state and both side vertices were saved
+        ucur = s.u[kk];
+        step = c_step; pruned = (c_state & 1) != 0; inited = (c_state >> 1) & 3;
+    } else if (lane == 0) { s.u[kk] = ucur; s.ord[kk] = 0; }
     __syncwarp();
     const bool forced = (n - k0) < P.static_depth;  // static split: every explored child of this record is published
     unsigned int wd = 0;
@@ -744,25 +838,42 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
             const int side = dir > 0 ? 0 : 1;
             use_side<BIG>(s, side);
             const double clast = fma(-(double)ucur, Rkk, gb);
-            int art = 0;
+            if (lane == 0) s.chat[qd0 - 1] = clast;
             if (!((inited >> side) & 1)) {
-                if (qd0 == 1) {
-                    if (lp_init1(s)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return nkept; }
-                } else {
-                    chain_load(s, s.Wpar, s.pzrow, s.psg, qpar);
-                    lp_extend(s);
-                }
+                if (qd0 == 1) { if (lp_init1(s)) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return nkept; } }
+                else chain_load(s, s.Wpar, s.pzrow, s.psg, qpar);  // the parent's vertex, one coordinate short
                 inited |= 1 << side;
-                if (qd0 > 1) art = dir;
-                if (lane == 0) s.chat[qd0 - 1] = clast;
-                __syncwarp();
-            } else {
-                s.qd = qd0;
-                if (lane == 0) s.chat[qd0 - 1] = clast;
-                __syncwarp();
+            } else s.qd = qd0;
+            __syncwarp();
+            // One loop serves the warm start (at most one extension) and the last resort after a failed warm start:
+            // rebuild the vertex coordinate by coordinate from nothing, every intermediate problem solved to optimality.
+            bool cold = false;
+            status = NODE_FAIL;
+#pragma unroll 1
+            for (;;) {
+                int art = 0;
+                double rad = P.radius;
+                if (s.qd < qd0) {
+                    lp_extend(s);
+                    if (cold) { lp_values(s); art = s.val[s.qd - 1] > 0.0 ? 1 : -1; if (s.qd < qd0) rad = INFINITY; }
+                    else art = dir;
+                }
+                status = lp_solve(s, rad, cmax, d, art);
+                if (status == NODE_FAIL) {
+                    if (cold || lp_init1(s)) { status = NODE_FAIL; break; }
+                    cold = true;
+                    continue;
+                }
+                if (s.qd == qd0) break;
+                if (status != NODE_EXPLORE) { status = NODE_FAIL; break; }
             }
-            status = lp_solve(s, P.radius, cmax, d, art);
-            if (status == NODE_FAIL) { fail_search(P, lane, BLTCU_STATUS_LP_FAIL); return nkept; }
+            if (status == NODE_FAIL) {
+                // Remember the failure and go on as if the node had been pruned: another warp may find a point inside
+                // the box, and then the failure is irrelevant (the sequential order might never have come here).
+                if (lane == 0 && atomicCAS(&P.q->fail_info, 0, s.failcode | (k0 << 8) | (qd0 << 16)) == 0) { for (int e = 0; e < n; ++e) P.q->fail_u[e] = s.u[e]; }
+                inited &= ~(1 << side);  // this side's vertex is unusable: the next node of the side starts over
+                status = NODE_PRUNE;
+            }
             if (status == NODE_EXPLORE) {  // real centre of the next level: x_{kk-1} of the optimum
                 gn = fma(-(double)ucur, Rk1k, g2);
                 xlast = (gn - s.v[qd0]) / Rk1;
@@ -798,6 +909,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 }
             }
             write_child(P, RL, s, C, k0, xlast, gn);
+            nexp++;
             if (dest == 0) nkept = 1;
             else if (dest == 1) { if (lane == 0) A.offs[A.acount + 1] = (int)(A.offs[A.acount] + need); A.acount++; __syncwarp(); }
             else {
@@ -848,6 +960,45 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         ucur += step; step = -step - (step > 0 ? 1 : -1);
         if (lane == 0) { s.u[kk] = ucur; if (s.ord[kk] < 255) s.ord[kk]++; }
         __syncwarp();
+        // Wide level or little stack space left: park the rest of this loop and go down into the first child, the way
+        // the depth-first order would.  The parked loop is a record like any other (it can even be donated).
+        if (status == NODE_EXPLORE && !forced && k0 > 1 && (nexp >= EAGER_MAX || (size_t)A.offs[A.acount] * 2 > A.cap)) {
+            const ContLayout CL = cont_layout(RL, m, k0);
+            unsigned char *C = nullptr;
+            int slot = -1;
+            const size_t top = (size_t)A.offs[A.acount];
+            const bool in_arena = A.acount + 1 < A.slots && top + CL.bytes <= A.cap;
+            if (in_arena) C = A.base + top;
+            else {
+                if (lane == 0) slot = ring_pop(P.q, &P.q->fhead, &P.q->ftail, P.fring, P.ring_mask);
+                slot = __shfl_sync(FULLMASK, slot, 0);
+                if (slot < 0) { fail_search(P, lane, BLTCU_STATUS_ERROR); return nkept; }
+                C = P.pool + (size_t)slot * RL.stride;
+            }
+            if (lane == 0) {
+                ((int *)C)[0] = k0; ((int *)C)[1] = (is_top ? REC_TOP : 0) | REC_CONT; ((double *)C)[1] = xc0; ((double *)C)[2] = gb;
+                ((int *)C)[6] = step; ((int *)C)[7] = (pruned ? 1 : 0) | (inited << 1); ((int *)C)[8] = (int)CL.bytes;
+            }
+            for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
+            for (int j = lane; j < m; j += 32) { ((double *)(C + RL.off_cpar))[j] = s.cpar[j]; ((signed char *)(C + RL.off_sg))[j] = s.psg[j]; }
+            for (int e = lane; e < qpar; e += 32) { ((double *)(C + RL.off_chat))[e] = s.chat[e]; ((int *)(C + RL.off_zrow))[e] = s.pzrow[e]; }
+            if (qpar > 0) copy_words(C + RL.off_H, s.Wpar, (size_t)qpar * qpar * 8, lane);
+            for (int side = 0; side < 2; ++side) {
+                if (!((inited >> side) & 1)) continue;
+                use_side<BIG>(s, side);
+                s.qd = qd0;
+                chain_store(s, (double *)(C + (side ? CL.off_HB : CL.off_HA)), (int *)(C + (side ? CL.off_zB : CL.off_zA)),
+                            (signed char *)(C + (side ? CL.off_sB : CL.off_sA)));
+            }
+            __syncwarp();
+            if (in_arena) { if (lane == 0) A.offs[A.acount + 1] = (int)(top + CL.bytes); A.acount++; __syncwarp(); }
+            else {
+                __threadfence();
+                if (lane == 0) { atomicAdd(&P.q->pending, 1); ring_push(P.q, &P.q->tail, P.ring, P.ring_mask, slot); }
+                cnt.donated++;
+            }
+            return nkept;
+        }
     }
 }
 
@@ -913,7 +1064,7 @@ __global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
     }
     s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
     s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-    s.pivots = s.quick = s.refactors = s.colds = 0;
+    s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
     use_side<false>(s, 0);
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     Arena A;
@@ -1034,7 +1185,7 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
         s.LDS = 1; s.LDG = m | 1; s.QS = 0;
         use_side<true>(s, 0);
         s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-        s.pivots = s.quick = s.refactors = s.colds = 0;
+        s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0;
         const RecLayout RL = rec_layout(n, m);
         const int qpar = m - n;
         unsigned long long *cnt_out = now + 2;  // pivots, cold starts, refactorisations, quick prunes of this solve
@@ -1087,7 +1238,7 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
     s.LDS = 1; s.LDG = m | 1; s.QS = 0;
     use_side<true>(s, 0);
     s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-    s.pivots = s.quick = s.refactors = s.colds = 0;
+    s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0;
     int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
     double cm = 0.0;
     for (int i = lane; i < m; i += 32) {
@@ -1276,7 +1427,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
     Layout L;
-    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 8, 4096, 24)) {
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 8, 4096, 64)) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }
@@ -1344,6 +1495,8 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     CK(cudaMemsetAsync(P.sol, 0, (size_t)n * 8, st));
 
     float kernel_ms = 0.f;
+    bool lp_failed = false;
+    const bool verbose = getenv("BLTCU_VERBOSE") != nullptr;
     QCtl acc;  // totals
     memset(&acc, 0, sizeof acc);
     auto add_counts = [&](const QCtl &x) {
@@ -1362,6 +1515,12 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
         kernel_ms += ms;
         launches++;
+        if (hq.fail_info) lp_failed = true;
+        if (hq.fail_info && verbose) {
+            fprintf(stderr, "bltcu: LP failure code %d at level k=%d (basis size %d), u =", hq.fail_info & 255, (hq.fail_info >> 8) & 255, hq.fail_info >> 16);
+            for (int e = ((hq.fail_info >> 8) & 255) - 1; e < n; ++e) fprintf(stderr, " %lld", hq.fail_u[e]);
+            fprintf(stderr, "\n");
+        }
         if (hq.timed_out)
             fprintf(stderr, "bltcu: watchdog fired (where=%d) pending=%d idle=%d head=%u tail=%u fhead=%u ftail=%u found=%d\n",
                     hq.timed_out, hq.pending, hq.idle, hq.head, hq.tail, hq.fhead, hq.ftail, hq.found);
@@ -1414,6 +1573,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         add_counts(hq);
     }
 
+    if (!found && lp_failed && status == BLTCU_STATUS_OK) status = BLTCU_STATUS_LP_FAIL;
     // ---- result: the point found, else the last recorded candidate in DFS order (uhat) ----
     std::vector<int64_t> hsol(n, 0);
     if (found) {
@@ -1581,9 +1741,9 @@ extern "C" const char *bltcu_version(void) { return "blt-b200 0.2 (sm_100a)"; }
 // the fixed array below, which is part of the library image: every GPU that loads libbltcu.so holds these 20 MiB
 // from the moment the library is loaded until the process exits, whether or not this entry point is ever called.
 #define BLTCU_NOALLOC_BYTES (20u << 20)
-#define BLTCU_NOALLOC_WPC 2       // warps per CTA of this variant (fixed so that the level store has a fixed size)
+#define BLTCU_NOALLOC_WPC 1       // warps per CTA of this variant (fixed so that the per-warp stacks have a fixed size)
 #define BLTCU_NOALLOC_CTAS 148    // at most this many CTAs
-#define BLTCU_NOALLOC_POOL 512    // subtree records (power of two)
+#define BLTCU_NOALLOC_POOL 256    // subtree records (power of two)
 #define BLTCU_NOALLOC_ARENA_RECS 6 // private stack of each warp, in units of the largest record
 #define BLTCU_NOALLOC_MAXDEV 64
 
@@ -1725,5 +1885,5 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     if (niter) *niter = hq.niter;
     if (nprune) *nprune = hq.nprune;
     if (found) *found = hq.found;
-    return hq.status;
+    return (hq.status == BLTCU_STATUS_OK && !hq.found && hq.fail_info) ? BLTCU_STATUS_LP_FAIL : hq.status;
 }

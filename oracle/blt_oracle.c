@@ -55,6 +55,9 @@
 #define DIST_EPS 1.0e-4   /* glpk_wrapper.h:13 */
 #define EPS_OPT 1.0e-9    /* optimality tolerance, relative to (|c|_inf + t) */
 #define PIV_TOL 1.0e-11   /* ratio-test pivot threshold, relative to |w|_inf */
+#define HARRIS_DELTA 1.0e-10 /* dual infeasibility the ratio test tolerates */
+#define STALL_MAX 40      /* degenerate steps before the anti-cycling rule takes over */
+#define PIV_REL 1.0e-9    /* preferred pivots are at least this large next to the leaving row's scale */
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
 
@@ -167,7 +170,7 @@ typedef struct {
     int *zrow, *pos;     /* zrow[p] = row held by basic position p >= 1 (-1 = artificial); pos[j] = position or 0 */
     signed char *sg;     /* sign of each active row */
     double *chat, *val, *alpha, *beta, *w, *a, *r, *v;
-    uint64_t pivots, refactors, quick, colds;
+    uint64_t pivots, refactors, quick, colds, repairs;
 } LP;
 
 static LP *lp_new(const Geo *g) {
@@ -209,40 +212,71 @@ static double lp_alpha_beta(LP *lp, int pe) {
     }
     return butterfly32(part);
 }
+/* Sign repair.  The basis Z fixes the dual vector y up to scale; the signs are supposed to be sg_j = sign(n_j . y).  When
+ * round-off has pushed some sg_j*alpha_j below -HARRIS_DELTA those rows are flipped to the other bound: column 0 of A
+ * changes by Delta = sum_flipped -2 sg_j n_j, a rank-one correction of H.  Needs alpha from lp_alpha_beta.  Returns 1
+ * if anything was flipped. */
+static int lp_repair(LP *lp) {
+    const int m = lp->m, qd = lp->qd, ld = lp->ld;
+    int any = 0;
+    for (int j = 0; j < m; ++j) {
+        lp->r[j] = 0.0;
+        if (!lp->pos[j] && (double)lp->sg[j] * lp->alpha[j] < -HARRIS_DELTA) { lp->r[j] = -2.0 * (double)lp->sg[j]; any = 1; }
+    }
+    if (!any) return 0;
+    for (int c = 0; c < qd; ++c) lp->a[c] = dot4(lp->r, 1, lp->g->Qrev + c, m, m);   /* Delta */
+    for (int i = 0; i < qd; ++i) lp->w[i] = dot4(lp->H + (size_t)i * ld, 1, lp->a, 1, qd);
+    const double den = 1.0 + lp->w[0];
+    for (int c = 0; c < qd; ++c) lp->v[c] = lp->H[c];
+    for (int i = 0; i < qd; ++i) {
+        const double f = lp->w[i] / den;
+        double *Hi = lp->H + (size_t)i * ld;
+        for (int c = 0; c < qd; ++c) Hi[c] = fma(-f, lp->v[c], Hi[c]);
+    }
+    for (int j = 0; j < m; ++j) if (lp->r[j] != 0.0) lp->sg[j] = (signed char)-lp->sg[j];
+    lp->repairs++;
+    return 1;
+}
 /* Entering row (Harris two-pass ratio test).  With den_j = -se*sg_j*beta_j and num_j = max(0, sg_j*alpha_j):
- * pass 1: theta_max = min over den_j > dmin of (num_j + HARRIS_DELTA) / den_j;
+ * pass 1: theta_max = min over den_j > dmin of max(0, sg_j*alpha_j + HARRIS_DELTA) / den_j;
  * pass 2: among den_j > dmin with num_j/den_j <= theta_max the largest den_j wins (ties: lowest j).
- * dmin = 0 when a row of Z leaves (its pivot is num+den), PIV_TOL*scale when an artificial leaves (its pivot is den).
+ * dmin = 0; when an artificial leaves its pivot is den itself, and a winner below 1e-3*PIV_TOL*scale is refused.
  * If no row qualifies and a row of Z leaves, the dual vector moves all the way onto the leaving row's own ray, where
  * exactly the rows with beta_j = 0 vanish: take the one with the largest alpha among |beta_j| <= PIV_TOL*scale. */
-#define HARRIS_DELTA 1.0e-10
-static int lp_ratio(LP *lp, int se, int pe) {
+static int lp_ratio(LP *lp, int se, int pe, int bland) {
     const int m = lp->m;
     const int artificial = lp->zrow[pe] < 0;
     double scale = 0.0;
     for (int c = 0; c < lp->qd; ++c) if (fabs(lp->H[(size_t)pe * lp->ld + c]) > scale) scale = fabs(lp->H[(size_t)pe * lp->ld + c]);
     for (int j = 0; j < m; ++j) if (!lp->pos[j] && fabs(lp->beta[j]) > scale) scale = fabs(lp->beta[j]);
-    const double tiny = PIV_TOL * scale, dmin = artificial ? tiny : 0.0;
-    double tmax = INFINITY;
-    for (int j = 0; j < m; ++j) {
-        if (lp->pos[j]) continue;
-        const double den = -(double)(se * lp->sg[j]) * lp->beta[j];
-        if (!(den > dmin)) continue;
-        double num = (double)lp->sg[j] * lp->alpha[j];
-        if (num < 0.0) num = 0.0;
-        const double rt = (num + HARRIS_DELTA) / den;
-        if (rt < tmax) tmax = rt;
-    }
+    const double tiny = PIV_TOL * scale;
     int best = -1; double bd = 0.0;
-    for (int j = 0; j < m; ++j) {
-        if (lp->pos[j]) continue;
-        const double den = -(double)(se * lp->sg[j]) * lp->beta[j];
-        if (!(den > dmin)) continue;
-        double num = (double)lp->sg[j] * lp->alpha[j];
-        if (num < 0.0) num = 0.0;
-        if (num / den <= tmax && den > bd) { bd = den; best = j; }
+    /* tier 0 only accepts pivots that are not tiny next to the row's scale (rows below the bar may then drift a little
+     * below zero, which the bound tolerates); tier 1 accepts any positive pivot */
+    for (int tier = 0; tier < 2 && best < 0; ++tier) {
+        const double dmin = tier == 0 ? PIV_REL * scale : 0.0;
+        double tmax = INFINITY;
+        for (int j = 0; j < m; ++j) {
+            if (lp->pos[j]) continue;
+            const double den = -(double)(se * lp->sg[j]) * lp->beta[j];
+            if (!(den > dmin)) continue;
+            double num = (double)lp->sg[j] * lp->alpha[j] + HARRIS_DELTA; /* rows already below zero get less room, not more */
+            if (num < 0.0) num = 0.0;
+            const double rt = num / den;
+            if (rt < tmax) tmax = rt;
+        }
+        bd = 0.0;
+        for (int j = 0; j < m; ++j) {
+            if (lp->pos[j]) continue;
+            const double den = -(double)(se * lp->sg[j]) * lp->beta[j];
+            if (!(den > dmin)) continue;
+            double num = (double)lp->sg[j] * lp->alpha[j];
+            if (num < 0.0) num = 0.0;
+            if (num / den <= tmax && (bland ? best < 0 : den > bd)) { bd = den; best = j; }
+        }
     }
-    if (best >= 0 || artificial) return best;
+    if (artificial) return (best >= 0 && bd > 1.0e-3 * tiny) ? best : -1;  /* its pivot is den itself: refuse a vanishing one */
+    if (best >= 0) return best;
     double ba = -1.0;
     for (int j = 0; j < m; ++j) {
         if (lp->pos[j] || fabs(lp->beta[j]) > tiny) continue;
@@ -309,7 +343,8 @@ static void lp_extend(LP *lp) {
 static int lp_drop_artificial(LP *lp, int sf) {
     const int pe = lp->qd - 1;
     lp_alpha_beta(lp, pe);
-    const int l = lp_ratio(lp, sf, pe);
+    if (lp_repair(lp)) lp_alpha_beta(lp, pe);
+    const int l = lp_ratio(lp, sf, pe, 0);
     if (l < 0) return -1;
     return lp_replace(lp, pe, l, sf);
 }
@@ -367,13 +402,20 @@ static int lp_solve(LP *lp, double radius, double cmax, double *d_out) {
     lp_values(lp);
     if (lp->val[0] < 0.0) lp_flip(lp);
     const int cap = 100 * m + 1000;
-    int refactored = 0;
+    int refactored = 0, stall = 0, bland = 0;
+    double tbest = -1.0;
     for (int iter = 0;; ++iter) {
         const double t = lp->val[0];
         if (!approximatelyLE(t, radius, DIST_EPS)) { if (iter == 0) lp->quick++; return NODE_PRUNE; }
+        /* degenerate stalling: after STALL_MAX steps without progress switch to lowest-index (Bland) choices */
+        if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= STALL_MAX) bland = 1;
+        const double tol = EPS_OPT * (cmax + t);
         int pe = -1; double vmax = -1.0;
         for (int p = 1; p < qd; ++p) if (fabs(lp->val[p]) > vmax) { vmax = fabs(lp->val[p]); pe = p; }
-        const double tol = EPS_OPT * (cmax + t);
+        if (bland && pe >= 0 && vmax > t + tol) { /* the violated basic row with the lowest row index */
+            int br = -1;
+            for (int p = 1; p < qd; ++p) if (fabs(lp->val[p]) > t + tol && (br < 0 || lp->zrow[p] < br)) { br = lp->zrow[p]; pe = p; }
+        }
         if (pe < 0 || vmax <= t + tol) {
             /* optimal by the books: verify the vertex against the data before trusting it */
             const int nv = qd < m ? qd + 1 : qd;
@@ -391,7 +433,12 @@ static int lp_solve(LP *lp, double radius, double cmax, double *d_out) {
         if (iter >= cap) return NODE_FAIL;
         const int se = lp->val[pe] > 0.0 ? 1 : -1;
         const double nrm1 = lp_alpha_beta(lp, pe);
-        if (fabs(nrm1 - 1.0) > 1.0e-6) { /* the dual vector has drifted */
+        if (lp_repair(lp)) { /* the vertex moved a little: price again */
+            lp_values(lp);
+            if (lp->val[0] < 0.0) lp_flip(lp);
+            continue;
+        }
+        if (fabs(nrm1 - 1.0) > 1.0e-5) { /* the dual vector has drifted */
             if (refactored) return NODE_FAIL;
             refactored = 1;
             if (lp_refactor(lp)) return NODE_FAIL;
@@ -399,10 +446,35 @@ static int lp_solve(LP *lp, double radius, double cmax, double *d_out) {
             if (lp->val[0] < 0.0) lp_flip(lp);
             continue;
         }
-        const int l = lp_ratio(lp, se, pe);
+        const int l = lp_ratio(lp, se, pe, bland);
         if (l < 0) return NODE_FAIL;
         if (lp_replace(lp, pe, l, se)) return NODE_FAIL;
         lp_values(lp);
+    }
+}
+
+/* lp_solve preceded by the removal of a fresh coordinate's artificial column (art = its sign, 0 = none) */
+static int lp_solve_art(LP *lp, double radius, double cmax, double *d_out, int art) {
+    if (art && lp_drop_artificial(lp, art)) return NODE_FAIL;
+    return lp_solve(lp, radius, cmax, d_out);
+}
+/* Last resort after a failed warm start: rebuild the vertex of LP(m - qd) coordinate by coordinate from nothing, each
+ * intermediate problem solved to optimality.  lp->chat must hold all qd entries. */
+static int lp_cold_solve(LP *lp, int qd, double radius, double cmax, double *d_out) {
+    if (lp_init1(lp)) return NODE_FAIL;
+    int status = NODE_FAIL;
+    for (;;) {
+        int art = 0; double rad = radius;
+        if (lp->qd < qd) {
+            lp_extend(lp);
+            lp_values(lp);
+            art = lp->val[lp->qd - 1] > 0.0 ? 1 : -1;
+            if (lp->qd < qd) rad = INFINITY;
+        }
+        status = lp_solve_art(lp, rad, cmax, d_out, art);
+        if (status == NODE_FAIL) return NODE_FAIL;
+        if (lp->qd == qd) return status;
+        if (status != NODE_EXPLORE) return NODE_FAIL;
     }
 }
 
@@ -579,24 +651,21 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
             const int dir = sgn(xc[k] - (double)u[k - 1]);
             side = dir > 0 ? 0 : 1;
             const double clast = fma(-(double)u[k - 1], g.Rm[(size_t)kk * n + kk], gbase[k]);
+            int art = 0;
             if (!ch[k][side].init) {
                 if (qd == 1) {
                     if (lp_init1(lp)) { rc = BLT_STATUS_LP_FAIL; goto done; }
-                    lp->chat[0] = clast;
                 } else {
                     chain_load(lp, &ch[k + 1][curside[k + 1]], qd - 1);
                     lp_extend(lp);
-                    memcpy(lp->chat, chatL[k], (qd - 1) * sizeof(double));
-                    lp->chat[qd - 1] = clast;
-                    if (lp_drop_artificial(lp, dir)) { rc = BLT_STATUS_LP_FAIL; goto done; }
+                    art = dir;
                 }
                 ch[k][side].init = 1;
-            } else {
-                chain_load(lp, &ch[k][side], qd);
-                memcpy(lp->chat, chatL[k], (qd - 1) * sizeof(double));
-                lp->chat[qd - 1] = clast;
-            }
-            status = lp_solve(lp, radius, cmax, &d);
+            } else chain_load(lp, &ch[k][side], qd);
+            memcpy(lp->chat, chatL[k], (qd - 1) * sizeof(double));
+            lp->chat[qd - 1] = clast;
+            status = lp_solve_art(lp, radius, cmax, &d, art);
+            if (status == NODE_FAIL) status = lp_cold_solve(lp, qd, radius, cmax, &d); /* warm start went bad: from scratch */
             if (status == NODE_FAIL) { rc = BLT_STATUS_LP_FAIL; goto done; }
             chain_store(&ch[k][side], lp);
             if (status == NODE_EXPLORE) { /* real centre of the next level: x_{kk-1} of the optimum */
