@@ -55,7 +55,8 @@ def workload_config(wl):
     return {"workload": f"dense UNSAT BILP n={wl['n']} m={wl['m']} |a|<=100 width={wl['w']} seed={wl['seed']}, "
                         "LLL-reduced, exhaustive enumeration",
             "fixture": "tests/golden/bench_dense60.npz",
-            "l2": "L2 flushed (256 MiB write) between timed steps; the per-warp level store (~0.9 GB) also exceeds L2"}
+            "l2": "L2 flushed (256 MiB write) between timed steps; inputs are 29 KB, the search's own scratch (per-warp record stacks, "
+                  "several GB) exceeds L2"}
 
 
 class ClockSampler(threading.Thread):
@@ -239,7 +240,7 @@ def main():
                 "niter": int(niter_all), "nprune": int(nprune_all), "nodes_per_step": nodes_all / args.steps,
                 "time_to_decision_ms": kernel_ms_max / args.steps, "wall_ms_per_step": 1e3 * wall_s / args.steps,
                 "pivots_per_node": last["pivots"] / max(1, last["nodes"]), "donated": last["donated"],
-                "warps": last["warps"],
+                "warps": last["warps"], "busy_frac": last["busy_frac"],
                 "e2e": {"value": e2e_nodes_all / e2e_s_max, "unit": UNIT, "h2d_bytes_per_step": (n * m + 2 * m) * 8,
                         "d2h_bytes_per_step": n * 8 + 1024},
                 "gpu_launches": int(launches_all),

@@ -46,7 +46,7 @@
 #define PIV_REL 1.0e-9
 #define STALL_MAX 40
 #define MAXD BLTCU_MAX_DIM
-#define QS_MAX 32  // largest basis kept in shared memory
+#define QS_MAX 24  // largest basis kept in shared memory (larger ones live in the per-warp global buffers)
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
 enum { REC_TOP = 1, REC_CONT = 2 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
@@ -249,44 +249,53 @@ __device__ __forceinline__ void warp_argmax(double &v, int &idx) {
 // ---- geometry: B^T = Q R by Gram-Schmidt applied twice, one warp (twin of geo_build in the oracle) ------------
 __device__ __forceinline__ double treedot_g(const double *a, const double *b, int len, int lane) {
     double acc = 0.0;
+#pragma unroll 1
     for (int e = lane; e < len; e += 32) acc = fma(a[e], b[e], acc);
     return butterfly(acc);
 }
 __device__ int geo_build_warp(const double *B, const double *p, int n, int m, double *Q, double *Qrev, double *Rm,
                               double *QTp, double *v, double *coef, int lane) {
+#pragma unroll 1
     for (int e = lane; e < n * n; e += 32) Rm[e] = 0.0;
     __syncwarp();
     for (int t = 0; t < m; ++t) {
         if (t < n) { for (int e = lane; e < m; e += 32) v[e] = B[(size_t)t * m + e]; }
         else {  // completion: the unit vector with the largest part outside the current span (ties: lowest j)
             int best = -1; double bv = -1.0;
+#pragma unroll 1
             for (int j = lane; j < m; j += 32) {
                 double sres = 1.0;
                 for (int i = 0; i < t; ++i) { const double x = Q[(size_t)i * m + j]; sres = fma(-x, x, sres); }
                 if (sres > bv) { bv = sres; best = j; }
             }
             warp_argmax(bv, best);
+#pragma unroll 1
             for (int e = lane; e < m; e += 32) v[e] = (e == best) ? 1.0 : 0.0;
         }
+#pragma unroll 1
         for (int e = lane; e < m; e += 32) coef[e] = 0.0;
         __syncwarp();
         for (int pass = 0; pass < 2; ++pass)
             for (int j = 0; j < t; ++j) {
                 const double *qj = Q + (size_t)j * m;
                 const double h = treedot_g(qj, v, m, lane);
+#pragma unroll 1
                 for (int e = lane; e < m; e += 32) v[e] = fma(-h, qj[e], v[e]);
                 if (lane == 0) coef[j] += h;
                 __syncwarp();
             }
         const double nrm = sqrt(treedot_g(v, v, m, lane));
         if (!(nrm > 0.0)) return -1;
+#pragma unroll 1
         for (int e = lane; e < m; e += 32) Q[(size_t)t * m + e] = v[e] / nrm;
         if (t < n) {
+#pragma unroll 1
             for (int j = lane; j < t; j += 32) Rm[(size_t)j * n + t] = coef[j];
             if (lane == 0) Rm[(size_t)t * n + t] = nrm;
         }
         __syncwarp();
     }
+#pragma unroll 1
     for (int e = lane; e < m * m; e += 32) { const int j = e / m, i = e - j * m; Qrev[e] = Q[(size_t)(m - 1 - i) * m + j]; }
     for (int t = 0; t < m; ++t) { const double x = treedot_g(Q + (size_t)t * m, p, m, lane); if (lane == 0) QTp[t] = x; }
     __syncwarp();
@@ -296,6 +305,7 @@ __device__ int geo_build_warp(const double *B, const double *p, int n, int m, do
 // ---- LP engine (twin of the oracle's lp_* functions) -----------------------------------------------------------
 __device__ __forceinline__ void lp_values(WS &s) {
     const int qd = s.qd;
+#pragma unroll 1
     for (int p = s.lane; p < qd; p += 32) {
         const double *Hp = s.W + (size_t)p * s.LD, *ch = s.chat;
         s.val[p] = dot4(qd, [&](int e) { return Hp[e]; }, [&](int e) { return ch[e]; });
@@ -303,7 +313,9 @@ __device__ __forceinline__ void lp_values(WS &s) {
     __syncwarp();
 }
 __device__ __forceinline__ void lp_flip(WS &s) {
+#pragma unroll 1
     for (int c = s.lane; c < s.qd; c += 32) s.W[c] = -s.W[c];
+#pragma unroll 1
     for (int j = s.lane; j < s.m; j += 32) s.sg[j] = (signed char)-s.sg[j];
     if (s.lane == 0) s.val[0] = -s.val[0];
     __syncwarp();
@@ -337,25 +349,30 @@ __device__ __forceinline__ int lp_repair(WS &s) {
     }
     if (!__any_sync(FULLMASK, any)) return 0;
     __syncwarp();
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) {
         const double *r = s.r, *Qc = s.Qs + c;
         const int LDQ = s.LDQ;
         s.a[c] = dot4(m, [&](int e) { return r[e]; }, [&](int e) { return Qc[(size_t)e * LDQ]; });
     }
     __syncwarp();
+#pragma unroll 1
     for (int i = s.lane; i < qd; i += 32) {
         const double *Hi = s.W + (size_t)i * LD, *a = s.a;
         s.w[i] = dot4(qd, [&](int e) { return Hi[e]; }, [&](int e) { return a[e]; });
     }
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) s.v[c] = s.W[c];
     __syncwarp();
     const double den = 1.0 + s.w[0];
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) {
         const double vc = s.v[c];
         double *Hc = s.W + c;
 #pragma unroll 1
         for (int i = 0; i < qd; ++i) { const double f = s.w[i] / den; Hc[(size_t)i * LD] = fma(-f, vc, Hc[(size_t)i * LD]); }
     }
+#pragma unroll 1
     for (int j = s.lane; j < m; j += 32) if (s.r[j] != 0.0) s.sg[j] = (signed char)-s.sg[j];
     __syncwarp();
     s.repairs++;
@@ -419,6 +436,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
     if (e >= 0) { for (int c = s.lane; c < qd; c += 32) Hp[c] = Hp[c] - (double)se * H[c]; }
     __syncwarp();
     const double *nl = s.Qs + (size_t)l * s.LDQ;
+#pragma unroll 1
     for (int i = s.lane; i < qd; i += 32) {
         const double *Hi = H + (size_t)i * LD;
         s.w[i] = dot4(qd, [&](int c) { return Hi[c]; }, [&](int c) { return nl[c]; });
@@ -426,6 +444,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
     __syncwarp();
     const double wp = s.w[pe];
     if (wp == 0.0) return -1;
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) s.v[c] = Hp[c] / wp;
     __syncwarp();
     if (qd <= 32) {  // one lane per column, rows in a loop: same arithmetic, no index division
@@ -435,6 +454,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
             for (int i = 0; i < qd; ++i) if (i != pe) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
         }
     } else {
+#pragma unroll 1
         for (int x = s.lane; x < qd * qd; x += 32) {
             const int i = x / qd, c = x - i * qd;
             if (i != pe) H[(size_t)i * LD + c] = fma(-s.w[i], s.v[c], H[(size_t)i * LD + c]);
@@ -442,6 +462,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
     }
     __syncwarp();
     const double sl = (double)s.sg[l];
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) Hp[c] = s.v[c] + sl * H[c];
     __syncwarp();
     if (s.lane == 0) {
@@ -455,6 +476,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
 __device__ __forceinline__ int lp_init1(WS &s) {
     const int m = s.m;
     double part = 0.0;
+#pragma unroll 1
     for (int j = s.lane; j < m; j += 32) {
         const double x = s.Qs[(size_t)j * s.LDQ];
         s.sg[j] = x >= 0.0 ? 1 : -1; s.pos[j] = 0;
@@ -471,15 +493,19 @@ __device__ __forceinline__ int lp_init1(WS &s) {
 __device__ __forceinline__ void lp_extend(WS &s) {
     const int m = s.m, qd = s.qd, LD = s.LD;
     double part = 0.0;
+#pragma unroll 1
     for (int j = s.lane; j < m; j += 32) if (!s.pos[j]) part = fma((double)s.sg[j], s.Qs[(size_t)j * s.LDQ + qd], part);
     const double a0 = butterfly(part);
     if (s.lane == 0) s.a[0] = a0;
+#pragma unroll 1
     for (int p = 1 + s.lane; p < qd; p += 32) s.a[p] = s.Qs[(size_t)s.zrow[p] * s.LDQ + qd];
     __syncwarp();
+#pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) {
         const double *a = s.a, *Hc = s.W + c;
         s.W[(size_t)qd * LD + c] = -dot4(qd, [&](int e) { return a[e]; }, [&](int e) { return Hc[(size_t)e * LD]; });
     }
+#pragma unroll 1
     for (int p = s.lane; p < qd; p += 32) s.W[(size_t)p * LD + qd] = 0.0;
     if (s.lane == 0) { s.W[(size_t)qd * LD + qd] = 1.0; s.zrow[qd] = -1; }
     s.qd = qd + 1;
@@ -542,8 +568,10 @@ __device__ __forceinline__ int lp_refactor(WS &s) {
 __device__ __forceinline__ void lp_image(WS &s, int nv) {
     const int m = s.m;
     const double t = s.val[0];
+#pragma unroll 1
     for (int j = s.lane; j < m; j += 32) s.r[j] = s.pos[j] ? s.val[s.pos[j]] : (double)s.sg[j] * t;
     __syncwarp();
+#pragma unroll 1
     for (int i = s.lane; i < nv; i += 32) {
         const double *Qi = s.Qs + i, *r = s.r;
         const int LDQ = s.LDQ;
@@ -576,10 +604,12 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
             if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= STALL_MAX) bland = true;
             const double tol = EPS_OPT * (cmax + t);
             pe = -1; double vmax = -1.0;
+#pragma unroll 1
             for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
             warp_argmax(vmax, pe);
             if (bland && pe >= 0 && vmax > t + tol) {  // the violated basic row with the lowest row index
                 int bp = -1; double key = 0.0;
+#pragma unroll 1
                 for (int p = 1 + s.lane; p < qd; p += 32)
                     if (fabs(s.val[p]) > t + tol && (bp < 0 || -(double)s.zrow[p] > key)) { key = -(double)s.zrow[p]; bp = p; }
                 warp_argmax(key, bp);
@@ -589,6 +619,7 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
                 const int nv = qd < m ? qd + 1 : qd;
                 lp_image(s, nv);
                 double err = 0.0;
+#pragma unroll 1
                 for (int i = s.lane; i < qd; i += 32) { const double e = fabs(s.v[i] - s.chat[i]); err = e > err ? e : err; }
                 err = warp_max(err);
                 if (err <= 1.0e-8 * ((double)m * cmax + t)) { d_out = t; return NODE_EXPLORE; }
@@ -637,18 +668,25 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
 // chain head: H (q x q packed), basic rows (q ints), signs (m bytes)
 __device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, signed char *dB) {
     const int q = s.qd, LD = s.LD;
+#pragma unroll 1
     for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; dH[x] = s.W[(size_t)i * LD + c]; }
+#pragma unroll 1
     for (int p = s.lane; p < q; p += 32) dI[p] = s.zrow[p];
+#pragma unroll 1
     for (int j = s.lane; j < s.m; j += 32) dB[j] = s.sg[j];
 }
 // loads a q x q head into the working matrix
 __device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *dI, const signed char *dB, int q) {
     const int LD = s.LD;
     s.qd = q;
+#pragma unroll 1
     for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
+#pragma unroll 1
     for (int j = s.lane; j < s.m; j += 32) { s.sg[j] = dB[j]; s.pos[j] = 0; }
+#pragma unroll 1
     for (int p = s.lane; p < q; p += 32) s.zrow[p] = dI[p];
     __syncwarp();
+#pragma unroll 1
     for (int p = 1 + s.lane; p < q; p += 32) if (s.zrow[p] >= 0) s.pos[s.zrow[p]] = (unsigned char)p;
     __syncwarp();
 }
@@ -696,6 +734,7 @@ __device__ __forceinline__ void ring_push(QCtl *q, unsigned int *tail, int *ring
 // exact check, closest.cc:330-340 (int64 products wrap like the reference's)
 __device__ bool check_soln_dev(const Params &P, const long long *u, int lane) {
     bool ok = true;
+#pragma unroll 1
     for (int j = lane; j < P.m; j += 32) {
         unsigned long long z = 0;
         for (int i = 0; i < P.n; ++i) z += (unsigned long long)u[i] * (unsigned long long)P.lat[(size_t)i * P.m + j];
@@ -732,6 +771,7 @@ __device__ __forceinline__ void use_side(WS &s, int side) {
 __device__ __forceinline__ void copy_words(void *dst, const void *src, size_t bytes, int lane) {  // bytes % 8 == 0
     unsigned long long *d = (unsigned long long *)dst;
     const unsigned long long *s = (const unsigned long long *)src;
+#pragma unroll 1
     for (size_t i = lane; i < bytes / 8; i += 32) d[i] = s[i];
 }
 // writes the record of an explored child (children level k-1) whose vertex is the current working state
@@ -739,8 +779,11 @@ __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL
                                             double gn) {
     const int n = P.n, m = P.m, lane = s.lane, qd = s.qd;
     if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gn; ((int *)C)[6] = 0; ((int *)C)[7] = 0; }
+#pragma unroll 1
     for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
+#pragma unroll 1
     for (int j = lane; j < m; j += 32) ((double *)(C + RL.off_cpar))[j] = s.c[j];
+#pragma unroll 1
     for (int e = lane; e < qd; e += 32) ((double *)(C + RL.off_chat))[e] = s.chat[e];
     if (k - 1 > 1) chain_store(s, (double *)(C + RL.off_H), (int *)(C + RL.off_zrow), (signed char *)(C + RL.off_sg));
     __syncwarp();
@@ -762,12 +805,17 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     const int kk = k0 - 1, qd0 = m - kk, qpar = m - k0;
 
     // ---- take what is needed out of the record; afterwards the record is dead ----
+#pragma unroll 1
     for (int e = lane; e < n; e += 32) { s.u[e] = ((const long long *)(R + RL.off_u))[e]; s.ord[e] = (R + RL.off_ord)[e]; }
+#pragma unroll 1
     for (int j = lane; j < m; j += 32) s.cpar[j] = ((const double *)(R + RL.off_cpar))[j];
     if (qpar > 0 && k0 > 1) {
         copy_words(s.Wpar, R + RL.off_H, (size_t)qpar * qpar * 8, lane);
+#pragma unroll 1
         for (int p = lane; p < qpar; p += 32) s.pzrow[p] = ((const int *)(R + RL.off_zrow))[p];
+#pragma unroll 1
         for (int j = lane; j < m; j += 32) s.psg[j] = ((const signed char *)(R + RL.off_sg))[j];
+#pragma unroll 1
         for (int e = lane; e < qpar; e += 32) s.chat[e] = ((const double *)(R + RL.off_chat))[e];
     }
     if (is_cont) {
@@ -788,6 +836,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
 
     double d = 0.0, xlast = 0.0;
     // ---- constants of this level ----
+#pragma unroll 1
     for (int j = lane; j < m; j += 32) s.brow[j] = P.B[(size_t)kk * m + j];
     const double Rkk = P.Rm[(size_t)kk * n + kk];
     double Rk1 = 1.0, Rk1k = 0.0, g2 = 0.0;
@@ -795,6 +844,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         const double *Rr = P.Rm + (size_t)(kk - 1) * n;
         Rk1 = Rr[kk - 1]; Rk1k = Rr[kk];
         double part = 0.0;
+#pragma unroll 1
         for (int i = kk + 1 + lane; i < n; i += 32) part = fma(-(double)s.u[i], Rr[i], part);
         g2 = P.QTp[kk - 1] + butterfly(part);
     }
@@ -823,6 +873,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         double cmax = 0.0;
         {
             const double mu = -(double)ucur;
+#pragma unroll 1
             for (int j = lane; j < m; j += 32) { const double cj = fma(mu, s.brow[j], s.cpar[j]); s.c[j] = cj; const double a = fabs(cj); cmax = a > cmax ? a : cmax; }
             cmax = warp_max(cmax);
             __syncwarp();
@@ -935,6 +986,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                     newer = cmp >= 0;
                 }
                 if (newer) {
+#pragma unroll 1
                     for (int e = lane; e < n; e += 32) { bk[e] = s.ord[e]; bu[e] = s.u[e]; }
                     if (lane == 0) P.best_valid[gwarp] = 1;
                 }
@@ -945,6 +997,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 if (lane == 0) won = (atomicCAS(&P.q->found, 0, 1) == 0);
                 won = __shfl_sync(FULLMASK, won, 0);
                 if (won) {
+#pragma unroll 1
                     for (int e = lane; e < n; e += 32) P.sol[e] = s.u[e];
                     __threadfence();
                 }
@@ -979,8 +1032,11 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 ((int *)C)[0] = k0; ((int *)C)[1] = (is_top ? REC_TOP : 0) | REC_CONT; ((double *)C)[1] = xc0; ((double *)C)[2] = gb;
                 ((int *)C)[6] = step; ((int *)C)[7] = (pruned ? 1 : 0) | (inited << 1); ((int *)C)[8] = (int)CL.bytes;
             }
+#pragma unroll 1
             for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
+#pragma unroll 1
             for (int j = lane; j < m; j += 32) { ((double *)(C + RL.off_cpar))[j] = s.cpar[j]; ((signed char *)(C + RL.off_sg))[j] = s.psg[j]; }
+#pragma unroll 1
             for (int e = lane; e < qpar; e += 32) { ((double *)(C + RL.off_chat))[e] = s.chat[e]; ((int *)(C + RL.off_zrow))[e] = s.pzrow[e]; }
             if (qpar > 0) copy_words(C + RL.off_H, s.Wpar, (size_t)qpar * qpar * 8, lane);
             for (int side = 0; side < 2; ++side) {
@@ -1041,7 +1097,7 @@ __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS)
 // ------------------------------------------------------------------------------------------------------------
 // The persistent kernel
 // ------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
+__global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     extern __shared__ __align__(16) double smem[];
     const int n = P.n, m = P.m;
     double *Qs = smem;
@@ -1066,6 +1122,7 @@ __global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
     s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
     use_side<false>(s, 0);
+#pragma unroll 1
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     Arena A;
     A.base = P.arena + (size_t)gwarp * P.arena_stride;
@@ -1160,6 +1217,7 @@ __global__ void __launch_bounds__(256, 1) bltcu_search_kernel(const Params P) {
         atomicAdd(&q->idle_ns, t_idle); atomicAdd(&q->busy_ns, t_busy);
     }
     __syncwarp();
+#pragma unroll 1
     for (int e = lane; e <= n; e += 32) if (hist[e]) atomicAdd(&q->hist[e], (unsigned long long)hist[e]);
 }
 
@@ -1174,7 +1232,9 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
     extern __shared__ __align__(16) double smem[];
     const int lane = threadIdx.x;
     if (lane == 0) *now = gtimer();
+#pragma unroll 1
     for (int e = lane; e < n * m; e += 32) B[e] = (double)lat[e];                                 // closest.cc:203
+#pragma unroll 1
     for (int j = lane; j < m; j += 32) p[j] = (double)(con[2 * j + 1] + con[2 * j]) / 2.0;        // closest.cc:180-185
     __syncwarp();
     int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
@@ -1190,11 +1250,14 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
         const int qpar = m - n;
         unsigned long long *cnt_out = now + 2;  // pivots, cold starts, refactorisations, quick prunes of this solve
         double cm = 0.0, d = 0.0, vq = 0.0;
+#pragma unroll 1
         for (int j = lane; j < m; j += 32) { const double a = fabs(p[j]); cm = a > cm ? a : cm; }
         cm = warp_max(cm);
+#pragma unroll 1
         for (size_t i = lane; i < RL.stride / 8; i += 32) ((unsigned long long *)rec)[i] = 0ull;
         __syncwarp();
         if (qpar > 0) {
+#pragma unroll 1
             for (int i = lane; i < qpar; i += 32) s.chat[i] = QTp[m - 1 - i];
             __syncwarp();
             r = lp_init1(s);
@@ -1206,6 +1269,7 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
             if (r == 0 && lp_solve(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
             if (r == 0) {
                 vq = s.v[qpar];
+#pragma unroll 1
                 for (int e = lane; e < qpar; e += 32) ((double *)(rec + RL.off_chat))[e] = s.chat[e];
                 chain_store(s, (double *)(rec + RL.off_H), (int *)(rec + RL.off_zrow), (signed char *)(rec + RL.off_sg));
             }
@@ -1214,6 +1278,7 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
             const double gb = QTp[n - 1];
             const double xlast = (gb - vq) / Rm[(size_t)(n - 1) * n + (n - 1)];
             if (lane == 0) { ((int *)rec)[0] = n; ((int *)rec)[1] = REC_TOP; ((double *)rec)[1] = xlast; ((double *)rec)[2] = gb; }
+#pragma unroll 1
             for (int j = lane; j < m; j += 32) ((double *)(rec + RL.off_cpar))[j] = p[j];
         }
         if (lane == 0) { cnt_out[0] = s.pivots; cnt_out[1] = s.colds; cnt_out[2] = s.refactors; cnt_out[3] = s.quick; }
@@ -1241,6 +1306,7 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
     s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0;
     int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
     double cm = 0.0;
+#pragma unroll 1
     for (int i = lane; i < m; i += 32) {
         double rhs1 = 0.0;
         for (int j = k; j < n; ++j) rhs1 += (double)(-u[j]) * B[(size_t)j * m + i];
@@ -1255,6 +1321,7 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
     if (k == 0) d = cm;
     else if (r == 0) {
         if (qd > 0) {
+#pragma unroll 1
             for (int i = lane; i < qd; i += 32) {
                 const double *Qi = Qrev + i, *c = s.c;
                 s.chat[i] = dot4(m, [&](int e) { return Qi[(size_t)e * m]; }, [&](int e) { return c[e]; });
@@ -1269,6 +1336,7 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
             if (r == 0 && lp_solve(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
             if (r == 0) {
                 const double t = s.val[0];
+#pragma unroll 1
                 for (int j = lane; j < m; j += 32) s.r[j] = s.pos[j] ? s.val[s.pos[j]] : (double)s.sg[j] * t;
                 __syncwarp();
             }
@@ -1427,7 +1495,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
     Layout L;
-    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 8, 4096, 64)) {
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 12, 4096, 64)) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }

@@ -1,0 +1,54 @@
+"""One process per GPU: every rank searches its share of the deterministic static split (bltcu_opts.rank/world) and the
+counters are summed at the end.  No collective on the data path; torch.distributed is plumbing.
+
+    res = blt_b200.dist.closest_sharded(lat, con)   # inside a torchrun / init_process_group context
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+def reduce_results(local: dict, n: int, group=None, device=None) -> dict:
+    """All-reduces the per-rank statistics of one sharded search.  `local` is the dict returned by blt_b200.closest();
+    works with the nccl backend (device tensors) and with gloo (CPU tensors, used by the CPU tests)."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return dict(local)
+    dev = device if device is not None else ("cuda" if dist.get_backend(group) == "nccl" else "cpu")
+    hist = np.zeros(n + 1, dtype=np.float64)
+    hist[: len(local["hist"])] = np.asarray(local["hist"], dtype=np.float64)
+    sums = torch.tensor([float(local["niter"]), float(local["nprune"]), float(local["nodes"]), float(local["pivots"]),
+                         float(local.get("donated", 0))] + hist.tolist(), dtype=torch.float64, device=dev)
+    maxs = torch.tensor([float(local["kernel_ms"]), float(local["rc"]), 1.0 if local["found"] else 0.0],
+                        dtype=torch.float64, device=dev)
+    dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(maxs, op=dist.ReduceOp.MAX, group=group)
+    # the solution comes from the lowest rank that found one
+    rank = dist.get_rank(group)
+    finder = torch.tensor([rank if local["found"] else world], dtype=torch.int64, device=dev)
+    dist.all_reduce(finder, op=dist.ReduceOp.MIN, group=group)
+    sol = torch.from_numpy(np.asarray(local["sol"], dtype=np.int64).copy()).to(dev)
+    if int(finder.item()) < world:
+        dist.broadcast(sol, src=dist.get_global_rank(group, int(finder.item())) if group is not None else int(finder.item()),
+                       group=group)
+    s = sums.cpu().numpy()
+    out = dict(local)
+    out.update(niter=int(s[0]), nprune=int(s[1]), nodes=int(s[2]), pivots=int(s[3]), donated=int(s[4]),
+               hist=s[5:].astype(np.uint64), kernel_ms=float(maxs[0].item()), rc=int(maxs[1].item()),
+               found=bool(maxs[2].item() > 0), sol=sol.cpu().numpy())
+    return out
+
+
+def closest_sharded(lat, con, split_depth: int = 8, **opts) -> dict:
+    """closest() of libblt/closest.h:50-54 over all ranks of the default process group (one GPU each)."""
+    import torch.distributed as dist
+
+    import blt_b200
+
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    local = blt_b200.closest(lat, con, rank=rank, world=world, split_depth=split_depth if world > 1 else 0, **opts)
+    return reduce_results(local, np.asarray(lat).shape[0])
