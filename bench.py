@@ -35,7 +35,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-FIXTURE = os.path.join(ROOT, "tests", "golden", "bench_dense60.npz")
+FIXTURE = os.path.join(ROOT, "tests", "golden", os.environ.get("BLT_BENCH_FIXTURE", "bench_dense60_w120.npz"))
 METRIC = "enum_nodes_per_s"
 UNIT = "nodes/s"
 
@@ -48,13 +48,13 @@ def f_alg(k: int, m: int) -> float:
 def load_workload():
     z = np.load(FIXTURE)
     return dict(lat=z["lat"].astype(np.int64), con=z["con"].astype(np.int64), w=int(z["w"]), seed=int(z["seed"]),
-                n=int(z["lat"].shape[0]), m=int(z["lat"].shape[1]))
+                n=int(z["lat"].shape[0]), m=int(z["lat"].shape[1]), nodes_expected=int(z["nodes"]))
 
 
 def workload_config(wl):
     return {"workload": f"dense UNSAT BILP n={wl['n']} m={wl['m']} |a|<=100 width={wl['w']} seed={wl['seed']}, "
                         "LLL-reduced, exhaustive enumeration",
-            "fixture": "tests/golden/bench_dense60.npz",
+            "fixture": "tests/golden/" + os.path.basename(FIXTURE), "nodes_expected": wl["nodes_expected"],
             "l2": "L2 flushed (256 MiB write) between timed steps; inputs are 29 KB, the search's own scratch (per-warp record stacks, "
                   "several GB) exceeds L2"}
 
@@ -162,7 +162,7 @@ def main():
     lat_d = lat_h.cuda(non_blocking=False)
     con_d = con_h.cuda(non_blocking=False)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    opts = dict(device=local_rank, rank=rank, world=world, split_depth=(8 if world > 1 else 0), timeout_ms=600000)
+    opts = dict(device=local_rank, rank=rank, world=world, split_depth=(6 if world > 1 else 0), timeout_ms=600000)
 
     def barrier():
         torch.cuda.synchronize()
@@ -177,6 +177,8 @@ def main():
         if r["rc"] != 0:
             raise SystemExit(f"bench.py: search failed with status {r['rc']}")
         return r
+
+    expected_nodes = wl["nodes_expected"]
 
     def step_e2e():
         flush.zero_()
@@ -241,6 +243,7 @@ def main():
                 "time_to_decision_ms": kernel_ms_max / args.steps, "wall_ms_per_step": 1e3 * wall_s / args.steps,
                 "pivots_per_node": last["pivots"] / max(1, last["nodes"]), "donated": last["donated"],
                 "warps": last["warps"], "busy_frac": last["busy_frac"],
+                "count_ok": bool(int(round(nodes_all / args.steps)) == expected_nodes),
                 "e2e": {"value": e2e_nodes_all / e2e_s_max, "unit": UNIT, "h2d_bytes_per_step": (n * m + 2 * m) * 8,
                         "d2h_bytes_per_step": n * 8 + 1024},
                 "gpu_launches": int(launches_all),

@@ -1285,6 +1285,14 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
     }
     if (lane == 0) *rc = r;
 }
+// static split: collects the path keys of the published subtrees into one contiguous buffer (one copy to the host)
+__global__ void bltcu_gather_keys_kernel(const unsigned char *pool, size_t stride, size_t off_ord, const int *out_list,
+                                         int count, int n, unsigned char *keys) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count * n) return;
+    const int r = i / n, e = i - r * n;
+    keys[i] = pool[(size_t)out_list[r] * stride + off_ord + (n - 1 - e)];  // top level first
+}
 __global__ void bltcu_check_kernel(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok) {
     Params P; P.n = n; P.m = m; P.lat = lat; P.con = con;
     const bool r = check_soln_dev(P, (const long long *)u, threadIdx.x & 31);
@@ -1613,9 +1621,18 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         if (hq.out_count) CK(cudaMemcpy(out.data(), P.out_list, (size_t)hq.out_count * 4, cudaMemcpyDeviceToHost));
         // order the collected subtrees by their path (DFS order) so that every rank deals the same hands
         std::vector<std::vector<unsigned char>> keys(out.size(), std::vector<unsigned char>(n));
-        for (size_t i = 0; i < out.size(); ++i) {
-            CK(cudaMemcpy(keys[i].data(), P.pool + (size_t)out[i] * RL.stride + RL.off_ord, n, cudaMemcpyDeviceToHost));
-            std::reverse(keys[i].begin(), keys[i].end());  // top level first
+        if (!out.empty()) {
+            // the per-warp buffers are idle between the two phases: borrow them for the gathered keys
+            unsigned char *dkeys = (unsigned char *)P.wbuf;
+            if ((size_t)out.size() * n > (size_t)nwarps * P.wbuf_stride * 8) return BLTCU_STATUS_ERROR;
+            const int total = (int)out.size() * n;
+            bltcu_gather_keys_kernel<<<(total + 255) / 256, 256, 0, st>>>(P.pool, RL.stride, RL.off_ord, P.out_list, (int)out.size(), n, dkeys);
+            CK(cudaGetLastError());
+            std::vector<unsigned char> flat((size_t)total);
+            CK(cudaMemcpyAsync(flat.data(), dkeys, (size_t)total, cudaMemcpyDeviceToHost, st));
+            CK(cudaStreamSynchronize(st));
+            launches++;
+            for (size_t i = 0; i < out.size(); ++i) keys[i].assign(flat.begin() + i * n, flat.begin() + (i + 1) * n);
         }
         std::vector<int> idx(out.size());
         for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;

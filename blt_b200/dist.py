@@ -42,7 +42,7 @@ def reduce_results(local: dict, n: int, group=None, device=None) -> dict:
     return out
 
 
-def closest_sharded(lat, con, split_depth: int = 8, **opts) -> dict:
+def closest_sharded(lat, con, split_depth: int = 6, **opts) -> dict:
     """closest() of libblt/closest.h:50-54 over all ranks of the default process group (one GPU each)."""
     import torch.distributed as dist
 

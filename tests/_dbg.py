@@ -1,8 +1,6 @@
 import sys; sys.path.insert(0,'.')
-import numpy as np, oracle, blt_b200
-from oracle import bltio, context
-for name in ("test_95","test_50","test_50_8"):
-    lat=bltio.read_boost(f"tests/golden/{name}.lat"); con=bltio.read_boost(f"tests/golden/{name}.con")
-    r=context.solve_raw(lat,con)
-    g=blt_b200.closest(r["lat"],con,timeout_ms=20000)
-    print(name,'rc',g['rc'],'found',g['found'],'nodes',g['nodes'],'ms',g['kernel_ms'],'refac',g['refactors'],flush=True)
+import numpy as np, blt_b200
+z=np.load("tests/golden/bench_dense60.npz")
+for d in (4,6,8):
+    r=blt_b200.closest(z["lat"],z["con"],rank=0,world=2,split_depth=d,timeout_ms=60000)
+    print(d,'rc',r['rc'],'nodes',r['nodes'],'ms',r['kernel_ms'],'donated',r['donated'],flush=True)

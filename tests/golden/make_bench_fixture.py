@@ -1,4 +1,5 @@
-"""Generates tests/golden/bench_dense60.npz: the bench.py workload (SURVEY.md section 8d, config 4 at the metric's
+"""Generates tests/golden/bench_dense60.npz (width 110, the full-size parity fixture) and bench_dense60_w<width>.npz
+(width 120: the bench.py workload; larger widths take the CPU oracle an hour and more): the bench.py workload (SURVEY.md section 8d, config 4 at the metric's
 shape n = m = 60).  The LLL-reduced basis comes from the oracle's exact LLL (oracle/lll.py); the expected counts
 come from the oracle's closest() and are stored so that the GPU run can be checked at full size.
 
@@ -26,6 +27,6 @@ r = oracle.closest(lat, con)
 print(f"oracle: rc={r['rc']} niter={r['niter']} nprune={r['nprune']} nodes={r['nodes']} pivots={r['pivots']} "
       f"{time.time() - t:.1f}s")
 assert r["rc"] == 0 and not oracle.check_soln(lat, con, r["sol"]), "bench instance must be UNSAT"
-np.savez_compressed(os.path.join(ROOT, "tests", "golden", "bench_dense60.npz"), lat=lat, con=con, A=A, C=C, w=w,
+np.savez_compressed(os.path.join(ROOT, "tests", "golden", "bench_dense60.npz" if w == 110 else f"bench_dense60_w{w}.npz"), lat=lat, con=con, A=A, C=C, w=w,
                     seed=seed, niter=r["niter"], nprune=r["nprune"], nodes=r["nodes"], pivots=r["pivots"],
                     hist=r["hist"], sol=r["sol"])

@@ -166,10 +166,11 @@ def test_subset_sum_sat(gpu):  # config 3 shape, small
         assert oracle.check_soln(lat, con, got["sol"])
 
 
-def test_bench_workload_full_size(gpu, golden):
-    """BASELINE.json's metric shape (n = m = 60) at full size: counts, histogram, pivots and uhat equal the values
-    the oracle produced when the fixture was made (tests/golden/make_bench_fixture.py)."""
-    z = np.load(f"{golden}/bench_dense60.npz")
+@pytest.mark.parametrize("fixture", ["bench_dense60.npz", "bench_dense60_w120.npz"])
+def test_bench_workload_full_size(gpu, golden, fixture):
+    """BASELINE.json's metric shape (n = m = 60) at full size (1.8 M and 6.3 M nodes): counts, histogram, pivots and uhat
+    equal the values the oracle produced when the fixture was made (tests/golden/make_bench_fixture.py)."""
+    z = np.load(f"{golden}/{fixture}")
     got = gpu.closest(z["lat"], z["con"], timeout_ms=300000)
     assert got["rc"] == 0 and not got["found"]
     assert got["niter"] == int(z["niter"]) and got["nprune"] == int(z["nprune"]) and got["nodes"] == int(z["nodes"])
