@@ -115,6 +115,22 @@ def run_reference(args, rank, world):
         tot_nodes += nodes
         tot_t += dt
     value = tot_nodes / tot_t
+    # Supplementary: what the host's cores could do if the reference were run once per core on independent work
+    # ("all-cores variant").  ctypes releases the GIL, so plain threads run in parallel.
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    done = []
+
+    def worker():
+        done.append(cpu_sample(wl, sample_nodes)[1])
+
+    ths = [threading.Thread(target=worker) for _ in range(cores)]
+    t0 = time.perf_counter()
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+    all_cores = {"value": sum(done) / (time.perf_counter() - t0), "unit": UNIT, "cores": cores,
+                 "sample": f"{cores} concurrent copies of the same {sample_nodes}-node sample, one per core"}
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -124,7 +140,7 @@ def run_reference(args, rank, world):
                                        "(oracle/blt_oracle.c), single thread like the reference; GaloisInc/blt itself "
                                        "cannot be built here (no NTL/GLPK/Boost)"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}
+            "all_cores": all_cores, "gpu_launches": 0}
     print(json.dumps(line))
     return 0
 
