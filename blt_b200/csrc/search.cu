@@ -108,6 +108,7 @@ struct Params {
     int donate_min_level;
     int lowwater;
     int no_early_exit;
+    int eager_max;          // explored children a sibling loop produces before it is parked (1 = the reference's depth-first order)
     int warps_per_cta;
     size_t warp_smem_doubles;
 };
@@ -1015,7 +1016,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         __syncwarp();
         // Wide level or little stack space left: park the rest of this loop and go down into the first child, the way
         // the depth-first order would.  The parked loop is a record like any other (it can even be donated).
-        if (status == NODE_EXPLORE && !forced && k0 > 1 && (nexp >= EAGER_MAX || (size_t)A.offs[A.acount] * 2 > A.cap)) {
+        if (status == NODE_EXPLORE && !forced && k0 > 1 && (nexp >= P.eager_max || (size_t)A.offs[A.acount] * 2 > A.cap)) {
             const ContLayout CL = cont_layout(RL, m, k0);
             unsigned char *C = nullptr;
             int slot = -1;
@@ -1222,16 +1223,13 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
 }
 
 // small helper kernels ---------------------------------------------------------------------------------------
-// fp64 basis, centre and the geometry of the problem; one warp
 // One warp: fp64 basis, centre, the geometry of the problem, then the initial solve LP(n) (closest.cc:206) whose
-// optimum is the parent vertex of the top level.  Writes the top-level record into `rec` (pool slot 0).  The basis
-// of this one solve lives in global memory (Wg); it is a cold path.
-__global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p, double *Q,
-                                   double *Qrev, double *Rm, double *QTp, double *tmp, unsigned long long *now, int *rc,
-                                   double *Wg, unsigned char *rec) {
-    extern __shared__ __align__(16) double smem[];
-    const int lane = threadIdx.x;
-    if (lane == 0) *now = gtimer();
+// optimum is the parent vertex of the top level.  Writes the top-level record into `rec`.  The basis of this one
+// solve lives in global memory (Wg); it is a cold path.  smem: warp_smem_bytes(n, m, 0, 1) bytes of shared memory.
+// cnt_out (global): pivots, cold starts, refactorisations, quick prunes of this solve.
+__device__ __forceinline__ int setup_warp(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p, double *Q,
+                                          double *Qrev, double *Rm, double *QTp, double *tmp, double *Wg, unsigned char *rec,
+                                          double *smem, unsigned long long *cnt_out, int lane) {
 #pragma unroll 1
     for (int e = lane; e < n * m; e += 32) B[e] = (double)lat[e];                                 // closest.cc:203
 #pragma unroll 1
@@ -1248,7 +1246,6 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
         s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0;
         const RecLayout RL = rec_layout(n, m);
         const int qpar = m - n;
-        unsigned long long *cnt_out = now + 2;  // pivots, cold starts, refactorisations, quick prunes of this solve
         double cm = 0.0, d = 0.0, vq = 0.0;
 #pragma unroll 1
         for (int j = lane; j < m; j += 32) { const double a = fabs(p[j]); cm = a > cm ? a : cm; }
@@ -1283,8 +1280,150 @@ __global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n
         }
         if (lane == 0) { cnt_out[0] = s.pivots; cnt_out[1] = s.colds; cnt_out[2] = s.refactors; cnt_out[3] = s.quick; }
     }
+    __syncwarp();
+    return r;
+}
+__global__ void bltcu_setup_kernel(const int64_t *lat, const int64_t *con, int n, int m, double *B, double *p, double *Q,
+                                   double *Qrev, double *Rm, double *QTp, double *tmp, unsigned long long *now, int *rc,
+                                   double *Wg, unsigned char *rec) {
+    extern __shared__ __align__(16) double smem[];
+    const int lane = threadIdx.x;
+    if (lane == 0) *now = gtimer();
+    const int r = setup_warp(lat, con, n, m, B, p, Q, Qrev, Rm, QTp, tmp, Wg, rec, smem, now + 2, lane);
     if (lane == 0) *rc = r;
 }
+// ------------------------------------------------------------------------------------------------------------
+// Batch form: many small independent problems of one shape, one warp per problem
+// ------------------------------------------------------------------------------------------------------------
+// Every warp takes the next problem off a counter, builds that problem's geometry in its own buffers, and searches it
+// alone with its private stack.  Sibling loops are parked after their first explored child (eager_max = 1), which is
+// exactly the reference's depth-first order: status, found, niter, nprune and the returned vector are those of
+// closest() on that problem alone, for SAT problems too.
+struct BatchParams {
+    Params P;                  // layout fields shared by all problems; the per-problem pointers are set by each warp
+    const int64_t *lat, *con;  // count x n*m, count x 2m
+    int count;
+    int *next;                 // problem counter
+    unsigned char *geo;        // per-warp: B, p, Q, Qrev, Rm, QTp, tmp (doubles), then 4 counters
+    size_t geo_stride;
+    QCtl *ctl;                 // per-warp control blocks
+    int64_t *sol;              // count x n
+    int *status, *found;       // count
+    unsigned long long *niter, *nprune;  // count
+    unsigned long long *totals;  // nodes, pivots, quick prunes, refactorisations, cold starts, then hist[MAXD + 1]
+    unsigned long long timeout_ns;
+    size_t warp_doubles;       // shared memory per warp: Q (m x LDQ) + the search block
+};
+__global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams BP) {
+    extern __shared__ __align__(16) double smem[];
+    Params P = BP.P;
+    const int n = P.n, m = P.m;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int gwarp = blockIdx.x * P.warps_per_cta + warp;
+    double *Qs = smem + (size_t)warp * BP.warp_doubles;
+    double *wsm = Qs + (size_t)m * P.LDQ;
+    double *g = (double *)(BP.geo + (size_t)gwarp * BP.geo_stride);
+    double *B = g; g += (size_t)n * m;
+    double *pc = g; g += m;
+    double *Q = g; g += (size_t)m * m;
+    double *Qrev = g; g += (size_t)m * m;
+    double *Rm = g; g += (size_t)n * n;
+    double *QTp = g; g += m;
+    double *tmp = g; g += 2 * (size_t)m;
+    unsigned long long *sc = (unsigned long long *)g;
+    P.B = B; P.p = pc; P.Qrev = Qrev; P.Rm = Rm; P.QTp = QTp;
+    QCtl *q = BP.ctl + gwarp;
+    P.q = q;
+    P.static_depth = 0; P.dynamic = 0; P.eager_max = 1;
+    const RecLayout RL = rec_layout(n, m);
+    unsigned char *nextbuf = P.nextrec + (size_t)gwarp * 2 * RL.stride;
+    double *wb = P.wbuf + (size_t)gwarp * P.wbuf_stride;
+    unsigned long long deadline = 0;
+    if (BP.timeout_ns) deadline = gtimer() + BP.timeout_ns;
+    deadline = __shfl_sync(FULLMASK, deadline, 0);
+    unsigned long long t_nodes = 0, t_piv = 0, t_quick = 0, t_ref = 0, t_cold = 0;
+    for (;;) {
+        int inst = 0;
+        if (lane == 0) inst = atomicAdd(BP.next, 1);
+        inst = __shfl_sync(FULLMASK, inst, 0);
+        if (inst >= BP.count) break;
+        const int64_t *lat = BP.lat + (size_t)inst * n * m, *con = BP.con + (size_t)inst * 2 * m;
+        int64_t *sol = BP.sol + (size_t)inst * n;
+        P.lat = lat; P.con = con; P.sol = sol;
+        P.radius = (double)(con[1] - con[0]) / 2.0;  // closest.cc:193-194: row 0 only
+#pragma unroll 1
+        for (int e = lane; e < (int)(sizeof(QCtl) / 8); e += 32) ((unsigned long long *)q)[e] = 0ull;
+#pragma unroll 1
+        for (int e = lane; e < n; e += 32) sol[e] = 0;
+        if (lane == 0) { P.best_valid[gwarp] = 0; sc[0] = sc[1] = sc[2] = sc[3] = 0; }
+        __syncwarp();
+        if (lane == 0) q->deadline_ns = deadline;
+        int st = BLTCU_STATUS_OK, fnd = 0;
+        Counters cnt = {0, 0, 0, 0};
+        const int r = setup_warp(lat, con, n, m, B, pc, Q, Qrev, Rm, QTp, tmp, wb, nextbuf, wsm, sc, lane);
+        if (r != 0) st = BLTCU_STATUS_LP_FAIL;  // dependent basis rows or a failed initial solve
+        else {
+#pragma unroll 1
+            for (int e = lane; e < m * P.LDQ; e += 32) {
+                const int j = e / P.LDQ, i = e - j * P.LDQ;
+                Qs[e] = i < m ? Qrev[(size_t)j * m + i] : 0.0;
+            }
+            WS s;
+            unsigned int *hist = carve_warp(s, wsm, n, m, P.QS, P.LDS);
+            s.Wpar = wb; s.Wg_a = wb + (size_t)m * m; s.Wg_b = s.Wg_a + (size_t)m * P.LDG; s.tmpA = s.Wg_b + (size_t)m * P.LDG;
+            s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
+            s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
+            s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
+            use_side<false>(s, 0);
+#pragma unroll 1
+            for (int e = lane; e <= n; e += 32) hist[e] = 0;
+            Arena A;
+            A.base = P.arena + (size_t)gwarp * P.arena_stride;
+            A.offs = (int *)(A.base + P.arena_bytes);
+            A.cap = P.arena_bytes; A.slots = P.arena_slots; A.acount = 0; A.abot = 0;
+            if (lane == 0) A.offs[0] = 0;
+            __syncwarp();
+            int nextsel = 0, have_next = 1;  // setup_warp left the top-level record in the first buffer
+            for (;;) {
+                const unsigned char *R;
+                if (have_next) { R = nextbuf + (size_t)nextsel * RL.stride; nextsel ^= 1; have_next = 0; }
+                else if (A.acount > 0) { A.acount--; R = A.base + A.offs[A.acount]; }
+                else break;
+                int ab = 0;
+                if (lane == 0) ab = *(volatile int *)&q->abort;
+                if (__shfl_sync(FULLMASK, ab, 0)) break;
+                have_next = expand(P, s, R, -1, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, cnt, hist);
+                __syncwarp();
+            }
+            __threadfence();
+            int fi = 0;
+            if (lane == 0) { st = *(volatile int *)&q->status; fnd = *(volatile int *)&q->found; fi = *(volatile int *)&q->fail_info; }
+            st = __shfl_sync(FULLMASK, st, 0); fnd = __shfl_sync(FULLMASK, fnd, 0); fi = __shfl_sync(FULLMASK, fi, 0);
+            if (!fnd && fi && st == BLTCU_STATUS_OK) st = BLTCU_STATUS_LP_FAIL;
+            if (!fnd) {  // the last recorded candidate (uhat), as the reference returns it
+                int bv = 0;
+                if (lane == 0) bv = P.best_valid[gwarp];
+                bv = __shfl_sync(FULLMASK, bv, 0);
+                if (bv) {
+#pragma unroll 1
+                    for (int e = lane; e < n; e += 32) sol[e] = P.best_u[(size_t)gwarp * n + e];
+                }
+            }
+            t_nodes += cnt.nodes + 1; t_piv += s.pivots + sc[0]; t_cold += s.colds + sc[1]; t_ref += s.refactors + sc[2];
+            t_quick += s.quick + sc[3];
+#pragma unroll 1
+            for (int e = lane; e <= n; e += 32) if (hist[e]) atomicAdd(&BP.totals[5 + e], (unsigned long long)hist[e]);
+            if (lane == 0) atomicAdd(&BP.totals[5 + n], 1ull);
+        }
+        if (lane == 0) { BP.status[inst] = st; BP.found[inst] = fnd; BP.niter[inst] = cnt.niter; BP.nprune[inst] = cnt.nprune; }
+        __syncwarp();
+    }
+    if (lane == 0) {
+        atomicAdd(&BP.totals[0], t_nodes); atomicAdd(&BP.totals[1], t_piv); atomicAdd(&BP.totals[2], t_quick);
+        atomicAdd(&BP.totals[3], t_ref); atomicAdd(&BP.totals[4], t_cold);
+    }
+}
+
 // static split: collects the path keys of the published subtrees into one contiguous buffer (one copy to the host)
 __global__ void bltcu_gather_keys_kernel(const unsigned char *pool, size_t stride, size_t off_ord, const int *out_list,
                                          int count, int n, unsigned char *keys) {
@@ -1488,6 +1627,7 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
     P.warps_per_cta = L.wpc;
     P.warp_smem_doubles = L.warp_bytes / 8;
     P.lowwater = std::min(L.nwarps, L.pool_cap / 4);
+    P.eager_max = EAGER_MAX;
 }
 }  // namespace
 
@@ -1745,6 +1885,130 @@ extern "C" int bltcu_closest(const int64_t *lat, const int64_t *con, int n, int 
         if (nprune) *nprune = st.nprune;
     }
     return rc;
+}
+
+// Batch form of the search seam ("arrays of problems, one status per problem").
+extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n, int m, const bltcu_opts *opts,
+                                   int64_t *sol, int *status, uint64_t *niter, uint64_t *nprune, int *found,
+                                   bltcu_stats *stats) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (count < 0) return BLTCU_STATUS_INPUT_ERROR;
+    const int v = validate(n, m);
+    if (v != BLTCU_STATUS_OK) return v;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (count == 0) return BLTCU_STATUS_OK;
+    if (!lat || !con || !sol || !status) return BLTCU_STATUS_INPUT_ERROR;
+    bltcu_opts o;
+    memset(&o, 0, sizeof o);
+    if (opts) o = *opts;
+    const int world = o.world > 1 ? o.world : 1, rank = world > 1 ? o.rank : 0;
+    if (rank < 0 || rank >= world) return BLTCU_STATUS_INPUT_ERROR;
+    const int lo = (int)((long long)count * rank / world), hi = (int)((long long)count * (rank + 1) / world);
+    const int mine = hi - lo;
+    if (mine == 0) return BLTCU_STATUS_OK;
+    std::lock_guard<std::mutex> lk(g_mu);
+    DevWs *w = nullptr;
+    if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
+
+    const int KQS = std::min(m, QS_MAX), LDS = KQS | 1, LDG = m | 1, LDQ = m | 1;
+    const size_t warp_bytes = warp_smem_bytes(n, m, KQS, LDS);
+    const size_t per_warp = align_up((size_t)m * LDQ * 8 + warp_bytes, 16);
+    int wpc = (int)std::min<size_t>(12, w->smem_optin / per_warp);
+    if (o.warps_per_cta > 0 && o.warps_per_cta < wpc) wpc = o.warps_per_cta;
+    if (wpc < 1) {
+        fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
+        return BLTCU_STATUS_ERROR;
+    }
+    int ctas = o.ctas > 0 ? o.ctas : w->sms;
+    ctas = std::max(1, std::min(ctas, (mine + wpc - 1) / wpc));
+    const int nwarps = ctas * wpc;
+    const RecLayout RL = rec_layout(n, m);
+    size_t arena_bytes = RL.stride;
+    for (int k0 = 2; k0 <= n; ++k0) arena_bytes += 2 * cont_layout(RL, m, k0).bytes;  // parks when half full
+    arena_bytes = align_up(arena_bytes, 256);
+    const int arena_slots = 2 * n + 16;
+    const size_t arena_stride = align_up(arena_bytes + (size_t)arena_slots * 4, 256);
+    const size_t wbuf_stride = align_up((size_t)2 * m * m + (size_t)2 * m * LDG, 32);
+    const size_t geo_stride = align_up(((size_t)n * m + 4 * (size_t)m + 2 * (size_t)m * m + (size_t)n * n) * 8 + 32, 256);
+
+    size_t off = 0;
+    auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
+    const size_t o_ctl = carve((size_t)nwarps * sizeof(QCtl)), o_next = carve(64), o_tot = carve((5 + MAXD + 1) * 8);
+    const size_t o_geo = carve((size_t)nwarps * geo_stride), o_bu = carve((size_t)nwarps * n * 8), o_bk = carve((size_t)nwarps * n);
+    const size_t o_bv = carve((size_t)nwarps * 4), o_wbuf = carve((size_t)nwarps * wbuf_stride * 8);
+    const size_t o_nrec = carve((size_t)nwarps * 2 * RL.stride), o_arena = carve((size_t)nwarps * arena_stride);
+    const size_t o_lat = carve((size_t)mine * n * m * 8), o_con = carve((size_t)mine * 2 * m * 8), o_sol = carve((size_t)mine * n * 8);
+    const size_t o_st = carve((size_t)mine * 4), o_fd = carve((size_t)mine * 4), o_ni = carve((size_t)mine * 8), o_np = carve((size_t)mine * 8);
+    if (ws_reserve(w, off)) return BLTCU_STATUS_ERROR;
+    unsigned char *base = (unsigned char *)w->buf;
+    cudaStream_t st = w->stream;
+
+    BatchParams BP;
+    memset(&BP, 0, sizeof BP);
+    Params &P = BP.P;
+    P.n = n; P.m = m; P.LDQ = LDQ; P.QS = KQS; P.LDS = LDS; P.LDG = LDG;
+    P.ring_mask = 0; P.rec_stride = RL.stride;
+    P.wbuf = (double *)(base + o_wbuf); P.wbuf_stride = wbuf_stride;
+    P.nextrec = base + o_nrec;
+    P.arena = base + o_arena; P.arena_stride = arena_stride; P.arena_bytes = arena_bytes; P.arena_slots = arena_slots;
+    P.best_u = (int64_t *)(base + o_bu); P.best_key = base + o_bk; P.best_valid = (int *)(base + o_bv);
+    P.no_early_exit = o.no_early_exit;
+    P.warps_per_cta = wpc;
+    P.warp_smem_doubles = warp_bytes / 8;
+    P.eager_max = 1;
+    BP.lat = (const int64_t *)(base + o_lat); BP.con = (const int64_t *)(base + o_con);
+    BP.count = mine;
+    BP.next = (int *)(base + o_next);
+    BP.geo = base + o_geo; BP.geo_stride = geo_stride;
+    BP.ctl = (QCtl *)(base + o_ctl);
+    BP.sol = (int64_t *)(base + o_sol); BP.status = (int *)(base + o_st); BP.found = (int *)(base + o_fd);
+    BP.niter = (unsigned long long *)(base + o_ni); BP.nprune = (unsigned long long *)(base + o_np);
+    BP.totals = (unsigned long long *)(base + o_tot);
+    {
+        long long tmo = o.timeout_ms;
+        if (tmo <= 0) { const char *e = getenv("BLTCU_TIMEOUT_MS"); if (e) tmo = atoll(e); }
+        BP.timeout_ns = tmo > 0 ? (unsigned long long)tmo * 1000000ull : 0ull;
+    }
+    BP.warp_doubles = per_warp / 8;
+    const size_t smem_bytes = (size_t)wpc * per_warp;
+
+    CK(cudaMemcpyAsync(base + o_lat, lat + (size_t)lo * n * m, (size_t)mine * n * m * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(base + o_con, con + (size_t)lo * 2 * m, (size_t)mine * 2 * m * 8, cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(base + o_next, 0, 64, st));
+    CK(cudaMemsetAsync(base + o_tot, 0, (5 + MAXD + 1) * 8, st));
+    CK(cudaFuncSetAttribute(bltcu_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
+    CK(cudaEventRecord(w->e0, st));
+    bltcu_batch_kernel<<<ctas, wpc * 32, smem_bytes, st>>>(BP);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(w->e1, st));
+    std::vector<unsigned long long> tot(5 + MAXD + 1), hni(mine), hnp(mine);
+    std::vector<int> hfd(mine);
+    CK(cudaMemcpyAsync(sol + (size_t)lo * n, base + o_sol, (size_t)mine * n * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(status + lo, base + o_st, (size_t)mine * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hfd.data(), base + o_fd, (size_t)mine * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hni.data(), base + o_ni, (size_t)mine * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hnp.data(), base + o_np, (size_t)mine * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(tot.data(), base + o_tot, tot.size() * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
+    unsigned long long sni = 0, snp = 0;
+    int nfound = 0;
+    for (int i = 0; i < mine; ++i) {
+        if (niter) niter[lo + i] = hni[i];
+        if (nprune) nprune[lo + i] = hnp[i];
+        if (found) found[lo + i] = hfd[i];
+        sni += hni[i]; snp += hnp[i]; nfound += hfd[i] ? 1 : 0;
+    }
+    if (stats) {
+        stats->niter = sni; stats->nprune = snp; stats->nodes = tot[0]; stats->pivots = tot[1]; stats->quick_prunes = tot[2];
+        stats->refactors = tot[3]; stats->cold_starts = tot[4];
+        for (int i = 0; i <= n; ++i) stats->hist[i] = tot[5 + i];
+        stats->kernel_ms = ms; stats->found = nfound; stats->launches = 1; stats->warps = nwarps; stats->ctas = ctas;
+        stats->scratch_bytes = off;
+        stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return BLTCU_STATUS_OK;
 }
 
 extern "C" int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok) {

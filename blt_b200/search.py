@@ -57,6 +57,10 @@ def lib() -> ctypes.CDLL:
         L.bltcu_closest_noalloc.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.c_int, i64p, u64p, u64p,
                                             ctypes.POINTER(ctypes.c_int)]
         L.bltcu_closest_noalloc.restype = ctypes.c_int
+        L.bltcu_closest_batch.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(Opts), i64p,
+                                          ctypes.POINTER(ctypes.c_int), u64p, u64p, ctypes.POINTER(ctypes.c_int),
+                                          ctypes.POINTER(Stats)]
+        L.bltcu_closest_batch.restype = ctypes.c_int
         L.bltcu_fp64_peak.argtypes = [ctypes.c_int, ctypes.c_int, f64p]
         L.bltcu_fp64_peak.restype = ctypes.c_int
         L.bltcu_release.argtypes = []
@@ -114,6 +118,30 @@ def closest_dev(d_lat_ptr: int, d_con_ptr: int, n: int, m: int, **opts):
     rc = lib().bltcu_closest_dev(ctypes.c_void_p(d_lat_ptr), ctypes.c_void_p(d_con_ptr), n, m, ctypes.byref(o),
                                  _p(sol, ctypes.c_int64), ctypes.byref(st))
     return _stats_dict(rc, sol, st, n)
+
+
+def closest_batch(lats, cons, **opts):
+    """Batch form of closest() (bltcu_closest_batch): lats is count x n x m, cons is count x m x 2.  Every problem is
+    searched on its own in the reference's depth-first order; returns per-problem arrays rc, sol, niter, nprune, found
+    plus the summed statistics."""
+    lats = _i64(lats)
+    cons = _i64(cons)
+    if lats.ndim != 3 or cons.ndim != 3 or cons.shape[2] != 2 or cons.shape[1] != lats.shape[2] or cons.shape[0] != lats.shape[0]:
+        raise ValueError("closest_batch wants lats (count, n, m) and cons (count, m, 2)")
+    count, n, m = lats.shape
+    sol = np.zeros((count, n), dtype=np.int64)
+    status = np.full(count, -1, dtype=np.int32)
+    found = np.zeros(count, dtype=np.int32)
+    niter = np.zeros(count, dtype=np.uint64)
+    nprune = np.zeros(count, dtype=np.uint64)
+    o = Opts(**opts)
+    st = Stats()
+    rc = lib().bltcu_closest_batch(_p(lats, ctypes.c_int64), _p(cons, ctypes.c_int64), count, n, m, ctypes.byref(o),
+                                   _p(sol, ctypes.c_int64), _p(status, ctypes.c_int), _p(niter, ctypes.c_uint64),
+                                   _p(nprune, ctypes.c_uint64), _p(found, ctypes.c_int), ctypes.byref(st))
+    d = _stats_dict(rc, None, st, n)
+    d.update(rc=rc, status=status, sol=sol, niter=niter, nprune=nprune, found=found.astype(bool))
+    return d
 
 
 def check_soln(lat, con, u) -> bool:

@@ -72,6 +72,16 @@ int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, int m, const
 int bltcu_closest_dev(const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
                       int64_t *sol, bltcu_stats *stats);
 
+/* Batch form of the same seam: `count` independent problems of one shape.
+ * lat: count x n x m, con: count x m x 2, sol: count x n, status/found/niter/nprune: count entries each (niter, nprune,
+ * found and stats may be NULL).  status[i] is what bltcu_closest() would return for problem i alone.  Each problem is
+ * searched by one warp in the reference's own depth-first order (closest.cc:208-318), so for SAT problems too sol,
+ * niter and nprune are those of the sequential search.  With opts->world > 1 only problems
+ * [count*rank/world, count*(rank+1)/world) are searched and written.  stats->found = number of problems with a point;
+ * the other counters are sums.  Returns BLT_STATUS_OK unless the call itself failed. */
+int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n, int m, const bltcu_opts *opts,
+                        int64_t *sol, int *status, uint64_t *niter, uint64_t *nprune, int *found, bltcu_stats *stats);
+
 /* LLL(): libblt/ntl_wrapper.h:20, libblt/ntl_wrapper.cc:37-52 (exact integral LLL, delta = 3/4, NTL::LLL(det2,B,U)).
  * B: r x c row-major, reduced in place: zero rows first, the `rank` reduced basis rows last.  U: r x r output with
  * U * B_in = B_out (may be NULL).  Returns BLT_STATUS_OK or BLT_STATUS_INPUT_ERROR. */
