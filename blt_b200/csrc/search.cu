@@ -118,6 +118,10 @@ struct RecLayout {
     size_t off_u, off_ord, off_cpar, off_chat, off_sg, off_zrow, off_H, stride;
 };
 __host__ __device__ inline size_t al8(size_t x) { return (x + 7) / 8 * 8; }
+// leading dimension (in doubles) of a shared-memory matrix whose rows are read with 16-byte loads, one row per lane:
+// the smallest value >= x that is 2 mod 4 (even => rows stay 16-byte aligned; half of it odd => eight consecutive
+// rows start in eight different 16-byte bank groups)
+__host__ __device__ inline int ld_vec(int x) { return (x + 1) / 4 * 4 + 2; }
 __host__ __device__ inline RecLayout rec_layout(int n, int m) {
     RecLayout L;
     size_t o = 48;  // header: int k, int flags, double xc, double gbase, int step, int state, int bytes, pad
@@ -225,13 +229,55 @@ __device__ __forceinline__ void dot4x2(int len, FA fa, FB fb, FC fc, double &r1,
     r2 = (b0 + b1) + (b2 + b3);
 }
 
+// The same sums in the same order with 16-byte loads (both operands 16-byte aligned): half the load instructions.
+__device__ __forceinline__ double dot4v(int len, const double *a, const double *b) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+    int e = 0;
+#pragma unroll 1
+    for (; e + 3 < len; e += 4) {
+        const double2 x0 = *(const double2 *)(a + e), x1 = *(const double2 *)(a + e + 2);
+        const double2 y0 = *(const double2 *)(b + e), y1 = *(const double2 *)(b + e + 2);
+        a0 = fma(x0.x, y0.x, a0); a1 = fma(x0.y, y0.y, a1); a2 = fma(x1.x, y1.x, a2); a3 = fma(x1.y, y1.y, a3);
+    }
+    if (e < len) { a0 = fma(a[e], b[e], a0); ++e; }
+    if (e < len) { a1 = fma(a[e], b[e], a1); ++e; }
+    if (e < len) { a2 = fma(a[e], b[e], a2); }
+    return (a0 + a1) + (a2 + a3);
+}
+__device__ __forceinline__ void dot4x2v(int len, const double *a, const double *b, const double *c, double &r1, double &r2) {
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+    int e = 0;
+#pragma unroll 1
+    for (; e + 3 < len; e += 4) {
+        const double2 x0 = *(const double2 *)(a + e), x1 = *(const double2 *)(a + e + 2);
+        const double2 y0 = *(const double2 *)(b + e), y1 = *(const double2 *)(b + e + 2);
+        const double2 z0 = *(const double2 *)(c + e), z1 = *(const double2 *)(c + e + 2);
+        a0 = fma(x0.x, y0.x, a0); b0 = fma(x0.x, z0.x, b0);
+        a1 = fma(x0.y, y0.y, a1); b1 = fma(x0.y, z0.y, b1);
+        a2 = fma(x1.x, y1.x, a2); b2 = fma(x1.x, z1.x, b2);
+        a3 = fma(x1.y, y1.y, a3); b3 = fma(x1.y, z1.y, b3);
+    }
+    if (e < len) { const double x = a[e]; a0 = fma(x, b[e], a0); b0 = fma(x, c[e], b0); ++e; }
+    if (e < len) { const double x = a[e]; a1 = fma(x, b[e], a1); b1 = fma(x, c[e], b1); ++e; }
+    if (e < len) { const double x = a[e]; a2 = fma(x, b[e], a2); b2 = fma(x, c[e], b2); }
+    r1 = (a0 + a1) + (a2 + a3);
+    r2 = (b0 + b1) + (b2 + b3);
+}
+
+// Reductions of NON-NEGATIVE doubles (every caller passes |x|, a ratio of non-negatives or +inf): the bit patterns order
+// like the values, so two 32-bit redux.sync steps (high word, then low word among the lanes that hold the winning high
+// word) give exactly the value a shuffle tree would.
 __device__ __forceinline__ double warp_max(double v) {
-    for (int off = 16; off >= 1; off >>= 1) { const double o = __shfl_xor_sync(FULLMASK, v, off); v = o > v ? o : v; }
-    return v;
+    const unsigned hi = (unsigned)__double2hiint(v);
+    const unsigned mh = __reduce_max_sync(FULLMASK, hi);
+    const unsigned ml = __reduce_max_sync(FULLMASK, hi == mh ? (unsigned)__double2loint(v) : 0u);
+    return __hiloint2double((int)mh, (int)ml);
 }
 __device__ __forceinline__ double warp_min(double v) {
-    for (int off = 16; off >= 1; off >>= 1) { const double o = __shfl_xor_sync(FULLMASK, v, off); v = o < v ? o : v; }
-    return v;
+    const unsigned hi = (unsigned)__double2hiint(v);
+    const unsigned mh = __reduce_min_sync(FULLMASK, hi);
+    const unsigned ml = __reduce_min_sync(FULLMASK, hi == mh ? (unsigned)__double2loint(v) : 0xffffffffu);
+    return __hiloint2double((int)mh, (int)ml);
 }
 __device__ __forceinline__ double butterfly(double v) {  // the oracle's butterfly32
     for (int off = 16; off >= 1; off >>= 1) v = v + __shfl_xor_sync(FULLMASK, v, off);
@@ -245,6 +291,18 @@ __device__ __forceinline__ void warp_argmax(double &v, int &idx) {
         const bool take = (oi >= 0) && (idx < 0 || ov > v || (ov == v && oi < idx));
         if (take) { v = ov; idx = oi; }
     }
+}
+
+// the same result for lanes whose value is non-negative whenever idx >= 0 (three redux.sync steps and a vote)
+__device__ __forceinline__ void warp_argmax_nn(double &v, int &idx) {
+    const bool valid = idx >= 0;
+    const unsigned hi = valid ? (unsigned)__double2hiint(v) : 0u;
+    const unsigned mh = __reduce_max_sync(FULLMASK, hi);
+    const bool m1 = valid && hi == mh;
+    const unsigned lo = m1 ? (unsigned)__double2loint(v) : 0u;
+    const unsigned ml = __reduce_max_sync(FULLMASK, lo);
+    const unsigned mi = __reduce_min_sync(FULLMASK, (m1 && lo == ml) ? (unsigned)idx : 0xffffffffu);
+    if (mi != 0xffffffffu) { idx = (int)mi; v = __hiloint2double((int)mh, (int)ml); }
 }
 
 // ---- geometry: B^T = Q R by Gram-Schmidt applied twice, one warp (twin of geo_build in the oracle) ------------
@@ -304,12 +362,14 @@ __device__ int geo_build_warp(const double *B, const double *p, int n, int m, do
 }
 
 // ---- LP engine (twin of the oracle's lp_* functions) -----------------------------------------------------------
+// V: H rows, the rows of Qs and chat are 16-byte aligned (the shared-memory layout), so dot products use 16-byte loads
+template <bool V>
 __device__ __forceinline__ void lp_values(WS &s) {
     const int qd = s.qd;
 #pragma unroll 1
     for (int p = s.lane; p < qd; p += 32) {
         const double *Hp = s.W + (size_t)p * s.LD, *ch = s.chat;
-        s.val[p] = dot4(qd, [&](int e) { return Hp[e]; }, [&](int e) { return ch[e]; });
+        s.val[p] = V ? dot4v(qd, Hp, ch) : dot4(qd, [&](int e) { return Hp[e]; }, [&](int e) { return ch[e]; });
     }
     __syncwarp();
 }
@@ -321,34 +381,44 @@ __device__ __forceinline__ void lp_flip(WS &s) {
     if (s.lane == 0) s.val[0] = -s.val[0];
     __syncwarp();
 }
-__device__ __forceinline__ double lp_alpha_beta(WS &s, int pe) {
+// alpha, beta of every non-basic row; returns |N y|_1.  bmax: this lane's largest |beta| (for the ratio test's scale);
+// need_repair: some row's sg*alpha fell below -HARRIS_DELTA (warp-uniform).
+template <bool V>
+__device__ __forceinline__ double lp_alpha_beta(WS &s, int pe, double &bmax, bool &need_repair) {
     const int qd = s.qd, m = s.m;
     const double *y = s.W, *rho = s.W + (size_t)pe * s.LD;
-    double part = 0.0;
+    double part = 0.0, bm = 0.0;
+    bool bad = false;
 #pragma unroll 1
     for (int j = s.lane; j < m; j += 32) {
         double a = 0.0, b = 0.0;
         if (!s.pos[j]) {
             const double *nj = s.Qs + (size_t)j * s.LDQ;
-            dot4x2(qd, [&](int e) { return nj[e]; }, [&](int e) { return y[e]; }, [&](int e) { return rho[e]; }, a, b);
+            if (V) dot4x2v(qd, nj, y, rho, a, b);
+            else dot4x2(qd, [&](int e) { return nj[e]; }, [&](int e) { return y[e]; }, [&](int e) { return rho[e]; }, a, b);
             part += fabs(a);
+            const double fb = fabs(b);
+            bm = fb > bm ? fb : bm;
+            bad = bad || ((double)s.sg[j] * a < -HARRIS_DELTA);
         }
         s.al[j] = a; s.be[j] = b;
     }
+    bmax = bm;
+    need_repair = __any_sync(FULLMASK, bad);
     return butterfly(part);
 }
 // sign repair (twin of the oracle's lp_repair): rows whose sg_j*alpha_j fell below -HARRIS_DELTA go to the other bound;
 // column 0 of A changes by Delta = sum -2 sg_j n_j, a rank-one correction of H.  Returns 1 if anything was flipped.
-__device__ __forceinline__ int lp_repair(WS &s) {
+__device__ __forceinline__ int lp_repair(WS &s, bool need) {
     const int m = s.m, qd = s.qd, LD = s.LD;
-    bool any = false;
+    if (!need) return 0;
+    __syncwarp();
 #pragma unroll 1
     for (int j = s.lane; j < m; j += 32) {
         double rj = 0.0;
-        if (!s.pos[j] && (double)s.sg[j] * s.al[j] < -HARRIS_DELTA) { rj = -2.0 * (double)s.sg[j]; any = true; }
+        if (!s.pos[j] && (double)s.sg[j] * s.al[j] < -HARRIS_DELTA) rj = -2.0 * (double)s.sg[j];
         s.r[j] = rj;
     }
-    if (!__any_sync(FULLMASK, any)) return 0;
     __syncwarp();
 #pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) {
@@ -379,14 +449,12 @@ __device__ __forceinline__ int lp_repair(WS &s) {
     s.repairs++;
     return 1;
 }
-__device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland) {
+__device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland, double bmax) {
     const int m = s.m, qd = s.qd;
     const bool artificial = s.zrow[pe] < 0;
-    double scale = 0.0;
+    double scale = bmax;  // this lane's largest |beta| over the non-basic rows (lp_alpha_beta)
 #pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) { const double a = fabs(s.W[(size_t)pe * s.LD + c]); scale = a > scale ? a : scale; }
-#pragma unroll 1
-    for (int j = s.lane; j < m; j += 32) if (!s.pos[j]) { const double a = fabs(s.be[j]); scale = a > scale ? a : scale; }
     scale = warp_max(scale);
     const double tiny = PIV_TOL * scale;
     int best = -1; double bd = 0.0;
@@ -417,7 +485,7 @@ __device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland) {
             if (num / den <= tmax && (bland ? best < 0 : den > bd)) { bd = den; best = j; }
         }
         if (bland) { double key = best >= 0 ? -(double)best : 0.0; warp_argmax(key, best); bd = __shfl_sync(FULLMASK, bd, 0); }  // lowest row index
-        else warp_argmax(bd, best);
+        else warp_argmax_nn(bd, best);
     }
     if (artificial) return (best >= 0 && bd > 1.0e-3 * tiny) ? best : -1;  // its pivot is den itself: refuse a vanishing one
     if (best >= 0) return best;
@@ -427,9 +495,10 @@ __device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland) {
         if (s.pos[j] || fabs(s.be[j]) > tiny) continue;
         if (fabs(s.al[j]) > ba) { ba = fabs(s.al[j]); best = j; }
     }
-    warp_argmax(ba, best);
+    warp_argmax_nn(ba, best);
     return best;
 }
+template <bool V>
 __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
     const int qd = s.qd, LD = s.LD;
     double *H = s.W, *Hp = s.W + (size_t)pe * LD;
@@ -440,7 +509,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
 #pragma unroll 1
     for (int i = s.lane; i < qd; i += 32) {
         const double *Hi = H + (size_t)i * LD;
-        s.w[i] = dot4(qd, [&](int c) { return Hi[c]; }, [&](int c) { return nl[c]; });
+        s.w[i] = V ? dot4v(qd, Hi, nl) : dot4(qd, [&](int c) { return Hi[c]; }, [&](int c) { return nl[c]; });
     }
     __syncwarp();
     const double wp = s.w[pe];
@@ -448,11 +517,21 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
 #pragma unroll 1
     for (int c = s.lane; c < qd; c += 32) s.v[c] = Hp[c] / wp;
     __syncwarp();
-    if (qd <= 32) {  // one lane per column, rows in a loop: same arithmetic, no index division
+    // H[i][c] -= w[i] v[c] for every row but pe.  Row pe is rewritten from v below, so it needs no exception here.
+    if (qd <= 16) {  // lanes 0-15 take the even rows, lanes 16-31 the odd ones; one lane per column
+        const int c = s.lane & 15;
+        if (c < qd) {
+            const double vc = s.v[c];
+            double *Hc = H + c;
+#pragma unroll 1
+            for (int i = s.lane >> 4; i < qd; i += 2) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
+        }
+    } else if (qd <= 32) {  // one lane per column, rows in a loop: same arithmetic, no index division
         if (s.lane < qd) {
             const double vc = s.v[s.lane];
             double *Hc = H + s.lane;
-            for (int i = 0; i < qd; ++i) if (i != pe) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
+#pragma unroll 1
+            for (int i = 0; i < qd; ++i) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
         }
     } else {
 #pragma unroll 1
@@ -515,11 +594,13 @@ __device__ __forceinline__ void lp_extend(WS &s) {
 // cold builds only (root solve, test seam): pivot the artificial at the last position out
 __device__ __forceinline__ int lp_drop_artificial(WS &s, int sf) {
     const int pe = s.qd - 1;
-    lp_alpha_beta(s, pe);
-    if (lp_repair(s)) lp_alpha_beta(s, pe);
-    const int l = lp_ratio(s, sf, pe, false);
+    double bmax;
+    bool need;
+    lp_alpha_beta<false>(s, pe, bmax, need);
+    if (lp_repair(s, need)) lp_alpha_beta<false>(s, pe, bmax, need);
+    const int l = lp_ratio(s, sf, pe, false, bmax);
     if (l < 0) return -1;
-    return lp_replace(s, pe, l, sf);
+    return lp_replace<false>(s, pe, l, sf);
 }
 // rare path: rebuild H = A^-1 from Z and the signs by Gauss-Jordan with row pivoting, one lane, the oracle's loops.
 // Takes plain pointers so that the caller's state can stay in registers.
@@ -584,10 +665,11 @@ __device__ __forceinline__ void lp_image(WS &s, int nv) {
 // qd < m.  art != 0: the basis still holds the artificial column of a fresh coordinate at position qd-1; it is pivoted
 // out first with sign `art` (the oracle's lp_drop_artificial followed by lp_solve; merged so that the pivot code
 // exists once in the instruction stream).
+template <bool V>
 __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, double &d_out, int art) {
     const int qd = s.qd, m = s.m;
     if (!art) {
-        lp_values(s);
+        lp_values<V>(s);
         if (s.val[0] < 0.0) lp_flip(s);
     }
     const int cap = 100 * m + 1000;
@@ -607,7 +689,7 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
             pe = -1; double vmax = -1.0;
 #pragma unroll 1
             for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
-            warp_argmax(vmax, pe);
+            warp_argmax_nn(vmax, pe);
             if (bland && pe >= 0 && vmax > t + tol) {  // the violated basic row with the lowest row index
                 int bp = -1; double key = 0.0;
 #pragma unroll 1
@@ -627,7 +709,7 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
                 if (refactored) { s.failcode = 1; return NODE_FAIL; }
                 refactored = true;
                 if (lp_refactor(s)) { s.failcode = 2; return NODE_FAIL; }
-                lp_values(s);
+                lp_values<V>(s);
                 if (s.val[0] < 0.0) lp_flip(s);
                 ++iter;
                 continue;
@@ -635,11 +717,13 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
             if (iter >= cap) { s.failcode = 3; return NODE_FAIL; }
             se = s.val[pe] > 0.0 ? 1 : -1;
         }
-        double nrm1 = lp_alpha_beta(s, pe);
-        if (lp_repair(s)) {
-            if (art) nrm1 = lp_alpha_beta(s, pe);
+        double bmax;
+        bool need;
+        double nrm1 = lp_alpha_beta<V>(s, pe, bmax, need);
+        if (lp_repair(s, need)) {
+            if (art) nrm1 = lp_alpha_beta<V>(s, pe, bmax, need);
             else {  // the vertex moved a little: price again
-                lp_values(s);
+                lp_values<V>(s);
                 if (s.val[0] < 0.0) lp_flip(s);
                 ++iter;
                 continue;
@@ -649,15 +733,15 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
             if (refactored) { s.failcode = 4; return NODE_FAIL; }
             refactored = true;
             if (lp_refactor(s)) { s.failcode = 5; return NODE_FAIL; }
-            lp_values(s);
+            lp_values<V>(s);
             if (s.val[0] < 0.0) lp_flip(s);
             ++iter;
             continue;
         }
-        const int l = lp_ratio(s, se, pe, bland);
+        const int l = lp_ratio(s, se, pe, bland, bmax);
         if (l < 0) { s.failcode = art ? 6 : 7; return NODE_FAIL; }
-        if (lp_replace(s, pe, l, se)) { s.failcode = 8; return NODE_FAIL; }
-        lp_values(s);
+        if (lp_replace<V>(s, pe, l, se)) { s.failcode = 8; return NODE_FAIL; }
+        lp_values<V>(s);
         if (art) { art = 0; if (s.val[0] < 0.0) lp_flip(s); }
         else ++iter;
     }
@@ -907,10 +991,10 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 double rad = P.radius;
                 if (s.qd < qd0) {
                     lp_extend(s);
-                    if (cold) { lp_values(s); art = s.val[s.qd - 1] > 0.0 ? 1 : -1; if (s.qd < qd0) rad = INFINITY; }
+                    if (cold) { lp_values<!BIG>(s); art = s.val[s.qd - 1] > 0.0 ? 1 : -1; if (s.qd < qd0) rad = INFINITY; }
                     else art = dir;
                 }
-                status = lp_solve(s, rad, cmax, d, art);
+                status = lp_solve<!BIG>(s, rad, cmax, d, art);
                 if (status == NODE_FAIL) {
                     if (cold || lp_init1(s)) { status = NODE_FAIL; break; }
                     cold = true;
@@ -1260,10 +1344,10 @@ __device__ __forceinline__ int setup_warp(const int64_t *lat, const int64_t *con
             r = lp_init1(s);
             for (int i = 1; i < qpar && r == 0; ++i) {
                 lp_extend(s);
-                lp_values(s);
+                lp_values<false>(s);
                 r = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
             }
-            if (r == 0 && lp_solve(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
+            if (r == 0 && lp_solve<false>(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
             if (r == 0) {
                 vq = s.v[qpar];
 #pragma unroll 1
@@ -1477,10 +1561,10 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
             r = lp_init1(s);
             for (int i = 1; i < qd && r == 0; ++i) {
                 lp_extend(s);
-                lp_values(s);
+                lp_values<false>(s);
                 r = lp_drop_artificial(s, s.val[i] > 0.0 ? 1 : -1);
             }
-            if (r == 0 && lp_solve(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
+            if (r == 0 && lp_solve<false>(s, INFINITY, cm, d, 0) != NODE_EXPLORE) r = -1;
             if (r == 0) {
                 const double t = s.val[0];
 #pragma unroll 1
@@ -1566,7 +1650,7 @@ struct Layout {
 // arena_recs: size of each warp's private stack in units of the largest record
 int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap,
                 int arena_recs) {
-    L.KQS = std::min(m, QS_MAX); L.LDS = L.KQS | 1; L.LDG = m | 1; L.LDQ = m | 1;
+    L.KQS = std::min(m, QS_MAX); L.LDS = ld_vec(L.KQS); L.LDG = m | 1; L.LDQ = ld_vec(m);
     L.warp_bytes = warp_smem_bytes(n, m, L.KQS, L.LDS);
     const size_t q_bytes = (size_t)m * L.LDQ * 8;
     int wpc = (int)((smem_budget > q_bytes ? smem_budget - q_bytes : 0) / L.warp_bytes);
@@ -1910,7 +1994,7 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     DevWs *w = nullptr;
     if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
 
-    const int KQS = std::min(m, QS_MAX), LDS = KQS | 1, LDG = m | 1, LDQ = m | 1;
+    const int KQS = std::min(m, QS_MAX), LDS = ld_vec(KQS), LDG = m | 1, LDQ = ld_vec(m);
     const size_t warp_bytes = warp_smem_bytes(n, m, KQS, LDS);
     const size_t per_warp = align_up((size_t)m * LDQ * 8 + warp_bytes, 16);
     int wpc = (int)std::min<size_t>(12, w->smem_optin / per_warp);
