@@ -179,6 +179,8 @@ struct WS {
     unsigned int repairs;
     // the two sides of the level being expanded, and the parent's vertex
     double *Ws_a, *Ws_b, *Wg_a, *Wg_b;
+    const double *Qsm;  // the first QS+1 columns of Qrev in shared memory (leading dimension LDQsm); larger bases read Qrev itself
+    int LDQsm;
     int *zrow_a, *zrow_b;
     unsigned char *pos_a, *pos_b;
     signed char *sg_a, *sg_b;
@@ -889,6 +891,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     const int c_step = ((const int *)R)[6], c_state = ((const int *)R)[7];
     const int kk = k0 - 1, qd0 = m - kk, qpar = m - k0;
 
+    if (BIG) { s.Qs = P.Qrev; s.LDQ = m; } else { s.Qs = s.Qsm; s.LDQ = s.LDQsm; }
     // ---- take what is needed out of the record; afterwards the record is dead ----
 #pragma unroll 1
     for (int e = lane; e < n; e += 32) { s.u[e] = ((const long long *)(R + RL.off_u))[e]; s.ord[e] = (R + RL.off_ord)[e]; }
@@ -1204,6 +1207,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         s.tmpA = wb;
     }
     s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
+    s.Qsm = Qs; s.LDQsm = P.LDQ;
     s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
     use_side<false>(s, 0);
@@ -1456,6 +1460,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
             unsigned int *hist = carve_warp(s, wsm, n, m, P.QS, P.LDS);
             s.Wpar = wb; s.Wg_a = wb + (size_t)m * m; s.Wg_b = s.Wg_a + (size_t)m * P.LDG; s.tmpA = s.Wg_b + (size_t)m * P.LDG;
             s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
+            s.Qsm = Qs; s.LDQsm = P.LDQ;
             s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
             s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
             use_side<false>(s, 0);
@@ -1650,7 +1655,7 @@ struct Layout {
 // arena_recs: size of each warp's private stack in units of the largest record
 int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap,
                 int arena_recs) {
-    L.KQS = std::min(m, QS_MAX); L.LDS = ld_vec(L.KQS); L.LDG = m | 1; L.LDQ = ld_vec(m);
+    L.KQS = std::min(m, QS_MAX); L.LDS = ld_vec(L.KQS); L.LDG = m | 1; L.LDQ = ld_vec(std::min(m, L.KQS + 1));
     L.warp_bytes = warp_smem_bytes(n, m, L.KQS, L.LDS);
     const size_t q_bytes = (size_t)m * L.LDQ * 8;
     int wpc = (int)((smem_budget > q_bytes ? smem_budget - q_bytes : 0) / L.warp_bytes);
@@ -1994,7 +1999,7 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     DevWs *w = nullptr;
     if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
 
-    const int KQS = std::min(m, QS_MAX), LDS = ld_vec(KQS), LDG = m | 1, LDQ = ld_vec(m);
+    const int KQS = std::min(m, QS_MAX), LDS = ld_vec(KQS), LDG = m | 1, LDQ = ld_vec(std::min(m, KQS + 1));
     const size_t warp_bytes = warp_smem_bytes(n, m, KQS, LDS);
     const size_t per_warp = align_up((size_t)m * LDQ * 8 + warp_bytes, 16);
     int wpc = (int)std::min<size_t>(12, w->smem_optin / per_warp);
