@@ -35,7 +35,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-FIXTURE = os.path.join(ROOT, "tests", "golden", os.environ.get("BLT_BENCH_FIXTURE", "bench_dense60_w120.npz"))
+FIXTURE = os.path.join(ROOT, "tests", "golden", os.environ.get("BLT_BENCH_FIXTURE", "bench_dense60_w130.npz"))
 METRIC = "enum_nodes_per_s"
 UNIT = "nodes/s"
 
@@ -100,6 +100,24 @@ def cpu_sample(wl, max_nodes):
     r = oracle.closest(wl["lat"], wl["con"], max_nodes=max_nodes)
     dt = time.perf_counter() - t0
     return r["nodes"] / dt, r["nodes"], dt
+
+
+def batch_supplement(blt_b200):
+    """Supplementary figure, outside the timed region of the headline metric: SURVEY.md section 8d config 5 through
+    bltcu_closest_batch -- the 400 committed n = m = 20 instances, tiled to 4000, host buffers in and out."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "batch20.npz"))
+    reps = 10
+    lats = np.ascontiguousarray(np.tile(z["lat"], (reps, 1, 1)))
+    cons = np.ascontiguousarray(np.tile(z["con"], (reps, 1, 1)))
+    blt_b200.closest_batch(lats[:400], cons[:400])
+    t0 = time.perf_counter()
+    r = blt_b200.closest_batch(lats, cons)
+    dt = time.perf_counter() - t0
+    ok = bool((r["niter"] == np.tile(z["niter"], reps)).all() and (r["nprune"] == np.tile(z["nprune"], reps)).all()
+              and (r["status"] == np.tile(z["rc"], reps)).all())
+    return {"workload": "config 5: 4000 dense 20x20 instances (tests/golden/batch20.npz x10), one warp per instance",
+            "instances_per_s": len(lats) / dt, "nodes_per_s": r["nodes"] / dt, "kernel_ms": r["kernel_ms"],
+            "e2e_ms": 1e3 * dt, "count_ok": ok}
 
 
 def run_reference(args, rank, world):
@@ -269,6 +287,14 @@ def main():
                                      "throughput measured on this GPU by bltcu_fp64_peak (MEASURED_PEAKS.json has no "
                                      "FP64 figure)"},
                 "clocks": sampler.summary()}
+        if world == 1:
+            line["batch"] = batch_supplement(blt_b200)
+            prof = os.path.join(ROOT, "profiles", "r1_final_summary.json")
+            if os.path.exists(prof):  # dram bytes of the search kernel from the committed ncu --set full capture
+                pj = json.load(open(prof))
+                if pj.get("fixture") == os.path.basename(FIXTURE):
+                    line["roofline"]["traffic"] = pj.get("dram_bytes_per_launch")
+                    line["roofline"]["traffic_source"] = "profiles/r1_final_summary.json (ncu --set full, one launch)"
         if not args.no_cpu and world == 1:
             v, cn, dt = cpu_sample(wl, args.cpu_nodes)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",

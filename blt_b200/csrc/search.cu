@@ -47,6 +47,8 @@
 #define STALL_MAX 40
 #define MAXD BLTCU_MAX_DIM
 #define QS_MAX 24  // largest basis kept in shared memory (larger ones live in the per-warp global buffers)
+#define LDS_C 26   // row stride of the shared-memory matrices: ld_vec(QS_MAX)
+#define LDQ_C 26   // row stride of the shared-memory copy of the first QS_MAX + 1 columns of Q: ld_vec(QS_MAX + 1)
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
 enum { REC_TOP = 1, REC_CONT = 2 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
@@ -401,7 +403,7 @@ __device__ __forceinline__ double lp_alpha_beta(WS &s, int pe, double &bmax, boo
             part += fabs(a);
             const double fb = fabs(b);
             bm = fb > bm ? fb : bm;
-            bad = bad || ((double)s.sg[j] * a < -HARRIS_DELTA);
+            bad = bad || ((s.sg[j] > 0 ? a : -a) < -HARRIS_DELTA);
         }
         s.al[j] = a; s.be[j] = b;
     }
@@ -468,9 +470,9 @@ __device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland, doubl
 #pragma unroll 1
         for (int j = s.lane; j < m; j += 32) {
             if (s.pos[j]) continue;
-            const double den = -(double)(se * s.sg[j]) * s.be[j];
+            const double bj = s.be[j]; const double den = ((se > 0) == (s.sg[j] > 0)) ? -bj : bj;  // -(se sg_j) beta_j
             if (!(den > dmin)) continue;
-            double num = (double)s.sg[j] * s.al[j] + HARRIS_DELTA;  // rows already below zero get less room, not more
+            double num = (s.sg[j] > 0 ? s.al[j] : -s.al[j]) + HARRIS_DELTA;  // rows already below zero get less room, not more
             if (num < 0.0) num = 0.0;
             const double rt = num / den;
             if (rt < tmax) tmax = rt;
@@ -480,9 +482,9 @@ __device__ __forceinline__ int lp_ratio(WS &s, int se, int pe, bool bland, doubl
 #pragma unroll 1
         for (int j = s.lane; j < m; j += 32) {
             if (s.pos[j]) continue;
-            const double den = -(double)(se * s.sg[j]) * s.be[j];
+            const double bj = s.be[j]; const double den = ((se > 0) == (s.sg[j] > 0)) ? -bj : bj;  // -(se sg_j) beta_j
             if (!(den > dmin)) continue;
-            double num = (double)s.sg[j] * s.al[j];
+            double num = s.sg[j] > 0 ? s.al[j] : -s.al[j];
             if (num < 0.0) num = 0.0;
             if (num / den <= tmax && (bland ? best < 0 : den > bd)) { bd = den; best = j; }
         }
@@ -685,14 +687,52 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
         else {
             const double t = s.val[0];
             if (!approxLE(t, radius)) { if (iter == 0) s.quick++; return NODE_PRUNE; }
-            // degenerate stalling: after STALL_MAX steps without progress switch to lowest-index (Bland) choices
-            if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= STALL_MAX) bland = true;
+            // degenerate stalling: after STALL_MAX steps without progress leave by largest violation, after twice as many
+            // switch to lowest-index (Bland) choices
+            if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= 2 * STALL_MAX) bland = true;
+            const bool dantzig = stall >= STALL_MAX;
             const double tol = EPS_OPT * (cmax + t);
-            pe = -1; double vmax = -1.0;
+            // Pricing (twin of the oracle's): among the basic rows outside the box the one with the steepest dual edge
+            // leaves, score = (|r_z| - t)^2 / |H[p] - se H[0]|^2 (N has orthonormal columns, so this is the exact norm of
+            // the dual ray); ties: lowest position.
+            pe = -1;
+            if (!bland) {
+                double best = -1.0;
+                const double *H0 = s.W;
 #pragma unroll 1
-            for (int p = 1 + s.lane; p < qd; p += 32) { const double a = fabs(s.val[p]); if (a > vmax) { vmax = a; pe = p; } }
-            warp_argmax_nn(vmax, pe);
-            if (bland && pe >= 0 && vmax > t + tol) {  // the violated basic row with the lowest row index
+                for (int p = 1 + s.lane; p < qd; p += 32) {
+                    const double vp = s.val[p], a = fabs(vp);
+                    if (!(a > t + tol)) continue;
+                    const double sp = vp > 0.0 ? 1.0 : -1.0;
+                    const double *Hp = s.W + (size_t)p * s.LD;
+                    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+                    int e = 0;
+                    if (V) {
+#pragma unroll 1
+                        for (; e + 3 < qd; e += 4) {
+                            const double2 h0 = *(const double2 *)(Hp + e), h1 = *(const double2 *)(Hp + e + 2);
+                            const double2 y0 = *(const double2 *)(H0 + e), y1 = *(const double2 *)(H0 + e + 2);
+                            const double x0 = h0.x - sp * y0.x, x1 = h0.y - sp * y0.y, x2 = h1.x - sp * y1.x, x3 = h1.y - sp * y1.y;
+                            a0 = fma(x0, x0, a0); a1 = fma(x1, x1, a1); a2 = fma(x2, x2, a2); a3 = fma(x3, x3, a3);
+                        }
+                    } else {
+#pragma unroll 1
+                        for (; e + 3 < qd; e += 4) {
+                            const double x0 = Hp[e] - sp * H0[e], x1 = Hp[e + 1] - sp * H0[e + 1];
+                            const double x2 = Hp[e + 2] - sp * H0[e + 2], x3 = Hp[e + 3] - sp * H0[e + 3];
+                            a0 = fma(x0, x0, a0); a1 = fma(x1, x1, a1); a2 = fma(x2, x2, a2); a3 = fma(x3, x3, a3);
+                        }
+                    }
+                    if (e < qd) { const double x = Hp[e] - sp * H0[e]; a0 = fma(x, x, a0); ++e; }
+                    if (e < qd) { const double x = Hp[e] - sp * H0[e]; a1 = fma(x, x, a1); ++e; }
+                    if (e < qd) { const double x = Hp[e] - sp * H0[e]; a2 = fma(x, x, a2); }
+                    const double nr = (a0 + a1) + (a2 + a3);
+                    const double viol = a - t;
+                    const double score = dantzig ? viol : viol * viol / nr;
+                    if (score > best) { best = score; pe = p; }
+                }
+                warp_argmax_nn(best, pe);
+            } else {  // the violated basic row with the lowest row index
                 int bp = -1; double key = 0.0;
 #pragma unroll 1
                 for (int p = 1 + s.lane; p < qd; p += 32)
@@ -700,7 +740,7 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
                 warp_argmax(key, bp);
                 pe = bp;
             }
-            if (pe < 0 || vmax <= t + tol) {
+            if (pe < 0) {
                 const int nv = qd < m ? qd + 1 : qd;
                 lp_image(s, nv);
                 double err = 0.0;
@@ -1149,7 +1189,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
 __device__ __forceinline__ int expand(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
                                       int gwarp, Counters &cnt, unsigned int *hist) {
     const int k0 = ((const int *)R)[0];
-    if (P.m - k0 + 1 <= P.QS) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
+    if (P.m - k0 + 1 <= QS_MAX) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
     return expand_impl<true>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
 }
 
@@ -1182,15 +1222,51 @@ __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS)
     return (d * 8 + i * 4 + 6 * nb + 15) / 16 * 16;
 }
 
+// Compile-time layout of the same block for the search kernels.  MC is the size class of the problem (m <= MC): every
+// array sits at a constant offset from the warp's base, so the compiler addresses all of them off ONE register with
+// immediate offsets instead of keeping (or recomputing) thirty pointers.
+template <int MC>
+struct SL {
+    static constexpr int V = MC + 2;             // doubles per vector (even, so everything stays 16-byte aligned)
+    static constexpr int H = QS_MAX * LDS_C;     // doubles per matrix
+    static constexpr int NB = MC + 8;            // bytes per byte array
+    static constexpr int o_vec = 2 * H;          // chat val w a v r c cpar brow al be
+    static constexpr int o_u = o_vec + 11 * V;
+    static constexpr int o_int = o_u + MC;       // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
+    static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
+    static constexpr size_t bytes = ((size_t)o_byte * 8 + 6 * NB + 15) / 16 * 16;
+};
+template <int MC>
+__device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
+    typedef SL<MC> L;
+    s.Ws_a = base; s.Ws_b = base + L::H;
+    double *v = base + L::o_vec;
+    s.chat = v; s.val = v + L::V; s.w = v + 2 * L::V; s.a = v + 3 * L::V; s.v = v + 4 * L::V; s.r = v + 5 * L::V;
+    s.c = v + 6 * L::V; s.cpar = v + 7 * L::V; s.brow = v + 8 * L::V; s.al = v + 9 * L::V; s.be = v + 10 * L::V;
+    s.u = (long long *)(base + L::o_u);
+    int *ib = (int *)(base + L::o_int);
+    s.zrow_a = ib; s.zrow_b = ib + L::V; s.pzrow = ib + 2 * L::V;
+    unsigned int *hist = (unsigned int *)(ib + 3 * L::V);
+    unsigned char *bb = (unsigned char *)(base + L::o_byte);
+    s.pos_a = bb; s.pos_b = bb + L::NB;
+    s.sg_a = (signed char *)(bb + 2 * L::NB); s.sg_b = (signed char *)(bb + 3 * L::NB); s.psg = (signed char *)(bb + 4 * L::NB);
+    s.ord = bb + 5 * L::NB;
+    s.chatpar = nullptr;
+    return hist;
+}
+__host__ inline int size_class(int m) { return m <= 32 ? 32 : (m <= 64 ? 64 : 96); }
+__host__ inline size_t fixed_warp_bytes(int mc) { return mc == 32 ? SL<32>::bytes : (mc == 64 ? SL<64>::bytes : SL<96>::bytes); }
+
 // ------------------------------------------------------------------------------------------------------------
 // The persistent kernel
 // ------------------------------------------------------------------------------------------------------------
+template <int MC>
 __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     extern __shared__ __align__(16) double smem[];
     const int n = P.n, m = P.m;
     double *Qs = smem;
-    for (int e = threadIdx.x; e < m * P.LDQ; e += blockDim.x) {
-        const int j = e / P.LDQ, i = e - j * P.LDQ;
+    for (int e = threadIdx.x; e < m * LDQ_C; e += blockDim.x) {
+        const int j = e / LDQ_C, i = e - j * LDQ_C;
         Qs[e] = i < m ? P.Qrev[(size_t)j * m + i] : 0.0;
     }
     __syncthreads();
@@ -1198,7 +1274,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     const int gwarp = blockIdx.x * P.warps_per_cta + warp;
     const RecLayout RL = rec_layout(n, m);
     WS s;
-    unsigned int *hist = carve_warp(s, smem + (size_t)m * P.LDQ + (size_t)warp * P.warp_smem_doubles, n, m, P.QS, P.LDS);
+    unsigned int *hist = carve_fixed<MC>(s, smem + (size_t)m * LDQ_C + (size_t)warp * (SL<MC>::bytes / 8));
     {
         double *wb = P.wbuf + (size_t)gwarp * P.wbuf_stride;
         s.Wpar = wb; wb += (size_t)m * m;
@@ -1206,9 +1282,9 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         s.Wg_b = wb; wb += (size_t)m * P.LDG;
         s.tmpA = wb;
     }
-    s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
-    s.Qsm = Qs; s.LDQsm = P.LDQ;
-    s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
+    s.LDS = LDS_C; s.LDG = P.LDG; s.QS = QS_MAX;
+    s.Qsm = Qs; s.LDQsm = LDQ_C;
+    s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
     use_side<false>(s, 0);
 #pragma unroll 1
@@ -1402,6 +1478,7 @@ struct BatchParams {
     unsigned long long timeout_ns;
     size_t warp_doubles;       // shared memory per warp: Q (m x LDQ) + the search block
 };
+template <int MC>
 __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams BP) {
     extern __shared__ __align__(16) double smem[];
     Params P = BP.P;
@@ -1409,7 +1486,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int gwarp = blockIdx.x * P.warps_per_cta + warp;
     double *Qs = smem + (size_t)warp * BP.warp_doubles;
-    double *wsm = Qs + (size_t)m * P.LDQ;
+    double *wsm = Qs + (size_t)m * LDQ_C;
     double *g = (double *)(BP.geo + (size_t)gwarp * BP.geo_stride);
     double *B = g; g += (size_t)n * m;
     double *pc = g; g += m;
@@ -1452,16 +1529,16 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
         if (r != 0) st = BLTCU_STATUS_LP_FAIL;  // dependent basis rows or a failed initial solve
         else {
 #pragma unroll 1
-            for (int e = lane; e < m * P.LDQ; e += 32) {
-                const int j = e / P.LDQ, i = e - j * P.LDQ;
+            for (int e = lane; e < m * LDQ_C; e += 32) {
+                const int j = e / LDQ_C, i = e - j * LDQ_C;
                 Qs[e] = i < m ? Qrev[(size_t)j * m + i] : 0.0;
             }
             WS s;
-            unsigned int *hist = carve_warp(s, wsm, n, m, P.QS, P.LDS);
+            unsigned int *hist = carve_fixed<MC>(s, wsm);
             s.Wpar = wb; s.Wg_a = wb + (size_t)m * m; s.Wg_b = s.Wg_a + (size_t)m * P.LDG; s.tmpA = s.Wg_b + (size_t)m * P.LDG;
-            s.LDS = P.LDS; s.LDG = P.LDG; s.QS = P.QS;
-            s.Qsm = Qs; s.LDQsm = P.LDQ;
-            s.Qs = Qs; s.LDQ = P.LDQ; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
+            s.LDS = LDS_C; s.LDG = P.LDG; s.QS = QS_MAX;
+            s.Qsm = Qs; s.LDQsm = LDQ_C;
+            s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
             s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
             use_side<false>(s, 0);
 #pragma unroll 1
@@ -1655,8 +1732,8 @@ struct Layout {
 // arena_recs: size of each warp's private stack in units of the largest record
 int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap,
                 int arena_recs) {
-    L.KQS = std::min(m, QS_MAX); L.LDS = ld_vec(L.KQS); L.LDG = m | 1; L.LDQ = ld_vec(std::min(m, L.KQS + 1));
-    L.warp_bytes = warp_smem_bytes(n, m, L.KQS, L.LDS);
+    L.KQS = QS_MAX; L.LDS = LDS_C; L.LDG = m | 1; L.LDQ = LDQ_C;
+    L.warp_bytes = fixed_warp_bytes(size_class(m));
     const size_t q_bytes = (size_t)m * L.LDQ * 8;
     int wpc = (int)((smem_budget > q_bytes ? smem_budget - q_bytes : 0) / L.warp_bytes);
     if (wpc > max_wpc) wpc = max_wpc;
@@ -1720,6 +1797,44 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
 }
 }  // namespace
 
+// the kernels are compiled once per size class of m (32, 64, 96): see SL<MC>
+static cudaError_t launch_search(int m, int ctas, int threads, size_t smem, cudaStream_t st, const Params &P) {
+    cudaError_t e;
+    switch (size_class(m)) {
+    case 32:
+        if ((e = cudaFuncSetAttribute(bltcu_search_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        bltcu_search_kernel<32><<<ctas, threads, smem, st>>>(P);
+        break;
+    case 64:
+        if ((e = cudaFuncSetAttribute(bltcu_search_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        bltcu_search_kernel<64><<<ctas, threads, smem, st>>>(P);
+        break;
+    default:
+        if ((e = cudaFuncSetAttribute(bltcu_search_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        bltcu_search_kernel<96><<<ctas, threads, smem, st>>>(P);
+        break;
+    }
+    return cudaGetLastError();
+}
+static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaStream_t st, const BatchParams &BP) {
+    cudaError_t e;
+    switch (size_class(m)) {
+    case 32:
+        if ((e = cudaFuncSetAttribute(bltcu_batch_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        bltcu_batch_kernel<32><<<ctas, threads, smem, st>>>(BP);
+        break;
+    case 64:
+        if ((e = cudaFuncSetAttribute(bltcu_batch_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        bltcu_batch_kernel<64><<<ctas, threads, smem, st>>>(BP);
+        break;
+    default:
+        if ((e = cudaFuncSetAttribute(bltcu_batch_kernel<96>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+        bltcu_batch_kernel<96><<<ctas, threads, smem, st>>>(BP);
+        break;
+    }
+    return cudaGetLastError();
+}
+
 static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
                        int64_t *sol, bltcu_stats *stats) {
     const auto t_start = std::chrono::steady_clock::now();
@@ -1750,7 +1865,6 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     P.donate_min_level = o.donate_min_level > 0 ? std::max(2, o.donate_min_level) : std::min(6, std::max(2, n / 3));
     P.no_early_exit = o.no_early_exit;
 
-    CK(cudaFuncSetAttribute(bltcu_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     int launches = 0;
     const size_t setup_smem = warp_smem_bytes(n, m, 0, 1);
     CK(cudaFuncSetAttribute(bltcu_setup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)setup_smem));
@@ -1811,8 +1925,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     };
     auto launch = [&]() -> int {
         CK(cudaEventRecord(w->e0, st));
-        bltcu_search_kernel<<<ctas, wpc * 32, smem_bytes, st>>>(P);
-        CK(cudaGetLastError());
+        CK(launch_search(m, ctas, wpc * 32, smem_bytes, st, P));
         CK(cudaEventRecord(w->e1, st));
         CK(cudaMemcpyAsync(&hq, P.q, sizeof hq, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -1820,6 +1933,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
         kernel_ms += ms;
         launches++;
+        if (verbose) fprintf(stderr, "bltcu: search launch %d (static depth %d): %.3f ms, %llu nodes, %u subtrees published\n", launches, P.static_depth, ms, (unsigned long long)hq.nodes, hq.out_count);
         if (hq.fail_info) lp_failed = true;
         if (hq.fail_info && verbose) {
             fprintf(stderr, "bltcu: LP failure code %d at level k=%d (basis size %d), u =", hq.fail_info & 255, (hq.fail_info >> 8) & 255, hq.fail_info >> 16);
@@ -1999,8 +2113,8 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     DevWs *w = nullptr;
     if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
 
-    const int KQS = std::min(m, QS_MAX), LDS = ld_vec(KQS), LDG = m | 1, LDQ = ld_vec(std::min(m, KQS + 1));
-    const size_t warp_bytes = warp_smem_bytes(n, m, KQS, LDS);
+    const int KQS = QS_MAX, LDS = LDS_C, LDG = m | 1, LDQ = LDQ_C;
+    const size_t warp_bytes = fixed_warp_bytes(size_class(m));
     const size_t per_warp = align_up((size_t)m * LDQ * 8 + warp_bytes, 16);
     int wpc = (int)std::min<size_t>(12, w->smem_optin / per_warp);
     if (o.warps_per_cta > 0 && o.warps_per_cta < wpc) wpc = o.warps_per_cta;
@@ -2065,10 +2179,8 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     CK(cudaMemcpyAsync(base + o_con, con + (size_t)lo * 2 * m, (size_t)mine * 2 * m * 8, cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(base + o_next, 0, 64, st));
     CK(cudaMemsetAsync(base + o_tot, 0, (5 + MAXD + 1) * 8, st));
-    CK(cudaFuncSetAttribute(bltcu_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
     CK(cudaEventRecord(w->e0, st));
-    bltcu_batch_kernel<<<ctas, wpc * 32, smem_bytes, st>>>(BP);
-    CK(cudaGetLastError());
+    CK(launch_batch(m, ctas, wpc * 32, smem_bytes, st, BP));
     CK(cudaEventRecord(w->e1, st));
     std::vector<unsigned long long> tot(5 + MAXD + 1), hni(mine), hnp(mine);
     std::vector<int> hfd(mine);
@@ -2288,9 +2400,7 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     }
     bltcu_noalloc_init_kernel<<<1, 256, 0, st>>>(P, deadline_ns, nwarps);  // one block: its barrier orders the clears
     CK(cudaGetLastError());
-    CK(cudaFuncSetAttribute(bltcu_search_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes));
-    bltcu_search_kernel<<<ctas, wpc * 32, smem_bytes, st>>>(P);
-    CK(cudaGetLastError());
+    CK(launch_search(m, ctas, wpc * 32, smem_bytes, st, P));
     static QCtl hq;  // host copies live in static storage: no heap use on the host either
     static int64_t h_bu[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * BLTCU_NOALLOC_MAX_DIM];
     static unsigned char h_bk[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * BLTCU_NOALLOC_MAX_DIM];

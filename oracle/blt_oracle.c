@@ -408,15 +408,36 @@ static int lp_solve(LP *lp, double radius, double cmax, double *d_out) {
         const double t = lp->val[0];
         if (!approximatelyLE(t, radius, DIST_EPS)) { if (iter == 0) lp->quick++; return NODE_PRUNE; }
         /* degenerate stalling: after STALL_MAX steps without progress switch to lowest-index (Bland) choices */
-        if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= STALL_MAX) bland = 1;
+        if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= 2 * STALL_MAX) bland = 1;
+        const int dantzig = stall >= STALL_MAX; /* first resort against stalling: leave by largest violation */
         const double tol = EPS_OPT * (cmax + t);
-        int pe = -1; double vmax = -1.0;
-        for (int p = 1; p < qd; ++p) if (fabs(lp->val[p]) > vmax) { vmax = fabs(lp->val[p]); pe = p; }
-        if (bland && pe >= 0 && vmax > t + tol) { /* the violated basic row with the lowest row index */
-            int br = -1;
-            for (int p = 1; p < qd; ++p) if (fabs(lp->val[p]) > t + tol && (br < 0 || lp->zrow[p] < br)) { br = lp->zrow[p]; pe = p; }
+        /* Pricing: among the basic rows outside the box (|r_z| > t + tol) the one with the steepest dual edge leaves,
+         * score = (|r_z| - t)^2 / |H[p] - se H[0]|^2.  The columns of N are orthonormal, so that norm IS the norm of the
+         * dual ray sum_j (n_j . rho)^2 -- exact dual steepest-edge weights for q flops per row, no recurrences.
+         * Ties: lowest position.  In Bland mode: the violated row with the lowest row index. */
+        int pe = -1; double best = -1.0; int br = -1;
+        for (int p = 1; p < qd; ++p) {
+            const double a = fabs(lp->val[p]);
+            if (!(a > t + tol)) continue;
+            if (bland) { if (br < 0 || lp->zrow[p] < br) { br = lp->zrow[p]; pe = p; } continue; }
+            const double se_p = lp->val[p] > 0.0 ? 1.0 : -1.0;
+            const double *Hp = lp->H + (size_t)p * lp->ld, *H0 = lp->H;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0; /* dot4 order */
+            int e = 0;
+            for (; e + 3 < qd; e += 4) {
+                const double x0 = Hp[e] - se_p * H0[e], x1 = Hp[e + 1] - se_p * H0[e + 1];
+                const double x2 = Hp[e + 2] - se_p * H0[e + 2], x3 = Hp[e + 3] - se_p * H0[e + 3];
+                a0 = fma(x0, x0, a0); a1 = fma(x1, x1, a1); a2 = fma(x2, x2, a2); a3 = fma(x3, x3, a3);
+            }
+            if (e < qd) { const double x = Hp[e] - se_p * H0[e]; a0 = fma(x, x, a0); ++e; }
+            if (e < qd) { const double x = Hp[e] - se_p * H0[e]; a1 = fma(x, x, a1); ++e; }
+            if (e < qd) { const double x = Hp[e] - se_p * H0[e]; a2 = fma(x, x, a2); }
+            const double nr = (a0 + a1) + (a2 + a3);
+            const double viol = a - t;
+            const double score = dantzig ? viol : viol * viol / nr;
+            if (score > best) { best = score; pe = p; }
         }
-        if (pe < 0 || vmax <= t + tol) {
+        if (pe < 0) {
             /* optimal by the books: verify the vertex against the data before trusting it */
             const int nv = qd < m ? qd + 1 : qd;
             lp_image(lp, nv);
