@@ -51,6 +51,8 @@
 #define LDQ_C 26   // row stride of the shared-memory copy of the first QS_MAX + 1 columns of Q: ld_vec(QS_MAX + 1)
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
+enum { C_NITER = 0, C_NPRUNE, C_NODES, C_DONATED, C_PIVOTS, C_QUICK, C_REFAC, C_COLDS, C_IDLE_NS, C_BUSY_NS, C_COUNT = 12 };
+#define CTR(s, k) do { if ((s).lane == 0) (s).ctr[k]++; } while (0)
 enum { REC_TOP = 1, REC_CONT = 2 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
 #define EAGER_MAX 4  // explored children a sibling loop produces before it is suspended in favour of its first child
 // REC_TOP: the record's children are the top level (first prune ends the search, closest.cc:280-286)
@@ -176,7 +178,7 @@ struct WS {
     const double *Qs;  // Qrev in shared memory, leading dimension LDQ
     int LDQ, n, m, qd, lane;
     double *al, *be;  // alpha_j = n_j . y, beta_j = n_j . H[pe] (shared memory, m each)
-    unsigned long long pivots, quick, refactors, colds;
+    unsigned long long *ctr;  // per-warp counters in shared memory (C_* below): they would cost twenty registers otherwise
     int failcode;  // why the last NODE_FAIL happened (diagnostics)
     unsigned int repairs;
     // the two sides of the level being expanded, and the parent's vertex
@@ -554,7 +556,7 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
         s.zrow[pe] = l; s.pos[l] = (unsigned char)pe;
     }
     __syncwarp();
-    s.pivots++;
+    CTR(s, C_PIVOTS);
     return 0;
 }
 __device__ __forceinline__ int lp_init1(WS &s) {
@@ -569,7 +571,7 @@ __device__ __forceinline__ int lp_init1(WS &s) {
     const double sum = butterfly(part);
     if (!(sum > 0.0)) return -1;
     if (s.lane == 0) { s.W[0] = 1.0 / sum; s.zrow[0] = -1; }
-    s.qd = 1; s.colds++;
+    s.qd = 1; CTR(s, C_COLDS);
     __syncwarp();
     return 0;
 }
@@ -648,7 +650,7 @@ __device__ __noinline__ int lp_refactor_impl(double *H, int LD, double *A, const
     return rc;
 }
 __device__ __forceinline__ int lp_refactor(WS &s) {
-    s.refactors++;
+    CTR(s, C_REFAC);
     return lp_refactor_impl(s.W, s.LD, s.tmpA, s.Qs, s.LDQ, s.qd, s.m, s.pos, s.sg, s.zrow, s.lane);
 }
 __device__ __forceinline__ void lp_image(WS &s, int nv) {
@@ -686,7 +688,7 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
         if (art) { pe = qd - 1; se = art; }
         else {
             const double t = s.val[0];
-            if (!approxLE(t, radius)) { if (iter == 0) s.quick++; return NODE_PRUNE; }
+            if (!approxLE(t, radius)) { if (iter == 0) CTR(s, C_QUICK); return NODE_PRUNE; }
             // degenerate stalling: after STALL_MAX steps without progress leave by largest violation, after twice as many
             // switch to lowest-index (Bland) choices
             if (t > tbest * (1.0 + 1.0e-12)) { tbest = t; stall = 0; } else if (++stall >= 2 * STALL_MAX) bland = true;
@@ -874,7 +876,6 @@ __device__ bool check_soln_dev(const Params &P, const long long *u, int lane) {
 // ------------------------------------------------------------------------------------------------------------
 // One task = the sibling loop below one explored node
 // ------------------------------------------------------------------------------------------------------------
-struct Counters { unsigned long long niter, nprune, nodes, donated; };
 
 // per-warp private stack of pending records (global memory): [abot, acount) entries of the offset table are live
 struct Arena {
@@ -920,7 +921,7 @@ __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL
 // the queue or the static-split output.
 template <bool BIG>
 __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
-                      int gwarp, Counters &cnt, unsigned int *hist) {
+                      int gwarp, unsigned int *hist) {
     const int n = P.n, m = P.m, lane = s.lane;
     const RecLayout RL = rec_layout(n, m);
     const int k0 = ((const int *)R)[0];
@@ -1006,7 +1007,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
             cmax = warp_max(cmax);
             __syncwarp();
         }
-        cnt.nodes++; if (lane == 0) hist[kk]++;
+        if (lane == 0) { s.ctr[C_NODES]++; hist[kk]++; }
         int status;
         double gn = 0.0;
         if (k0 == 1) {
@@ -1060,12 +1061,12 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         }
         if (status == NODE_PRUNE) {
             if (is_top) return nkept;  // closest.cc:280-286: first prune at the top level ends the search
-            cnt.nprune++;
+            CTR(s, C_NPRUNE);
             if (pruned) return nkept;  // second prune: the level is left
             pruned = true;
         } else if (k0 > 1) {
             // explored inner node: its children are one more task
-            cnt.niter++;
+            CTR(s, C_NITER);
             unsigned char *C = nullptr;
             int slot = -1, dest = 0;  // dest: 0 next, 1 arena, 2 queue, 3 static-split output
             const size_t need = rec_bytes(RL, m, k0 - 1);
@@ -1097,7 +1098,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                     if (dest == 3) { const unsigned int o = atomicAdd(&P.q->out_count, 1u); P.out_list[o] = slot; }
                     else { atomicAdd(&P.q->pending, 1); ring_push(P.q, &P.q->tail, P.ring, P.ring_mask, slot); }
                 }
-                cnt.donated++;
+                CTR(s, C_DONATED);
             }
         } else {
             // leaf: record, closest.cc:300-312
@@ -1134,7 +1135,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
             if (n == 1) return nkept;  // D4 of oracle/blt_oracle.c
             // explore(), closest.cc:99-104: the leaf level is abandoned and the parent level moves on (its loop has
             // already run here), so this task simply ends
-            cnt.niter++;
+            CTR(s, C_NITER);
             return nkept;
         }
         // next sibling, closest.cc:118-121
@@ -1179,7 +1180,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
             else {
                 __threadfence();
                 if (lane == 0) { atomicAdd(&P.q->pending, 1); ring_push(P.q, &P.q->tail, P.ring, P.ring_mask, slot); }
-                cnt.donated++;
+                CTR(s, C_DONATED);
             }
             return nkept;
         }
@@ -1187,10 +1188,10 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
 }
 
 __device__ __forceinline__ int expand(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
-                                      int gwarp, Counters &cnt, unsigned int *hist) {
+                                      int gwarp, unsigned int *hist) {
     const int k0 = ((const int *)R)[0];
-    if (P.m - k0 + 1 <= QS_MAX) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
-    return expand_impl<true>(P, s, R, pool_slot, next, A, gwarp, cnt, hist);
+    if (P.m - k0 + 1 <= QS_MAX) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, hist);
+    return expand_impl<true>(P, s, R, pool_slot, next, A, gwarp, hist);
 }
 
 // carves the per-warp shared-memory block; returns the node histogram
@@ -1202,6 +1203,7 @@ __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, 
     s.r = base; base += m; s.c = base; base += m; s.cpar = base; base += m; s.brow = base; base += m;
     s.al = base; base += m; s.be = base; base += m;
     s.u = (long long *)base; base += n;
+    s.ctr = (unsigned long long *)base; base += C_COUNT;
     int *ib = (int *)base;
     s.zrow_a = ib; ib += M1; s.zrow_b = ib; ib += M1; s.pzrow = ib; ib += M1;
     unsigned int *hist = (unsigned int *)ib; ib += n + 1;
@@ -1216,7 +1218,7 @@ __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, 
 }
 __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS) {
     const size_t M1 = (size_t)m + 1;
-    const size_t d = 2 * (size_t)QS * LDS + 5 * M1 + 6 * (size_t)m + n;
+    const size_t d = 2 * (size_t)QS * LDS + 5 * M1 + 6 * (size_t)m + n + C_COUNT;
     const size_t i = 3 * M1 + (size_t)(n + 1);
     const size_t nb = (size_t)((n > m ? n : m) + 8) / 8 * 8;
     return (d * 8 + i * 4 + 6 * nb + 15) / 16 * 16;
@@ -1232,7 +1234,8 @@ struct SL {
     static constexpr int NB = MC + 8;            // bytes per byte array
     static constexpr int o_vec = 2 * H;          // chat val w a v r c cpar brow al be
     static constexpr int o_u = o_vec + 11 * V;
-    static constexpr int o_int = o_u + MC;       // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
+    static constexpr int o_ctr = o_u + MC;       // C_COUNT counters
+    static constexpr int o_int = o_ctr + C_COUNT; // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
     static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
     static constexpr size_t bytes = ((size_t)o_byte * 8 + 6 * NB + 15) / 16 * 16;
 };
@@ -1244,6 +1247,7 @@ __device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
     s.chat = v; s.val = v + L::V; s.w = v + 2 * L::V; s.a = v + 3 * L::V; s.v = v + 4 * L::V; s.r = v + 5 * L::V;
     s.c = v + 6 * L::V; s.cpar = v + 7 * L::V; s.brow = v + 8 * L::V; s.al = v + 9 * L::V; s.be = v + 10 * L::V;
     s.u = (long long *)(base + L::o_u);
+    s.ctr = (unsigned long long *)(base + L::o_ctr);
     int *ib = (int *)(base + L::o_int);
     s.zrow_a = ib; s.zrow_b = ib + L::V; s.pzrow = ib + 2 * L::V;
     unsigned int *hist = (unsigned int *)(ib + 3 * L::V);
@@ -1285,7 +1289,8 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     s.LDS = LDS_C; s.LDG = P.LDG; s.QS = QS_MAX;
     s.Qsm = Qs; s.LDQsm = LDQ_C;
     s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-    s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
+    s.repairs = 0; s.failcode = 0;
+    if (lane < C_COUNT) s.ctr[lane] = 0ull;
     use_side<false>(s, 0);
 #pragma unroll 1
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
@@ -1297,10 +1302,9 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     __syncwarp();
     unsigned char *nextbuf = P.nextrec + (size_t)gwarp * 2 * RL.stride;
     int nextsel = 0, have_next = 0;
-    Counters cnt = {0, 0, 0, 0};
     QCtl *q = P.q;
     bool am_idle = false, have_token = false;
-    unsigned long long t_idle = 0, t_busy = 0, t_mark = gtimer();
+    unsigned long long t_mark = gtimer();
     for (;;) {
         const unsigned char *R = nullptr;
         int slot = -1;
@@ -1344,10 +1348,10 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         }
         // a popped stack record sits where new children would be pushed: expand() copies what it needs first, and the
         // stack top was lowered above, so the children overwrite it only after it is dead
-        { const unsigned long long t = gtimer(); t_idle += t - t_mark; t_mark = t; }
-        have_next = expand(P, s, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, cnt, hist);
+        { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_IDLE_NS] += t - t_mark; t_mark = t; }
+        have_next = expand(P, s, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
         __syncwarp();
-        { const unsigned long long t = gtimer(); t_busy += t - t_mark; t_mark = t; }
+        { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_BUSY_NS] += t - t_mark; t_mark = t; }
         // hand the oldest pending record to an idle warp
         if (P.dynamic && A.acount > A.abot) {
             int want = 0, dslot = -1;
@@ -1366,7 +1370,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
                 __threadfence();
                 if (lane == 0) { atomicAdd(&q->pending, 1); ring_push(q, &q->tail, P.ring, P.ring_mask, dslot); }
                 A.abot++;
-                cnt.donated++;
+                CTR(s, C_DONATED);
                 if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; __syncwarp(); }
             }
         }
@@ -1374,12 +1378,11 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     if (lane == 0) {
         if (have_token) { __threadfence(); atomicSub(&q->pending, 1); }
         if (am_idle) atomicSub(&q->idle, 1);
-        atomicAdd(&q->niter, cnt.niter); atomicAdd(&q->nprune, cnt.nprune); atomicAdd(&q->nodes, cnt.nodes);
-        atomicAdd(&q->donated, cnt.donated);
-        atomicAdd(&q->pivots, s.pivots); atomicAdd(&q->quick, s.quick); atomicAdd(&q->refactors, s.refactors);
-        atomicAdd(&q->colds, s.colds);
-        t_idle += gtimer() - t_mark;
-        atomicAdd(&q->idle_ns, t_idle); atomicAdd(&q->busy_ns, t_busy);
+        atomicAdd(&q->niter, s.ctr[C_NITER]); atomicAdd(&q->nprune, s.ctr[C_NPRUNE]); atomicAdd(&q->nodes, s.ctr[C_NODES]);
+        atomicAdd(&q->donated, s.ctr[C_DONATED]);
+        atomicAdd(&q->pivots, s.ctr[C_PIVOTS]); atomicAdd(&q->quick, s.ctr[C_QUICK]); atomicAdd(&q->refactors, s.ctr[C_REFAC]);
+        atomicAdd(&q->colds, s.ctr[C_COLDS]);
+        atomicAdd(&q->idle_ns, s.ctr[C_IDLE_NS] + (gtimer() - t_mark)); atomicAdd(&q->busy_ns, s.ctr[C_BUSY_NS]);
     }
     __syncwarp();
 #pragma unroll 1
@@ -1407,7 +1410,9 @@ __device__ __forceinline__ int setup_warp(const int64_t *lat, const int64_t *con
         s.LDS = 1; s.LDG = m | 1; s.QS = 0;
         use_side<true>(s, 0);
         s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-        s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0;
+        s.repairs = 0;
+        if (lane < C_COUNT) s.ctr[lane] = 0ull;
+        __syncwarp();
         const RecLayout RL = rec_layout(n, m);
         const int qpar = m - n;
         double cm = 0.0, d = 0.0, vq = 0.0;
@@ -1442,7 +1447,8 @@ __device__ __forceinline__ int setup_warp(const int64_t *lat, const int64_t *con
 #pragma unroll 1
             for (int j = lane; j < m; j += 32) ((double *)(rec + RL.off_cpar))[j] = p[j];
         }
-        if (lane == 0) { cnt_out[0] = s.pivots; cnt_out[1] = s.colds; cnt_out[2] = s.refactors; cnt_out[3] = s.quick; }
+        __syncwarp();
+        if (lane == 0) { cnt_out[0] = s.ctr[C_PIVOTS]; cnt_out[1] = s.ctr[C_COLDS]; cnt_out[2] = s.ctr[C_REFAC]; cnt_out[3] = s.ctr[C_QUICK]; }
     }
     __syncwarp();
     return r;
@@ -1524,7 +1530,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
         __syncwarp();
         if (lane == 0) q->deadline_ns = deadline;
         int st = BLTCU_STATUS_OK, fnd = 0;
-        Counters cnt = {0, 0, 0, 0};
+        unsigned long long c_niter = 0, c_nprune = 0;
         const int r = setup_warp(lat, con, n, m, B, pc, Q, Qrev, Rm, QTp, tmp, wb, nextbuf, wsm, sc, lane);
         if (r != 0) st = BLTCU_STATUS_LP_FAIL;  // dependent basis rows or a failed initial solve
         else {
@@ -1539,7 +1545,8 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
             s.LDS = LDS_C; s.LDG = P.LDG; s.QS = QS_MAX;
             s.Qsm = Qs; s.LDQsm = LDQ_C;
             s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-            s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0; s.failcode = 0;
+            s.repairs = 0; s.failcode = 0;
+            if (lane < C_COUNT) s.ctr[lane] = 0ull;
             use_side<false>(s, 0);
 #pragma unroll 1
             for (int e = lane; e <= n; e += 32) hist[e] = 0;
@@ -1558,7 +1565,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
                 int ab = 0;
                 if (lane == 0) ab = *(volatile int *)&q->abort;
                 if (__shfl_sync(FULLMASK, ab, 0)) break;
-                have_next = expand(P, s, R, -1, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, cnt, hist);
+                have_next = expand(P, s, R, -1, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
                 __syncwarp();
             }
             __threadfence();
@@ -1575,13 +1582,15 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
                     for (int e = lane; e < n; e += 32) sol[e] = P.best_u[(size_t)gwarp * n + e];
                 }
             }
-            t_nodes += cnt.nodes + 1; t_piv += s.pivots + sc[0]; t_cold += s.colds + sc[1]; t_ref += s.refactors + sc[2];
-            t_quick += s.quick + sc[3];
+            __syncwarp();
+            c_niter = s.ctr[C_NITER]; c_nprune = s.ctr[C_NPRUNE];
+            t_nodes += s.ctr[C_NODES] + 1; t_piv += s.ctr[C_PIVOTS] + sc[0]; t_cold += s.ctr[C_COLDS] + sc[1];
+            t_ref += s.ctr[C_REFAC] + sc[2]; t_quick += s.ctr[C_QUICK] + sc[3];
 #pragma unroll 1
             for (int e = lane; e <= n; e += 32) if (hist[e]) atomicAdd(&BP.totals[5 + e], (unsigned long long)hist[e]);
             if (lane == 0) atomicAdd(&BP.totals[5 + n], 1ull);
         }
-        if (lane == 0) { BP.status[inst] = st; BP.found[inst] = fnd; BP.niter[inst] = cnt.niter; BP.nprune[inst] = cnt.nprune; }
+        if (lane == 0) { BP.status[inst] = st; BP.found[inst] = fnd; BP.niter[inst] = c_niter; BP.nprune[inst] = c_nprune; }
         __syncwarp();
     }
     if (lane == 0) {
@@ -1616,7 +1625,9 @@ __global__ void bltcu_infdist_kernel(const double *B, int n, int m, const int64_
     s.LDS = 1; s.LDG = m | 1; s.QS = 0;
     use_side<true>(s, 0);
     s.Qs = Qrev; s.LDQ = m; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-    s.pivots = s.quick = s.refactors = s.colds = 0; s.repairs = 0;
+    s.repairs = 0;
+    if (lane < C_COUNT) s.ctr[lane] = 0ull;
+    __syncwarp();
     int r = geo_build_warp(B, p, n, m, Q, Qrev, Rm, QTp, tmp, tmp + m, lane);
     double cm = 0.0;
 #pragma unroll 1
