@@ -53,8 +53,10 @@
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
 enum { C_NITER = 0, C_NPRUNE, C_NODES, C_DONATED, C_PIVOTS, C_QUICK, C_REFAC, C_COLDS, C_IDLE_NS, C_BUSY_NS, C_COUNT = 12 };
 #define CTR(s, k) do { if ((s).lane == 0) (s).ctr[k]++; } while (0)
-enum { REC_TOP = 1, REC_CONT = 2 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
-#define EAGER_MAX 4  // explored children a sibling loop produces before it is suspended in favour of its first child
+enum { REC_TOP = 1, REC_CONT = 2, REC_DIVE = 4 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
+// REC_DIVE: this record is on the very first descent of the search (the reference's first dive towards the Babai
+// point): its loop is parked after the first explored child so that the first leaf is reached in n node latencies
+#define EAGER_MAX 8  // explored children a sibling loop produces before it is suspended in favour of its first child
 // REC_TOP: the record's children are the top level (first prune ends the search, closest.cc:280-286)
 
 // ------------------------------------------------------------------------------------------------------------
@@ -929,6 +931,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     double xc0 = ((const double *)R)[1];
     double gb = ((const double *)R)[2];
     const bool is_top = (rflags & REC_TOP) != 0, is_cont = (rflags & REC_CONT) != 0;
+    const int emax = (rflags & REC_DIVE) ? 1 : P.eager_max;
     const int c_step = ((const int *)R)[6], c_state = ((const int *)R)[7];
     const int kk = k0 - 1, qd0 = m - kk, qpar = m - k0;
 
@@ -1089,6 +1092,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 }
             }
             write_child(P, RL, s, C, k0, xlast, gn);
+            if ((rflags & REC_DIVE) && dest == 0 && lane == 0) ((int *)C)[1] = REC_DIVE;
             nexp++;
             if (dest == 0) nkept = 1;
             else if (dest == 1) { if (lane == 0) A.offs[A.acount + 1] = (int)(A.offs[A.acount] + need); A.acount++; __syncwarp(); }
@@ -1144,7 +1148,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         __syncwarp();
         // Wide level or little stack space left: park the rest of this loop and go down into the first child, the way
         // the depth-first order would.  The parked loop is a record like any other (it can even be donated).
-        if (status == NODE_EXPLORE && !forced && k0 > 1 && (nexp >= P.eager_max || (size_t)A.offs[A.acount] * 2 > A.cap)) {
+        if (status == NODE_EXPLORE && !forced && k0 > 1 && (nexp >= emax || (size_t)A.offs[A.acount] * 2 > A.cap)) {
             const ContLayout CL = cont_layout(RL, m, k0);
             unsigned char *C = nullptr;
             int slot = -1;
@@ -1443,7 +1447,7 @@ __device__ __forceinline__ int setup_warp(const int64_t *lat, const int64_t *con
         if (r == 0) {
             const double gb = QTp[n - 1];
             const double xlast = (gb - vq) / Rm[(size_t)(n - 1) * n + (n - 1)];
-            if (lane == 0) { ((int *)rec)[0] = n; ((int *)rec)[1] = REC_TOP; ((double *)rec)[1] = xlast; ((double *)rec)[2] = gb; }
+            if (lane == 0) { ((int *)rec)[0] = n; ((int *)rec)[1] = REC_TOP | REC_DIVE; ((double *)rec)[1] = xlast; ((double *)rec)[2] = gb; }
 #pragma unroll 1
             for (int j = lane; j < m; j += 32) ((double *)(rec + RL.off_cpar))[j] = p[j];
         }
@@ -1875,6 +1879,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     P.lat = d_lat; P.con = d_con;
     P.donate_min_level = o.donate_min_level > 0 ? std::max(2, o.donate_min_level) : std::min(6, std::max(2, n / 3));
     P.no_early_exit = o.no_early_exit;
+    if (o.eager > 0) P.eager_max = o.eager;
 
     int launches = 0;
     const size_t setup_smem = warp_smem_bytes(n, m, 0, 1);

@@ -17,7 +17,8 @@ _LIB = None
 class Opts(ctypes.Structure):
     _fields_ = [("device", ctypes.c_int), ("rank", ctypes.c_int), ("world", ctypes.c_int),
                 ("split_depth", ctypes.c_int), ("donate_min_level", ctypes.c_int), ("no_early_exit", ctypes.c_int),
-                ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int), ("timeout_ms", ctypes.c_int)]
+                ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int), ("timeout_ms", ctypes.c_int),
+                ("eager", ctypes.c_int)]
 
 
 class Stats(ctypes.Structure):

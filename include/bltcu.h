@@ -38,6 +38,8 @@ typedef struct bltcu_opts {
     int ctas;            /* 0 = one per SM */
     int timeout_ms;      /* device-side watchdog: give up with BLT_STATUS_ERROR after this long (0 = env
                             BLTCU_TIMEOUT_MS, else none) */
+    int eager;           /* explored children a warp collects on one level before it descends into the first (0 = default;
+                            1 = each warp descends at once, the reference's depth-first order inside a subtree) */
 } bltcu_opts;
 
 /* Statistics of one search.  niter/nprune are SolverStats of libblt/closest.h:14-17. */

@@ -183,3 +183,17 @@ def test_bench_workload_full_size(gpu, golden, fixture):
         assert g["rc"] == 0
         tot += g["nodes"]
     assert tot == int(z["nodes"])
+
+
+@pytest.mark.parametrize("name", ["test_95", "test_50_8"])
+def test_first_dive_reaches_the_babai_point(gpu, golden, name):
+    """The reference finds these two JPEG instances on its first descent (65 solves).  The first descent of the GPU search
+    is flagged to go down after the first explored child of every level, so a single warp needs exactly as many."""
+    z = np.load(f"{golden}/jpeg_reduced.npz")
+    lat, con = z[f"lat_{name}"], z[f"con_{name}"]
+    got = gpu.closest(lat, con, ctas=1, warps_per_cta=1)
+    assert got["rc"] == 0 and got["found"] and oracle.check_soln(lat, con, got["sol"])
+    assert got["nodes"] == int(z[f"nodes_{name}"]) == 65
+    assert (got["sol"] == z[f"sol_{name}"]).all()
+    full = gpu.closest(lat, con)
+    assert full["rc"] == 0 and full["found"] and oracle.check_soln(lat, con, full["sol"])
