@@ -6,7 +6,7 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = [os.path.join(HERE, "csrc", "search.cu"), os.path.join(HERE, "csrc", "peaks.cu"),
-       os.path.join(HERE, "csrc", "host", "lll.cpp")]
+       os.path.join(HERE, "csrc", "lll_batch.cu"), os.path.join(HERE, "csrc", "host", "lll.cpp")]
 HOST_SRC = [os.path.join(HERE, "csrc", "host", f) for f in ("context.cpp", "blt_api.cpp")]
 HOST_HDR = [os.path.join(HERE, "csrc", "host", "context.h"), os.path.join(HERE, "..", "include", "blt.h"),
             os.path.join(HERE, "..", "include", "codes.h")]
@@ -19,7 +19,7 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    deps = SRC + [os.path.join(HERE, "..", "include", "bltcu.h")]
+    deps = SRC + [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h")]
     if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in deps):
         build_host()
         return OUT

@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "../../../include/bltcu.h"
+#include "../lll_fixed.h"
 
 namespace {
 
@@ -332,5 +333,32 @@ extern "C" int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank) {
         for (int j = 0; j < c; ++j) B[(size_t)i * c + j] = S.B[i][j].to_i64();
         if (U) for (int j = 0; j < r; ++j) U[(size_t)i * r + j] = S.U[i][j].to_i64();
     }
+    return BLTCU_STATUS_OK;
+}
+
+// Test seam (not in include/bltcu.h): the fixed-capacity implementation that the batched device kernel runs, executed
+// on the host, so that its arithmetic can be pinned against the arbitrary-precision one without a GPU.
+// limbs: 8, 16 or 32 (x 32 bits).  Returns BLT_STATUS_ERROR when a number did not fit.
+extern "C" int bltcu_lll_fixed_host(int64_t *B, int64_t *U, int r, int c, int *rank, int limbs) {
+    if (!B || r <= 0 || c <= 0 || !rank) return BLTCU_STATUS_INPUT_ERROR;
+    long bytes = 0;
+    switch (limbs) {
+    case 8: bytes = lllfix::bytes_needed<8>(r, c); break;
+    case 16: bytes = lllfix::bytes_needed<16>(r, c); break;
+    case 32: bytes = lllfix::bytes_needed<32>(r, c); break;
+    default: return BLTCU_STATUS_INPUT_ERROR;
+    }
+    void *work = malloc((size_t)bytes);
+    if (!work) return BLTCU_STATUS_ERROR;
+    std::vector<int64_t> b(B, B + (size_t)r * c), u((size_t)r * r);
+    int rk = -1;
+    if (limbs == 8) rk = lllfix::reduce_one<8>(b.data(), u.data(), r, c, work);
+    else if (limbs == 16) rk = lllfix::reduce_one<16>(b.data(), u.data(), r, c, work);
+    else rk = lllfix::reduce_one<32>(b.data(), u.data(), r, c, work);
+    free(work);
+    if (rk < 0) return BLTCU_STATUS_ERROR;
+    memcpy(B, b.data(), b.size() * 8);
+    if (U) memcpy(U, u.data(), u.size() * 8);
+    *rank = rk;
     return BLTCU_STATUS_OK;
 }

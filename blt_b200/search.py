@@ -51,6 +51,11 @@ def lib() -> ctypes.CDLL:
         L.bltcu_closest_dev.restype = ctypes.c_int
         L.bltcu_lll.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
         L.bltcu_lll.restype = ctypes.c_int
+        L.bltcu_lll_batch.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int),
+                                      ctypes.c_int, ctypes.POINTER(Stats)]
+        L.bltcu_lll_batch.restype = ctypes.c_int
+        L.bltcu_lll_fixed_host.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+        L.bltcu_lll_fixed_host.restype = ctypes.c_int
         L.bltcu_check_soln.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
         L.bltcu_check_soln.restype = ctypes.c_int
         L.bltcu_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
@@ -210,3 +215,31 @@ def lll(B):
     if rc != BLT_STATUS_OK:
         raise RuntimeError(f"bltcu_lll failed with status {rc}")
     return int(rk.value), B, U
+
+
+def lll_batch(Bs, device: int = 0):
+    """Batched LLL on the GPU (bltcu_lll_batch): Bs is count x r x c.  Returns (ranks, reduced Bs, Us, info) with the same
+    bases and transforms a loop over lll() gives; info has kernel_ms, total_ms and on_host (problems whose numbers
+    outgrew the kernel's 512-bit integers and were reduced by the host implementation)."""
+    Bs = _i64(Bs).copy()
+    if Bs.ndim != 3:
+        raise ValueError("lll_batch wants Bs (count, r, c)")
+    count, r, c = Bs.shape
+    Us = np.zeros((count, r, r), dtype=np.int64)
+    ranks = np.zeros(count, dtype=np.int32)
+    st = Stats()
+    rc = lib().bltcu_lll_batch(_p(Bs, ctypes.c_int64), _p(Us, ctypes.c_int64), count, r, c, _p(ranks, ctypes.c_int), device,
+                               ctypes.byref(st))
+    if rc != BLT_STATUS_OK:
+        raise RuntimeError(f"bltcu_lll_batch failed with status {rc}")
+    return ranks, Bs, Us, dict(kernel_ms=float(st.kernel_ms), total_ms=float(st.total_ms), on_host=int(st.found))
+
+
+def lll_fixed_host(B, limbs: int = 16):
+    """Test seam: the kernel's fixed-capacity LLL executed on the host.  Returns (rc, rank, B, U)."""
+    B = _i64(B).copy()
+    r, c = B.shape
+    U = np.zeros((r, r), dtype=np.int64)
+    rk = ctypes.c_int(0)
+    rc = lib().bltcu_lll_fixed_host(_p(B, ctypes.c_int64), _p(U, ctypes.c_int64), r, c, ctypes.byref(rk), limbs)
+    return rc, int(rk.value), B, U

@@ -89,6 +89,13 @@ int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n
  * U * B_in = B_out (may be NULL).  Returns BLT_STATUS_OK or BLT_STATUS_INPUT_ERROR. */
 int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank);
 
+/* Batched LLL() for many small problems of one shape (configs 2 and 5 are reduction-bound).
+ * B: count x r x c, reduced in place; U: count x r x r out (may be NULL); rank: count.  One GPU warp reduces one problem
+ * with 512-bit exact integers, the same operations in the same order as bltcu_lll(), so basis and U are identical to
+ * what a loop over bltcu_lll() gives; a problem whose numbers outgrow 512 bits is reduced by bltcu_lll() on the host
+ * (stats->found, if stats is not NULL, reports how many).  Returns BLT_STATUS_OK / INPUT_ERROR / ERROR. */
+int bltcu_lll_batch(int64_t *B, int64_t *U, int count, int r, int c, int *rank, int device, bltcu_stats *stats);
+
 /* check_soln(): libblt/closest.cc:330-340, evaluated on the device (int64, wraps like the reference). */
 int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok);
 

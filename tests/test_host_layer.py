@@ -53,6 +53,38 @@ def test_lll_fixture_bases(golden):
         assert rk == rk2 == 64 and (Bo == _to_i64(B2)).all() and (Uo == _to_i64(U2)).all()
 
 
+def test_fixed_capacity_lll_equals_arbitrary_precision():
+    """The batched GPU kernel runs lll_fixed.h; here the same code runs on the host and must give the basis, the
+    transform and the rank of the arbitrary-precision implementation, or say that its numbers did not fit."""
+    rng = np.random.default_rng(7)
+    cases = []
+    for _ in range(120):
+        r, c = int(rng.integers(2, 22)), int(rng.integers(2, 22))
+        amax = int(rng.choice([3, 100, 10**4, 10**9]))
+        cases.append(rng.integers(-amax, amax + 1, size=(r, c)))
+    for _ in range(30):  # dependent rows
+        r, c = int(rng.integers(3, 14)), int(rng.integers(2, 10))
+        M = rng.integers(-50, 51, size=(r, c))
+        M[-1] = M[0] + 2 * M[1]
+        cases.append(M)
+    for _ in range(10):  # config 2: 40 x 20 of rank 20
+        cases.append(rng.integers(-100, 101, size=(40, 20)))
+    fitted = 0
+    for B in cases:
+        rk0, B0, U0 = blt_b200.lll(B)
+        for limbs in (16, 32):
+            rc, rk1, B1, U1 = blt_b200.lll_fixed_host(B, limbs)
+            if rc != blt_b200.BLT_STATUS_OK:
+                assert rc == blt_b200.BLT_STATUS_ERROR  # did not fit: said so, nothing truncated
+                continue
+            fitted += 1
+            assert rk1 == rk0 and (B1 == B0).all() and (U1 == U0).all()
+    assert fitted >= 250
+    # numbers that cannot fit 256 bits are reported, not truncated
+    big = rng.integers(-10**17, 10**17, size=(12, 12))
+    assert blt_b200.lll_fixed_host(big, 8)[0] == blt_b200.BLT_STATUS_ERROR
+
+
 def test_api_bookkeeping():  # libblt/test_context.cc:67-104 and blt.h contracts, no device needed
     ctx = api.Context()
     x, y = ctx.var("x"), ctx.var("y")
