@@ -35,7 +35,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-FIXTURE = os.path.join(ROOT, "tests", "golden", os.environ.get("BLT_BENCH_FIXTURE", "bench_dense60_w130.npz"))
+FIXTURE = os.path.join(ROOT, "tests", "golden", os.environ.get("BLT_BENCH_FIXTURE", "bench_dense60_w140.npz"))
 METRIC = "enum_nodes_per_s"
 UNIT = "nodes/s"
 

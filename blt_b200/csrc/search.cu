@@ -1862,7 +1862,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
     Layout L;
-    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 12, 4096, 64)) {
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 12, 16384, 64)) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }
@@ -1970,10 +1970,31 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     }
     if (o.split_depth > 0) {
         // phase A: deterministic static split of the top levels (every rank computes the same list)
-        initial.assign(1, 0);
-        if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
-        P.static_depth = o.split_depth; P.dynamic = 0;
-        if (launch()) return BLTCU_STATUS_ERROR;
+        // The depth is lowered until the published subtrees fill at most half of the record pool: the count is a property
+        // of the tree, so every rank settles on the same depth (a run can only run out of records above that count).
+        for (int depth = o.split_depth;; --depth) {
+            // the top-level record written by the setup kernel sits in slot 0; a failed attempt has consumed it
+            if (depth != o.split_depth) {
+                bltcu_setup_kernel<<<1, 32, setup_smem, st>>>(d_lat, d_con, n, m, (double *)P.B, (double *)P.p, (double *)(base + L.o_Q),
+                                                             (double *)P.Qrev, (double *)P.Rm, (double *)P.QTp, (double *)(base + L.o_tmp),
+                                                             (unsigned long long *)(base + L.o_rc), (int *)(base + L.o_rc + 8), P.wbuf,
+                                                             P.pool);
+                CK(cudaGetLastError());
+                launches++;
+                CK(cudaMemsetAsync(P.best_valid, 0, (size_t)nwarps * 4, st));
+            }
+            initial.assign(1, 0);
+            if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
+            P.static_depth = depth; P.dynamic = 0;
+            lp_failed = false;
+            if (launch()) return BLTCU_STATUS_ERROR;
+            const bool overflow = (hq.status == BLTCU_STATUS_ERROR && !hq.timed_out) || hq.out_count > (unsigned int)pool_cap / 2;
+            if (overflow && depth > 1 && !(hq.found && !o.no_early_exit)) {
+                if (verbose) fprintf(stderr, "bltcu: static split at depth %d publishes too many subtrees (%u), trying %d\n", depth, hq.out_count, depth - 1);
+                continue;
+            }
+            break;
+        }
         status = hq.status; found = hq.found;
         if (rank == 0) add_counts(hq);
         std::vector<int> out(hq.out_count);

@@ -166,7 +166,7 @@ def test_subset_sum_sat(gpu):  # config 3 shape, small
         assert oracle.check_soln(lat, con, got["sol"])
 
 
-@pytest.mark.parametrize("fixture", ["bench_dense60.npz", "bench_dense60_w120.npz", "bench_dense60_w130.npz"])
+@pytest.mark.parametrize("fixture", ["bench_dense60.npz", "bench_dense60_w120.npz", "bench_dense60_w130.npz", "bench_dense60_w140.npz"])
 def test_bench_workload_full_size(gpu, golden, fixture):
     """BASELINE.json's metric shape (n = m = 60) at full size (1.8 M and 6.3 M nodes): counts, histogram, pivots and uhat
     equal the values the oracle produced when the fixture was made (tests/golden/make_bench_fixture.py)."""
