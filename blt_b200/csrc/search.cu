@@ -240,34 +240,36 @@ __device__ __forceinline__ void dot4x2(int len, FA fa, FB fb, FC fc, double &r1,
 // The same sums in the same order with 16-byte loads (both operands 16-byte aligned): half the load instructions.
 __device__ __forceinline__ double dot4v(int len, const double *a, const double *b) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    int e = 0;
+    const double *ae = a + (len & ~3);  // pointers are bumped so that the loop carries no index arithmetic
 #pragma unroll 1
-    for (; e + 3 < len; e += 4) {
-        const double2 x0 = *(const double2 *)(a + e), x1 = *(const double2 *)(a + e + 2);
-        const double2 y0 = *(const double2 *)(b + e), y1 = *(const double2 *)(b + e + 2);
+    for (; a != ae; a += 4, b += 4) {
+        const double2 x0 = ((const double2 *)a)[0], x1 = ((const double2 *)a)[1];
+        const double2 y0 = ((const double2 *)b)[0], y1 = ((const double2 *)b)[1];
         a0 = fma(x0.x, y0.x, a0); a1 = fma(x0.y, y0.y, a1); a2 = fma(x1.x, y1.x, a2); a3 = fma(x1.y, y1.y, a3);
     }
-    if (e < len) { a0 = fma(a[e], b[e], a0); ++e; }
-    if (e < len) { a1 = fma(a[e], b[e], a1); ++e; }
-    if (e < len) { a2 = fma(a[e], b[e], a2); }
+    const int t = len & 3;
+    if (t > 0) a0 = fma(a[0], b[0], a0);
+    if (t > 1) a1 = fma(a[1], b[1], a1);
+    if (t > 2) a2 = fma(a[2], b[2], a2);
     return (a0 + a1) + (a2 + a3);
 }
 __device__ __forceinline__ void dot4x2v(int len, const double *a, const double *b, const double *c, double &r1, double &r2) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
-    int e = 0;
+    const double *ae = a + (len & ~3);
 #pragma unroll 1
-    for (; e + 3 < len; e += 4) {
-        const double2 x0 = *(const double2 *)(a + e), x1 = *(const double2 *)(a + e + 2);
-        const double2 y0 = *(const double2 *)(b + e), y1 = *(const double2 *)(b + e + 2);
-        const double2 z0 = *(const double2 *)(c + e), z1 = *(const double2 *)(c + e + 2);
+    for (; a != ae; a += 4, b += 4, c += 4) {
+        const double2 x0 = ((const double2 *)a)[0], x1 = ((const double2 *)a)[1];
+        const double2 y0 = ((const double2 *)b)[0], y1 = ((const double2 *)b)[1];
+        const double2 z0 = ((const double2 *)c)[0], z1 = ((const double2 *)c)[1];
         a0 = fma(x0.x, y0.x, a0); b0 = fma(x0.x, z0.x, b0);
         a1 = fma(x0.y, y0.y, a1); b1 = fma(x0.y, z0.y, b1);
         a2 = fma(x1.x, y1.x, a2); b2 = fma(x1.x, z1.x, b2);
         a3 = fma(x1.y, y1.y, a3); b3 = fma(x1.y, z1.y, b3);
     }
-    if (e < len) { const double x = a[e]; a0 = fma(x, b[e], a0); b0 = fma(x, c[e], b0); ++e; }
-    if (e < len) { const double x = a[e]; a1 = fma(x, b[e], a1); b1 = fma(x, c[e], b1); ++e; }
-    if (e < len) { const double x = a[e]; a2 = fma(x, b[e], a2); b2 = fma(x, c[e], b2); }
+    const int t = len & 3;
+    if (t > 0) { const double x = a[0]; a0 = fma(x, b[0], a0); b0 = fma(x, c[0], b0); }
+    if (t > 1) { const double x = a[1]; a1 = fma(x, b[1], a1); b1 = fma(x, c[1], b1); }
+    if (t > 2) { const double x = a[2]; a2 = fma(x, b[2], a2); b2 = fma(x, c[2], b2); }
     r1 = (a0 + a1) + (a2 + a3);
     r2 = (b0 + b1) + (b2 + b3);
 }
@@ -799,8 +801,17 @@ __device__ __forceinline__ int lp_solve(WS &s, double radius, double cmax, doubl
 // chain head: H (q x q packed), basic rows (q ints), signs (m bytes)
 __device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, signed char *dB) {
     const int q = s.qd, LD = s.LD;
+    if (q <= 32) {  // one lane per column: no index division
+        if (s.lane < q) {
+            const double *src = s.W + s.lane;
+            double *dst = dH + s.lane;
 #pragma unroll 1
-    for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; dH[x] = s.W[(size_t)i * LD + c]; }
+            for (int i = 0; i < q; ++i) dst[(size_t)i * q] = src[(size_t)i * LD];
+        }
+    } else {
+#pragma unroll 1
+        for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; dH[x] = s.W[(size_t)i * LD + c]; }
+    }
 #pragma unroll 1
     for (int p = s.lane; p < q; p += 32) dI[p] = s.zrow[p];
 #pragma unroll 1
@@ -810,8 +821,17 @@ __device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, si
 __device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *dI, const signed char *dB, int q) {
     const int LD = s.LD;
     s.qd = q;
+    if (q <= 32) {
+        if (s.lane < q) {
+            const double *src = dH + s.lane;
+            double *dst = s.W + s.lane;
 #pragma unroll 1
-    for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
+            for (int i = 0; i < q; ++i) dst[(size_t)i * LD] = src[(size_t)i * q];
+        }
+    } else {
+#pragma unroll 1
+        for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
+    }
 #pragma unroll 1
     for (int j = s.lane; j < s.m; j += 32) { s.sg[j] = dB[j]; s.pos[j] = 0; }
 #pragma unroll 1
