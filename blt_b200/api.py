@@ -42,6 +42,7 @@ def lib() -> ctypes.CDLL:
                                           ctypes.POINTER(ci), ctypes.POINTER(ctypes.c_double),
                                           ctypes.POINTER(ctypes.c_double)]
         L.blt_b200_last_stats.restype = ci
+        L.blt_check_batch.argtypes, L.blt_check_batch.restype = [ctypes.POINTER(vp), ci, ctypes.POINTER(ci)], ci
         _LIB = L
     return _LIB
 
@@ -116,3 +117,15 @@ class Context:
         if self.h:
             lib().blt_free(self.h)
             self.h = None
+
+
+def check_batch(contexts):
+    """blt_check_batch(): blt_check() for many contexts at once (one batched LLL and one batched search per shape on
+    the GPU).  Returns the list of per-context results (BLT_CHECK_SAT / BLT_CHECK_UNSAT / BLT_STATUS_*)."""
+    n = len(contexts)
+    hs = (ctypes.c_void_p * n)(*[c.h for c in contexts])
+    res = (ctypes.c_int * n)()
+    rc = lib().blt_check_batch(hs, n, res)
+    if rc != 0:
+        raise RuntimeError(f"blt_check_batch failed with status {rc}")
+    return list(res)

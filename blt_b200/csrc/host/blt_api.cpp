@@ -49,6 +49,10 @@ int blt_assume(CContext ctx, int64 ln, int64 ld, const CExpr ce, int64 un, int64
 
 int blt_check(CContext ctx) { return reinterpret_cast<Context *>(ctx)->check(); }
 
+int blt_check_batch(CContext *ctxs, int count, int *results) {
+    return check_batch(reinterpret_cast<Context **>(ctxs), count, results);
+}
+
 int blt_model(const CContext ctx, const char *name, int64 *val) {
     return reinterpret_cast<Context *>(ctx)->get_model(std::string(name), val);
 }

@@ -178,10 +178,12 @@ bool check_soln_host(const std::vector<int64> &lat, const std::vector<int64> &co
     return true;
 }
 
-int Context::check() {  // context.cc:139-280
-    using clk = std::chrono::steady_clock;
-    const size_t m = (size_t)nvars();       // lattice vectors (rows) = active variables
-    const size_t n = assumptions.size();    // constraints = dimension of the ambient space
+// Context::check() in three parts, so that the batch front-end below can run the two GPU seams for many contexts at
+// once: prepare (context.cc:139-174), reduced (context.cc:176-208), finish (context.cc:246-279).
+int Context::prepare(Prepared &p) {
+    p.m = (size_t)nvars();          // lattice vectors (rows) = active variables
+    p.n = assumptions.size();       // constraints = dimension of the ambient space
+    const size_t m = p.m, n = p.n;
     if (n == 0 || m == 0) {
         WARN("Context::check: zero-dimensional input lattice or constraint set");
         return BLT_STATUS_INPUT_ERROR;
@@ -197,50 +199,119 @@ int Context::check() {  // context.cc:139-280
         C0[2 * col] = assumptions[col].lower - c;
         C0[2 * col + 1] = assumptions[col].upper - c;
     }
-    std::vector<int64> L, C;
-    int rc = convert_to_integral(L0, C0, m, n, L, C);
+    int rc = convert_to_integral(L0, C0, m, n, p.L, p.C);
     if (rc != BLT_STATUS_OK) return rc;
-    rc = stretch_to_cube(L, C, m, n);
+    rc = stretch_to_cube(p.L, p.C, m, n);
     if (rc != BLT_STATUS_OK) return rc;
-
-    // reduction seam: rank = LLL(L, U), context.cc:176
-    std::vector<int64> U(m * m);
-    int rank = 0;
-    auto t0 = clk::now();
-    rc = bltcu_lll(L.data(), U.data(), (int)m, (int)n, &rank);
-    last.lll_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
-    if (rc != BLT_STATUS_OK) return rc;
+    p.U.assign(m * m, 0);
+    return BLT_STATUS_OK;
+}
+// after rank = LLL(L, U): the reduced basis is the last `rank` rows
+int Context::reduced(Prepared &p, int rank) {
     last.rank = rank;
     if (rank == 0) return BLT_STATUS_INPUT_ERROR;
-    std::vector<int64> newL((size_t)rank * n);
+    p.rank = rank;
+    p.newL.assign((size_t)rank * p.n, 0);
     for (size_t i = 0; i < (size_t)rank; ++i)
-        for (size_t j = 0; j < n; ++j) newL[i * n + j] = L[(i + m - rank) * n + j];
-
+        for (size_t j = 0; j < p.n; ++j) p.newL[i * p.n + j] = p.L[(i + p.m - rank) * p.n + j];
     if (enable_yices_) {  // context.cc:210-228: this build carries no Yices; same failure as a missing libyices.so
         ERROR("Context::check: ERROR Yices support was requested, but libyices.so failed to load!");
         return BLT_STATUS_ERROR;
     }
-
-    // search seam: closest(newL, C, yok, presoln_b, stats), context.cc:236
-    std::vector<int64> presoln_b((size_t)rank, 0);
-    bltcu_stats st;
-    t0 = clk::now();
-    rc = bltcu_closest_ex(newL.data(), C.data(), rank, (int)n, nullptr, presoln_b.data(), &st);
-    last.search_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
-    if (rc != BLT_STATUS_OK) return rc;
-    last.niter = st.niter; last.nprune = st.nprune;
-
+    p.presoln.assign((size_t)rank, 0);
+    return BLT_STATUS_OK;
+}
+int Context::finish(const Prepared &p, uint64_t niter, uint64_t nprune) {
+    const size_t m = p.m, n = p.n, rank = (size_t)p.rank;
+    last.niter = niter; last.nprune = nprune;
     // back-substitution soln = [0 .. 0 | presoln_b] * U, context.cc:246-254 (int64 products wrap like ublas prod)
     std::vector<int64> soln(m, 0);
     for (size_t j = 0; j < m; ++j) {
         uint64_t acc = 0;
-        for (size_t i = m - rank; i < m; ++i) acc += (uint64_t)presoln_b[i - (m - rank)] * (uint64_t)U[i * m + j];
+        for (size_t i = m - rank; i < m; ++i) acc += (uint64_t)p.presoln[i - (m - rank)] * (uint64_t)p.U[i * m + j];
         soln[j] = (int64)acc;
     }
     model.clear();
     for (size_t i = 0, j = 0; i < mask.size(); ++i)
         if (mask[i]) model[names[i]] = soln[j++];
-    return check_soln_host(newL, C, (size_t)rank, n, presoln_b) ? BLT_CHECK_SAT : BLT_CHECK_UNSAT;  // context.cc:276-279
+    return check_soln_host(p.newL, p.C, rank, n, p.presoln) ? BLT_CHECK_SAT : BLT_CHECK_UNSAT;  // context.cc:276-279
+}
+
+int Context::check() {  // context.cc:139-280
+    using clk = std::chrono::steady_clock;
+    Prepared p;
+    int rc = prepare(p);
+    if (rc != BLT_STATUS_OK) return rc;
+    // reduction seam: rank = LLL(L, U), context.cc:176
+    int rank = 0;
+    auto t0 = clk::now();
+    rc = bltcu_lll(p.L.data(), p.U.data(), (int)p.m, (int)p.n, &rank);
+    last.lll_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
+    if (rc != BLT_STATUS_OK) return rc;
+    rc = reduced(p, rank);
+    if (rc != BLT_STATUS_OK) return rc;
+    // search seam: closest(newL, C, yok, presoln_b, stats), context.cc:236
+    bltcu_stats st;
+    t0 = clk::now();
+    rc = bltcu_closest_ex(p.newL.data(), p.C.data(), rank, (int)p.n, nullptr, p.presoln.data(), &st);
+    last.search_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
+    if (rc != BLT_STATUS_OK) return rc;
+    return finish(p, st.niter, st.nprune);
+}
+
+// Many contexts at once (no counterpart in the reference): contexts of equal shape share
+// one bltcu_lll_batch() call, reduced problems of equal shape one bltcu_closest_batch() call.  results[i] is what
+// ctx[i]->check() would return; a model is left in every context that is SAT.
+int check_batch(Context **ctx, int count, int *results) {
+    if (count < 0 || (count > 0 && (!ctx || !results))) return BLT_STATUS_INPUT_ERROR;
+    std::vector<Prepared> P((size_t)count);
+    std::vector<char> live((size_t)count, 0);
+    for (int i = 0; i < count; ++i) {
+        if (!ctx[i]) { results[i] = BLT_STATUS_INPUT_ERROR; continue; }
+        results[i] = ctx[i]->prepare(P[i]);
+        live[i] = results[i] == BLT_STATUS_OK;
+    }
+    // ---- reduction, grouped by (m, n) ----
+    std::map<std::pair<size_t, size_t>, std::vector<int>> groups;
+    for (int i = 0; i < count; ++i) if (live[i]) groups[{P[i].m, P[i].n}].push_back(i);
+    for (auto &g : groups) {
+        const size_t m = g.first.first, n = g.first.second, k = g.second.size();
+        std::vector<int64> B(k * m * n), U(k * m * m);
+        std::vector<int> rank(k, 0);
+        for (size_t j = 0; j < k; ++j) std::copy(P[g.second[j]].L.begin(), P[g.second[j]].L.end(), B.begin() + j * m * n);
+        const int rc = bltcu_lll_batch(B.data(), U.data(), (int)k, (int)m, (int)n, rank.data(), 0, nullptr);
+        for (size_t j = 0; j < k; ++j) {
+            const int i = g.second[j];
+            if (rc != BLT_STATUS_OK) { results[i] = rc; live[i] = 0; continue; }
+            std::copy(B.begin() + j * m * n, B.begin() + (j + 1) * m * n, P[i].L.begin());
+            std::copy(U.begin() + j * m * m, U.begin() + (j + 1) * m * m, P[i].U.begin());
+            const int r2 = ctx[i]->reduced(P[i], rank[j]);
+            if (r2 != BLT_STATUS_OK) { results[i] = r2; live[i] = 0; }
+        }
+    }
+    // ---- search, grouped by (rank, n) ----
+    groups.clear();
+    for (int i = 0; i < count; ++i) if (live[i]) groups[{(size_t)P[i].rank, P[i].n}].push_back(i);
+    for (auto &g : groups) {
+        const size_t r = g.first.first, n = g.first.second, k = g.second.size();
+        std::vector<int64> lat(k * r * n), con(k * n * 2), sol(k * r);
+        std::vector<int> status(k, 0), found(k, 0);
+        std::vector<uint64_t> niter(k, 0), nprune(k, 0);
+        for (size_t j = 0; j < k; ++j) {
+            std::copy(P[g.second[j]].newL.begin(), P[g.second[j]].newL.end(), lat.begin() + j * r * n);
+            std::copy(P[g.second[j]].C.begin(), P[g.second[j]].C.end(), con.begin() + j * n * 2);
+        }
+        const int rc = bltcu_closest_batch(lat.data(), con.data(), (int)k, (int)r, (int)n, nullptr, sol.data(), status.data(),
+                                           niter.data(), nprune.data(), found.data(), nullptr);
+        for (size_t j = 0; j < k; ++j) {
+            const int i = g.second[j];
+            if (rc != BLT_STATUS_OK) { results[i] = rc; continue; }
+            if (status[j] != BLT_STATUS_OK) { results[i] = status[j]; continue; }
+            std::copy(sol.begin() + j * r, sol.begin() + (j + 1) * r, P[i].presoln.begin());
+            results[i] = ctx[i]->finish(P[i], niter[j], nprune[j]);
+        }
+    }
+    return BLT_STATUS_OK;
 }
 
 // ---- parser (libblt/parser.cc:72-166) -------------------------------------------------------------------------------

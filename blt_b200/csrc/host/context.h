@@ -89,7 +89,19 @@ public:
     int backtrack(SolvState);
     int get_model(const std::string &, int64 *) const;
     int check();
+
+    // the parts of check(), used one after the other by check() and in bulk by check_batch()
+    struct Prepared {
+        size_t m = 0, n = 0;
+        int rank = 0;
+        std::vector<int64> L, C, U, newL, presoln;
+    };
+    int prepare(Prepared &p);
+    int reduced(Prepared &p, int rank);
+    int finish(const Prepared &p, uint64_t niter, uint64_t nprune);
 };
+typedef Context::Prepared Prepared;
+int check_batch(Context **ctx, int count, int *results);
 
 // libblt/context.cc:405-501, on row-major vectors: L is nrows x ncols (rows = variables), C is ncols x 2
 int convert_to_integral(const std::vector<rat64> &L0, const std::vector<rat64> &C0, size_t nrows, size_t ncols,

@@ -2,24 +2,31 @@
 // and of its per-node layer-distance solve (infdist(), libblt/glpk_wrapper.cc:33-232).
 //
 // Execution model (DESIGN.md sections 3-5):
-//   * ONE persistent kernel per search, one CTA per SM, W warps per CTA.  A warp owns one depth-first search of
-//     one subtree at a time; its 32 lanes cooperate on that subtree's current node.
+//   * ONE persistent kernel per search, one CTA per SM, up to 12 warps per CTA.  A warp owns one task at a time; its
+//     32 lanes cooperate on that task's current node.
 //   * Geometry once per problem: B^T = Q R (Gram-Schmidt applied twice).  A node with kk free coefficients is the LP
 //         min |r|_inf   s.t.   N^T r = chat,      N = the last q = m - kk columns of Q,  chat = N^T c,
 //     i.e. a dual simplex whose basis is the set Z of the q-1 rows that are strictly inside the box, not the kk+1 rows
-//     on its boundary.  H = A^-1 (q x q) lives in shared memory while q <= 32 and in an L2-resident per-warp buffer
-//     above that.  Row 0 of H is the dual vector y; sg_j (n_j . y) >= 0 is the invariant, so t = y . chat is a valid
-//     lower bound at every step and a node is pruned as soon as the bound crosses the radius.
+//     on its boundary.  H = A^-1 (q x q) lives in shared memory while q <= QS_MAX = 24 (the template parameter BIG
+//     selects the home at compile time) and in an L2-resident per-warp buffer above that.  Row 0 of H is the dual
+//     vector y; sg_j (n_j . y) >= 0 is the invariant, so t = y . chat is a valid lower bound at every step and a node
+//     is pruned as soon as the bound crosses the radius.  Pricing is dual steepest edge with exact weights (the
+//     columns of N are orthonormal), the ratio test is Harris' two-pass test.
 //   * Going one level down adds one coordinate: H is bordered with an artificial column which is then pivoted out.
 //   * Warm starts ("side chains"): a node starts from the final vertex of the previous sibling on the same side of
 //     the level's real centre, or, for the first node of a side, from its parent's optimal vertex extended by the
 //     level's coordinate.  Both chains of the level being expanded live in shared memory.
 //   * A task is ONE sibling loop: all children of an explored node are solved back to back (the set of siblings
 //     visited depends only on their own LP outcomes, closest.cc:110-122), every explored child becomes a record: the
-//     first one is expanded next by the same warp, the others go on the warp's private stack in global memory.
+//     first one is expanded next by the same warp, the others go on the warp's private stack in global memory.  A
+//     loop that has produced EAGER_MAX explored children is parked as a continuation record; on the first descent of
+//     the search (REC_DIVE) it is parked after the first one, so that the first leaf is reached in n node latencies.
 //   * Load balance: a global MPMC queue of records.  A warp whose stack is non-empty while other warps are idle
 //     moves its OLDEST record (the largest subtree) to the queue.  Every node is solved exactly once, from the same
 //     starting vertex as in the sequential order, so niter and nprune do not depend on scheduling.
+//   * The shared-memory layout of a warp is a compile-time function of the size class of m (SL<MC>), so every array
+//     is addressed off one base register; per-warp counters live in shared memory too.
+//   * bltcu_batch_kernel: many small problems, one warp each, in the reference's own depth-first order.
 //
 // Floating point: every operation below has a twin in oracle/blt_oracle.c with the same operand order; compile
 // with -fmad=false so that only the explicit fma() calls fuse.  FP64 FMA pipe is the roofline (no tensor cores:

@@ -45,6 +45,13 @@ int blt_backtrack(CContext, CSolvState);
 /* libblt/blt.cc:109-120 */
 void blt_free(CContext);
 
+/* Extension, no counterpart in the reference (its globals forbid many checks in flight, libblt/blt.cc:22-23):
+ * blt_check() for `count` contexts at once.  Contexts of equal shape share one batched LLL and one batched search on
+ * the GPU (bltcu_lll_batch, bltcu_closest_batch); results[i] receives what blt_check(ctxs[i]) returns, and
+ * blt_model() works on every context afterwards as after blt_check().  Returns BLT_STATUS_OK unless the arguments
+ * are unusable. */
+int blt_check_batch(CContext *ctxs, int count, int *results);
+
 #ifdef __cplusplus
 }
 #endif

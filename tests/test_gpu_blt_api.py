@@ -151,3 +151,39 @@ def test_run_blt_dense_unsat(tmp_path):  # config 2/5 shape: n = 20, counters th
     assert ref["rc"] == UNSAT
     mt = re.search(r"BLT_STATS niter (\d+) nprune (\d+) rank (\d+)", r.stderr)
     assert (int(mt.group(1)), int(mt.group(2)), int(mt.group(3))) == (ref["niter"], ref["nprune"], 20)
+
+
+def test_check_batch_equals_single_checks(api):
+    """blt_check_batch (extension): the reference's own systems plus a pile of config-5-style dense systems, all in one
+    call; every decision equals blt_check's and the oracle's, every SAT context has a model that satisfies its rows."""
+    systems = [(rows, names, want) for _, rows, names, want in CASES]
+    rng = np.random.default_rng(11)
+    for i in range(40):  # 8 variables, 8 rows: A uniform on [-100, 100], common width (a mix of SAT and UNSAT)
+        A = rng.integers(-100, 101, size=(8, 8))
+        c = rng.integers(-10**6, 10**6 + 1, size=8)
+        w = int(rng.choice([60, 110, 160]))
+        rows = [(int(c[r]), [int(x) for x in A[r]], int(c[r]) + w, 0) for r in range(8)]
+        systems.append((rows, "abcdefgh", None))
+    ctxs = [_system(api, rows, names) for rows, names, _ in systems]
+    got = api.check_batch(ctxs)
+    nsat = 0
+    for (rows, names, want), ctx, g in zip(systems, ctxs, got):
+        ref = _oracle(rows, len(names))
+        assert g == ref["rc"]
+        if want is not None:
+            assert g == want
+        single = _system(api, rows, names)
+        assert single.check() == g
+        single.free()
+        if g == SAT:
+            nsat += 1
+            x = [ctx.model(nm)[1] for nm in names]
+            for lo, coef, hi, const in rows:
+                val = sum(c * xi for c, xi in zip(coef, x)) + const
+                assert lo <= val <= hi
+            st = ctx.last_stats()
+            assert st["niter"] == ref["niter"] and st["nprune"] == ref["nprune"]  # the batch search is the sequential order
+    assert 5 <= nsat < len(systems)
+    for ctx in ctxs:
+        ctx.free()
+    assert api.check_batch([]) == []
