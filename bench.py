@@ -196,7 +196,8 @@ def main():
     lat_d = lat_h.cuda(non_blocking=False)
     con_d = con_h.cuda(non_blocking=False)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    opts = dict(device=local_rank, rank=rank, world=world, split_depth=(6 if world > 1 else 0), timeout_ms=600000)
+    opts = dict(device=local_rank, rank=rank, world=world, split_depth=(6 if world > 1 else 0),
+                timeout_ms=int(os.environ.get("BLT_BENCH_TIMEOUT_MS", "600000")))  # 0 under ncu: replays outlast any deadline
 
     def barrier():
         torch.cuda.synchronize()
@@ -295,6 +296,12 @@ def main():
                 if pj.get("fixture") == os.path.basename(FIXTURE):
                     line["roofline"]["traffic"] = pj.get("dram_bytes_per_launch")
                     line["roofline"]["traffic_source"] = "profiles/r1_final_summary.json (ncu --set full, one launch)"
+                elif pj.get("dram_bytes_per_node"):
+                    # the capture was taken on a smaller instance of the same workload (a replay of this one outlasts
+                    # the search's watchdog): scaled by the node count, and said so
+                    line["roofline"]["traffic"] = pj["dram_bytes_per_node"] * nodes_all / args.steps
+                    line["roofline"]["traffic_source"] = (f"profiles/r1_final_summary.json: {pj['dram_bytes_per_node']:.0f} B/node measured "
+                                                          f"by ncu --set full on {pj.get('fixture')}, times the nodes of this launch")
         if not args.no_cpu and world == 1:
             v, cn, dt = cpu_sample(wl, args.cpu_nodes)
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": 1, "kind": "port",

@@ -352,9 +352,9 @@ extern "C" int bltcu_lll_fixed_host(int64_t *B, int64_t *U, int r, int c, int *r
     if (!work) return BLTCU_STATUS_ERROR;
     std::vector<int64_t> b(B, B + (size_t)r * c), u((size_t)r * r);
     int rk = -1;
-    if (limbs == 8) rk = lllfix::reduce_one<8>(b.data(), u.data(), r, c, work);
-    else if (limbs == 16) rk = lllfix::reduce_one<16>(b.data(), u.data(), r, c, work);
-    else rk = lllfix::reduce_one<32>(b.data(), u.data(), r, c, work);
+    if (limbs == 8) rk = lllfix::reduce_one<8, lllfix::OneLane>(b.data(), u.data(), r, c, work);
+    else if (limbs == 16) rk = lllfix::reduce_one<16, lllfix::OneLane>(b.data(), u.data(), r, c, work);
+    else rk = lllfix::reduce_one<32, lllfix::OneLane>(b.data(), u.data(), r, c, work);
     free(work);
     if (rk < 0) return BLTCU_STATUS_ERROR;
     memcpy(B, b.data(), b.size() * 8);

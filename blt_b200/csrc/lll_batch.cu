@@ -3,9 +3,9 @@
 // for many small problems (config 5: 10 000 instances of 20 x 20; config 2: 40 x 20 of rank 20)
 // the time-to-decision is the reduction, not the search.  One warp reduces one problem with the fixed-capacity exact
 // arithmetic of lll_fixed.h (512-bit integers): the same operations in the same order as bltcu_lll() on the host, so the
-// same reduced basis and the same U, bit for bit.  The algorithm is a chain of data-dependent multiprecision steps, so
-// one lane of the warp runs it (32 problems in one warp would execute their different branches one after the other);
-// the GPU's part is running a few thousand such chains side by side.  A problem whose numbers outgrow 512 bits is
+// same reduced basis and the same U, bit for bit.  The algorithm is a chain of data-dependent steps, so problems do not
+// share a warp (32 of them would execute their different branches one after the other); inside a problem the row
+// operations of the size reduction and of the swaps, which are the bulk of the work, are dealt to the 32 lanes.  A problem whose numbers outgrow 512 bits is
 // reduced by the arbitrary-precision host implementation instead (reported in stats->found).
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -23,10 +23,13 @@
 __global__ void __launch_bounds__(128) bltcu_lll_batch_kernel(int64_t *B, int64_t *U, int count, int r, int c, int *rank, int *status,
                                                               unsigned char *work, size_t work_stride) {
     const int w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (w >= count || (threadIdx.x & 31) != 0) return;
-    const int rk = lllfix::reduce_one<LLL_W>(B + (size_t)w * r * c, U ? U + (size_t)w * r * r : nullptr, r, c, work + (size_t)w * work_stride);
-    rank[w] = rk < 0 ? 0 : rk;
-    status[w] = rk < 0 ? 1 : 0;
+    if (w >= count) return;  // whole warps leave together
+    const int rk = lllfix::reduce_one<LLL_W, lllfix::WarpLanes>(B + (size_t)w * r * c, U ? U + (size_t)w * r * r : nullptr, r, c,
+                                                               work + (size_t)w * work_stride);
+    if ((threadIdx.x & 31) == 0) {
+        rank[w] = rk < 0 ? 0 : rk;
+        status[w] = rk < 0 ? 1 : 0;
+    }
 }
 
 #define CKL(call)                                                                                          \

@@ -261,21 +261,42 @@ struct Arith {
     }
 };
 
+// Who runs the reduction: one thread (host, or a single device thread), or the 32 lanes of a warp.  In the warp form the
+// loops over a row of B, U or lam (the bulk of the work: size reduction and the swap updates) are dealt to the lanes,
+// scalar updates are done by lane 0, and every decision is computed by all lanes from the same memory, so control flow
+// stays uniform.  Both forms perform the same operations on the same numbers.
+struct OneLane {
+    LF_HD int lane() const { return 0; }
+    LF_HD int width() const { return 1; }
+    LF_HD void sync() const {}
+    LF_HD int any(int x) const { return x; }
+};
+#if defined(__CUDACC__)
+struct WarpLanes {
+    __device__ int lane() const { return (int)(threadIdx.x & 31); }
+    __device__ int width() const { return 32; }
+    __device__ void sync() const { __syncwarp(); }
+    __device__ int any(int x) const { return __any_sync(0xffffffffu, x); }
+};
+#endif
+
 // The reduction itself.  Storage is supplied by the caller (global memory on the device):
-//   B: m x n, U: m x m, lam: (m+1) x (m+1) (1-based like host/lll.cpp), D: m+1, P: m+1 ints.
+//   B: m x n, U: m x m, lam: (m+1) x (m+1) (1-based like host/lll.cpp), D: m+1, P: m+2 ints (P[m+1] = rank so far).
 // Returns the rank, or -1 when a number overflowed its W limbs or the step limit was hit.
-template <int W>
+template <int W, class Lanes>
 struct Reducer {
     typedef Num<W> N;
     typedef Arith<W> A;
-    int m, n, s;
+    int m, n;
     N *B, *U, *lam, *D;
     int *P;
     A ar;
+    Lanes L;
 
     LF_HD N &b(int i, int t) { return B[(long)i * n + t]; }
     LF_HD N &u(int i, int t) { return U[(long)i * m + t]; }
     LF_HD N &l(int k, int j) { return lam[(long)k * (m + 1) + j]; }
+    LF_HD int &rank_so_far() { return P[m + 1]; }
 
     LF_HD void inner(N &r, int a, int c) {
         typename A::Wd acc, p, t;
@@ -283,19 +304,24 @@ struct Reducer {
         for (int x = 0; x < n; ++x) { ar.mul(p, b(a - 1, x), b(c - 1, x)); ar.addsub(t, acc, p, +1); acc = t; }
         ar.copy(r, acc);
     }
+    // a chain of dependent steps: lane 0
     LF_HD void incremental_gs(int k) {
-        N uu;
-        for (int j = 1; j < k; ++j) {
-            const int posj = P[j];
-            if (posj == 0) continue;
-            inner(uu, k, j);
-            for (int i = 1; i < posj; ++i) { N t; ar.muladd_div(t, D[i], uu, -1, l(k, i), l(j, i), D[i - 1]); uu = t; }
-            l(k, posj) = uu;
+        if (L.lane() == 0) {
+            N uu;
+            for (int j = 1; j < k; ++j) {
+                const int posj = P[j];
+                if (posj == 0) continue;
+                inner(uu, k, j);
+                for (int i = 1; i < posj; ++i) { N t; ar.muladd_div(t, D[i], uu, -1, l(k, i), l(j, i), D[i - 1]); uu = t; }
+                l(k, posj) = uu;
+            }
+            inner(uu, k, k);
+            const int s = rank_so_far();
+            for (int i = 1; i <= s; ++i) { N t; ar.muladd_div(t, D[i], uu, -1, l(k, i), l(k, i), D[i - 1]); uu = t; }
+            if (uu.len == 0) P[k] = 0;
+            else { rank_so_far() = s + 1; P[k] = s + 1; D[s + 1] = uu; }
         }
-        inner(uu, k, k);
-        for (int i = 1; i <= s; ++i) { N t; ar.muladd_div(t, D[i], uu, -1, l(k, i), l(k, i), D[i - 1]); uu = t; }
-        if (uu.len == 0) P[k] = 0;
-        else { ++s; P[k] = s; D[s] = uu; }
+        L.sync();
     }
     LF_HD void reduce(int k, int ll) {
         const int pl = P[ll];
@@ -309,87 +335,99 @@ struct Reducer {
             if (A::cmp(t, dw) <= 0) return;
         }
         N r;
-        ar.baldiv(r, l(k, pl), D[pl]);
-        for (int t = 0; t < n; ++t) { N x; ar.submul(x, b(k - 1, t), r, b(ll - 1, t)); b(k - 1, t) = x; }
-        for (int t = 0; t < m; ++t) { N x; ar.submul(x, u(k - 1, t), r, u(ll - 1, t)); u(k - 1, t) = x; }
-        for (int j = 1; j < ll; ++j) {
+        ar.baldiv(r, l(k, pl), D[pl]);  // every lane computes the same multiplier
+        L.sync();                       // ... before lane 0 changes lam[k][pl] below
+        for (int t = L.lane(); t < n; t += L.width()) { N x; ar.submul(x, b(k - 1, t), r, b(ll - 1, t)); b(k - 1, t) = x; }
+        for (int t = L.lane(); t < m; t += L.width()) { N x; ar.submul(x, u(k - 1, t), r, u(ll - 1, t)); u(k - 1, t) = x; }
+        for (int j = 1 + L.lane(); j < ll; j += L.width()) {
             const int pj = P[j];
             if (pj != 0) { N x; ar.submul(x, l(k, pj), r, l(ll, pj)); l(k, pj) = x; }
         }
-        { N x; ar.submul(x, l(k, pl), r, D[pl]); l(k, pl) = x; }
+        if (L.lane() == 0) { N x; ar.submul(x, l(k, pl), r, D[pl]); l(k, pl) = x; }
+        L.sync();
     }
     LF_HD void swap_num(N &x, N &y) { const N t = x; x = y; y = t; }
+    LF_HD void swap_rows_data(int k) {  // rows k-1 and k of B, U and lam (columns of the rows above)
+        for (int t = L.lane(); t < n; t += L.width()) swap_num(b(k - 2, t), b(k - 1, t));
+        for (int t = L.lane(); t < m; t += L.width()) swap_num(u(k - 2, t), u(k - 1, t));
+        for (int j = 1 + L.lane(); j <= k - 2; j += L.width()) { const int pj = P[j]; if (pj) swap_num(l(k - 1, pj), l(k, pj)); }
+        L.sync();
+    }
     LF_HD int swap_rows(int k, int max_k) {
         if (P[k] != 0) {
-            for (int t = 0; t < n; ++t) swap_num(b(k - 2, t), b(k - 1, t));
-            for (int t = 0; t < m; ++t) swap_num(u(k - 2, t), u(k - 1, t));
-            for (int j = 1; j <= k - 2; ++j) { const int pj = P[j]; if (pj) swap_num(l(k - 1, pj), l(k, pj)); }
+            swap_rows_data(k);
             const int pk = P[k];
-            for (int i = k + 1; i <= max_k; ++i) {
+            for (int i = k + 1 + L.lane(); i <= max_k; i += L.width()) {
                 N t1, t2;
                 ar.muladd_div(t1, l(i, pk - 1), l(k, pk - 1), +1, l(i, pk), D[pk - 2], D[pk - 1]);
                 ar.muladd_div(t2, l(i, pk - 1), D[pk], -1, l(i, pk), l(k, pk - 1), D[pk - 1]);
                 l(i, pk - 1) = t1; l(i, pk) = t2;
             }
-            N nd;
-            ar.muladd_div(nd, D[pk], D[pk - 2], +1, l(k, pk - 1), l(k, pk - 1), D[pk - 1]);
-            D[pk - 1] = nd;
+            L.sync();
+            if (L.lane() == 0) {
+                N nd;
+                ar.muladd_div(nd, D[pk], D[pk - 2], +1, l(k, pk - 1), l(k, pk - 1), D[pk - 1]);
+                D[pk - 1] = nd;
+            }
+            L.sync();
             return 0;
         }
         const int pk1 = P[k - 1];
         if (l(k, pk1).len != 0) {
-            N e, x, y, t1, t2, t3;
+            N e, x, y, t1, t2, t3;  // the same in every lane
             ar.xgcd(l(k, pk1), D[pk1], e, x, y);
             ar.fdiv(t1, l(k, pk1), e);
             ar.fdiv(t2, D[pk1], e);
             t3 = t2;
             if (t2.len) t2.neg = !t2.neg;
-            for (int t = 0; t < n; ++t) {
+            L.sync();
+            for (int t = L.lane(); t < n; t += L.width()) {
                 const N c1 = b(k - 2, t), c2 = b(k - 1, t);
                 ar.lin2(b(k - 2, t), t1, c1, t2, c2);
                 ar.lin2(b(k - 1, t), y, c1, x, c2);
             }
-            for (int t = 0; t < m; ++t) {
+            for (int t = L.lane(); t < m; t += L.width()) {
                 const N c1 = u(k - 2, t), c2 = u(k - 1, t);
                 ar.lin2(u(k - 2, t), t1, c1, t2, c2);
                 ar.lin2(u(k - 1, t), y, c1, x, c2);
             }
-            for (int j = 1; j <= k - 2; ++j) {
+            for (int j = 1 + L.lane(); j <= k - 2; j += L.width()) {
                 const int pj = P[j];
                 if (!pj) continue;
                 const N c1 = l(k - 1, pj), c2 = l(k, pj);
                 ar.lin2(l(k - 1, pj), t1, c1, t2, c2);
                 ar.lin2(l(k, pj), y, c1, x, c2);
             }
-            typename A::Wd t2sw;
-            ar.mul(t2sw, t2, t2);
-            N t2s;
-            ar.copy(t2s, t2sw);
-            { N q; ar.fdiv(q, D[pk1], t2s); D[pk1] = q; }
-            for (int i = k + 1; i <= max_k; ++i) {
-                const int pi = P[i];
-                if (!pi) continue;
-                { N q; ar.fdiv(q, D[pi], t2s); D[pi] = q; }
-                for (int j = i + 1; j <= max_k; ++j) { N q; ar.fdiv(q, l(j, pi), t2s); l(j, pi) = q; }
+            L.sync();
+            if (L.lane() == 0) {  // the rare branch (dependent rows): the divisions stay with one lane
+                typename A::Wd t2sw;
+                ar.mul(t2sw, t2, t2);
+                N t2s;
+                ar.copy(t2s, t2sw);
+                { N q; ar.fdiv(q, D[pk1], t2s); D[pk1] = q; }
+                for (int i = k + 1; i <= max_k; ++i) {
+                    const int pi = P[i];
+                    if (!pi) continue;
+                    { N q; ar.fdiv(q, D[pi], t2s); D[pi] = q; }
+                    for (int j = i + 1; j <= max_k; ++j) { N q; ar.fdiv(q, l(j, pi), t2s); l(j, pi) = q; }
+                }
+                for (int i = k + 1; i <= max_k; ++i) { N q; ar.fdiv(q, l(i, pk1), t3); l(i, pk1) = q; }
+                const int tp = P[k - 1]; P[k - 1] = P[k]; P[k] = tp;
             }
-            for (int i = k + 1; i <= max_k; ++i) { N q; ar.fdiv(q, l(i, pk1), t3); l(i, pk1) = q; }
-            const int tp = P[k - 1]; P[k - 1] = P[k]; P[k] = tp;
+            L.sync();
             return 1;
         }
-        for (int t = 0; t < n; ++t) swap_num(b(k - 2, t), b(k - 1, t));
-        for (int t = 0; t < m; ++t) swap_num(u(k - 2, t), u(k - 1, t));
-        for (int j = 1; j <= k - 2; ++j) { const int pj = P[j]; if (pj) swap_num(l(k - 1, pj), l(k, pj)); }
-        const int tp = P[k - 1]; P[k - 1] = P[k]; P[k] = tp;
+        swap_rows_data(k);
+        if (L.lane() == 0) { const int tp = P[k - 1]; P[k - 1] = P[k]; P[k] = tp; }
+        L.sync();
         return 0;
     }
     // delta = a/b
     LF_HD int run(int a, int bq, long max_steps) {
         int k = 1, max_k = 0, force_reduce = 1;
-        N An, Bn;
-        A::set_i64(An, a); A::set_i64(Bn, bq);
         long steps = 0;
         while (k <= m) {
-            if (ar.ovf || ++steps > max_steps) return -1;
+            if (L.any(ar.ovf) || ++steps > max_steps) return -1;
             if (k > max_k) { incremental_gs(k); max_k = k; }
             if (k == 1) { force_reduce = 1; ++k; continue; }
             if (force_reduce) for (int j = k - 1; j >= 1; --j) reduce(k, j);
@@ -411,42 +449,48 @@ struct Reducer {
                     do_swap = A::cmp(lhs, rhs) > 0;
                 }
             }
+            L.sync();  // every lane has read what it needs for the decision
             if (do_swap) { force_reduce = swap_rows(k, max_k); --k; }
             else { force_reduce = 1; ++k; }
         }
-        return ar.ovf ? -1 : s;
+        return L.any(ar.ovf) ? -1 : rank_so_far();
     }
 };
 
 // One problem, storage carved from `work` (bytes_needed<W>(r, c) bytes).  B: r x c in/out, U: r x r out.
 template <int W>
 LF_HD inline long bytes_needed(int r, int c) {
-    return (long)sizeof(Num<W>) * ((long)r * c + (long)r * r + (long)(r + 1) * (r + 1) + (r + 1)) + (long)sizeof(int) * (r + 2);
+    return (long)sizeof(Num<W>) * ((long)r * c + (long)r * r + (long)(r + 1) * (r + 1) + (r + 1)) + (long)sizeof(int) * (r + 4);
 }
-template <int W>
+template <int W, class Lanes>
 LF_HD inline int reduce_one(int64_t *B, int64_t *U, int r, int c, void *work) {
     typedef Num<W> N;
-    Reducer<W> R;
-    R.m = r; R.n = c; R.s = 0;
+    Reducer<W, Lanes> R;
+    R.m = r; R.n = c;
     N *p = (N *)work;
     R.B = p; p += (long)r * c;
     R.U = p; p += (long)r * r;
     R.lam = p; p += (long)(r + 1) * (r + 1);
     R.D = p; p += r + 1;
     R.P = (int *)p;
-    for (int i = 0; i < r; ++i) {
+    const int lane = R.L.lane(), width = R.L.width();
+    for (int i = lane; i < r; i += width) {
         for (int j = 0; j < c; ++j) Arith<W>::set_i64(R.b(i, j), B[(long)i * c + j]);
         for (int j = 0; j < r; ++j) Arith<W>::set_i64(R.u(i, j), i == j ? 1 : 0);
     }
-    for (long i = 0; i < (long)(r + 1) * (r + 1); ++i) { R.lam[i].len = 0; R.lam[i].neg = 0; }
-    for (int i = 0; i <= r; ++i) { R.P[i] = 0; R.D[i].len = 0; R.D[i].neg = 0; }
-    Arith<W>::set_i64(R.D[0], 1);
+    for (long i = lane; i < (long)(r + 1) * (r + 1); i += width) { R.lam[i].len = 0; R.lam[i].neg = 0; }
+    for (int i = lane; i <= r + 1; i += width) R.P[i] = 0;
+    for (int i = lane; i <= r; i += width) { R.D[i].len = 0; R.D[i].neg = 0; }
+    R.L.sync();
+    if (lane == 0) Arith<W>::set_i64(R.D[0], 1);
+    R.L.sync();
     const int rank = R.run(3, 4, 4000000L);
     if (rank < 0) return -1;
-    for (int i = 0; i < r; ++i) {
+    for (int i = lane; i < r; i += width) {
         for (int j = 0; j < c; ++j) B[(long)i * c + j] = Arith<W>::to_i64(R.b(i, j));
         if (U) for (int j = 0; j < r; ++j) U[(long)i * r + j] = Arith<W>::to_i64(R.u(i, j));
     }
+    R.L.sync();
     return rank;
 }
 
