@@ -85,6 +85,12 @@ struct QCtl {
     unsigned long long idle_ns, busy_ns;  // summed over warps: time spent waiting for work / expanding records
     unsigned long long hist[MAXD + 1];
     long long fail_u[MAXD];     // coefficients of the node whose LP failed first (diagnostics)
+    // batch kernel only: a problem's control block is shared by its owner warp and the warps that help it
+    int lock;                   // guards the problem's shared best candidate (uhat)
+    int owner_inst;             // index of the problem this block belongs to
+    int helped;                 // subtrees of this problem were handed to other warps
+    int active;                 // global block only: problems not finished yet
+    double radius_b;            // the problem's radius, for the helpers
 };
 
 struct Params {
@@ -1514,7 +1520,127 @@ struct BatchParams {
     unsigned long long *totals;  // nodes, pivots, quick prunes, refactorisations, cold starts, then hist[MAXD + 1]
     unsigned long long timeout_ns;
     size_t warp_doubles;       // shared memory per warp: Q (m x LDQ) + the search block
+    // helping: warps that ran out of problems take subtrees of the problems still running
+    int allow_help;
+    QCtl *gq;                  // global block: help ring, free ring, idle helpers, problems not finished
+    int *hring, *hfring;       // help ring / free-slot ring (record indices)
+    unsigned int hmask;
+    unsigned char *hpool;      // records handed over
+    int64_t *sbest_u;          // per owner warp: the problem's shared best candidate, its key and validity
+    unsigned char *sbest_key;
+    int *sbest_valid;
+    int *helped;               // count: 1 if the problem was searched by more than one warp
 };
+// what a warp of the batch kernel owns
+struct BWarp {
+    double *Qs, *wsm, *wb;       // shared-memory copy of Q, shared-memory search block, global per-warp buffers
+    unsigned char *nextbuf;
+    int gwarp, lane;
+};
+// loads Q of the problem whose geometry P points to and readies the warp's search state; returns the node histogram
+template <int MC>
+__device__ __forceinline__ unsigned int *batch_prepare(const Params &P, WS &s, Arena &A, const BWarp &w) {
+    const int n = P.n, m = P.m, lane = w.lane;
+#pragma unroll 1
+    for (int e = lane; e < m * LDQ_C; e += 32) {
+        const int j = e / LDQ_C, i = e - j * LDQ_C;
+        w.Qs[e] = i < m ? P.Qrev[(size_t)j * m + i] : 0.0;
+    }
+    unsigned int *hist = carve_fixed<MC>(s, w.wsm);
+    s.Wpar = w.wb; s.Wg_a = w.wb + (size_t)m * m; s.Wg_b = s.Wg_a + (size_t)m * P.LDG; s.tmpA = s.Wg_b + (size_t)m * P.LDG;
+    s.LDS = LDS_C; s.LDG = P.LDG; s.QS = QS_MAX;
+    s.Qsm = w.Qs; s.LDQsm = LDQ_C;
+    s.Qs = w.Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
+    s.repairs = 0; s.failcode = 0;
+    if (lane < C_COUNT) s.ctr[lane] = 0ull;
+    use_side<false>(s, 0);
+#pragma unroll 1
+    for (int e = lane; e <= n; e += 32) hist[e] = 0;
+    A.base = P.arena + (size_t)w.gwarp * P.arena_stride;
+    A.offs = (int *)(A.base + P.arena_bytes);
+    A.cap = P.arena_bytes; A.slots = P.arena_slots; A.acount = 0; A.abot = 0;
+    if (lane == 0) { A.offs[0] = 0; P.best_valid[w.gwarp] = 0; }
+    __syncwarp();
+    return hist;
+}
+// folds this warp's last recorded leaf into the problem's shared candidate (later in depth-first order wins)
+__device__ __forceinline__ void batch_merge_best(const BatchParams &BP, const Params &P, QCtl *oq, int owner, int gwarp, int lane) {
+    const int n = P.n;
+    int bv = 0;
+    if (lane == 0) bv = P.best_valid[gwarp];
+    if (!__shfl_sync(FULLMASK, bv, 0)) return;
+    const unsigned char *mk = P.best_key + (size_t)gwarp * n;
+    unsigned char *sk = BP.sbest_key + (size_t)owner * n;
+    int newer = 1;
+    if (lane == 0) {
+        while (atomicCAS(&oq->lock, 0, 1) != 0) __nanosleep(50);
+        __threadfence();
+        if (*(volatile int *)&BP.sbest_valid[owner]) {
+            int cmp = 0;
+            for (int e = n - 1; e >= 0 && cmp == 0; --e) cmp = (int)mk[e] - (int)((volatile unsigned char *)sk)[e];
+            newer = cmp >= 0;
+        }
+    }
+    newer = __shfl_sync(FULLMASK, newer, 0);
+    if (newer) {
+#pragma unroll 1
+        for (int e = lane; e < n; e += 32) { sk[e] = mk[e]; BP.sbest_u[(size_t)owner * n + e] = P.best_u[(size_t)gwarp * n + e]; }
+    }
+    __syncwarp();
+    __threadfence();
+    if (lane == 0) { if (newer) BP.sbest_valid[owner] = 1; __threadfence(); atomicExch(&oq->lock, 0); }
+    __syncwarp();
+}
+// Runs the warp's own stack to exhaustion.  have_next: a record waits in the first `next` buffer.  While other warps
+// are idle, the OLDEST record of the stack (the largest subtree left) is handed over after every task.
+template <int MC>
+__device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P, WS &s, Arena &A, const BWarp &w,
+                                          const RecLayout &RL, int have_next, int owner, unsigned int *hist) {
+    const int lane = w.lane;
+    QCtl *oq = P.q;
+    int nextsel = 0;
+    for (;;) {
+        const unsigned char *R;
+        if (have_next) { R = w.nextbuf + (size_t)nextsel * RL.stride; nextsel ^= 1; have_next = 0; }
+        else if (A.acount > A.abot) {
+            A.acount--;
+            R = A.base + A.offs[A.acount];
+            if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; __syncwarp(); }
+        } else break;
+        int ab = 0;
+        if (lane == 0) ab = *(volatile int *)&oq->abort;
+        if (__shfl_sync(FULLMASK, ab, 0)) break;
+        have_next = expand(P, s, R, -1, w.nextbuf + (size_t)nextsel * RL.stride, A, w.gwarp, hist);
+        __syncwarp();
+        if (BP.allow_help && A.acount > A.abot) {
+            int dslot = -1;
+            if (lane == 0) {
+                const int idle = *(volatile int *)&BP.gq->idle;
+                if (idle > 0) {
+                    const int qlen = (int)(*(volatile unsigned int *)&BP.gq->tail - *(volatile unsigned int *)&BP.gq->head);
+                    if (qlen < idle) dslot = ring_pop(BP.gq, &BP.gq->fhead, &BP.gq->ftail, BP.hfring, BP.hmask);
+                }
+            }
+            dslot = __shfl_sync(FULLMASK, dslot, 0);
+            if (dslot >= 0) {
+                unsigned char *dst = BP.hpool + (size_t)dslot * RL.stride;
+                const unsigned char *src = A.base + A.offs[A.abot];
+                copy_words(dst, src, (size_t)(A.offs[A.abot + 1] - A.offs[A.abot]), lane);
+                __syncwarp();
+                if (lane == 0) ((int *)dst)[9] = owner;
+                __threadfence();
+                if (lane == 0) { oq->helped = 1; atomicAdd(&oq->pending, 1); ring_push(BP.gq, &BP.gq->tail, BP.hring, BP.hmask, dslot); }
+                A.abot++;
+                if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; }
+                __syncwarp();
+            }
+        }
+    }
+}
+// The kernel is a loop over work units with ONE call site of the search loop: a unit is either the warp's own share of
+// a new problem (it becomes the problem's owner) or a subtree handed over by another owner.  Every unit folds its
+// counters and its last recorded leaf into the owner's control block; the owner writes the problem's results when
+// its own share and all handed-over subtrees are in (pending == 0).
 template <int MC>
 __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams BP) {
     extern __shared__ __align__(16) double smem[];
@@ -1522,109 +1648,168 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
     const int n = P.n, m = P.m;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int gwarp = blockIdx.x * P.warps_per_cta + warp;
-    double *Qs = smem + (size_t)warp * BP.warp_doubles;
-    double *wsm = Qs + (size_t)m * LDQ_C;
-    double *g = (double *)(BP.geo + (size_t)gwarp * BP.geo_stride);
-    double *B = g; g += (size_t)n * m;
-    double *pc = g; g += m;
-    double *Q = g; g += (size_t)m * m;
-    double *Qrev = g; g += (size_t)m * m;
-    double *Rm = g; g += (size_t)n * n;
-    double *QTp = g; g += m;
-    double *tmp = g; g += 2 * (size_t)m;
-    unsigned long long *sc = (unsigned long long *)g;
-    P.B = B; P.p = pc; P.Qrev = Qrev; P.Rm = Rm; P.QTp = QTp;
-    QCtl *q = BP.ctl + gwarp;
-    P.q = q;
-    P.static_depth = 0; P.dynamic = 0; P.eager_max = 1;
     const RecLayout RL = rec_layout(n, m);
-    unsigned char *nextbuf = P.nextrec + (size_t)gwarp * 2 * RL.stride;
-    double *wb = P.wbuf + (size_t)gwarp * P.wbuf_stride;
+    BWarp w;
+    w.Qs = smem + (size_t)warp * BP.warp_doubles;
+    w.wsm = w.Qs + (size_t)m * LDQ_C;
+    w.wb = P.wbuf + (size_t)gwarp * P.wbuf_stride;
+    w.nextbuf = P.nextrec + (size_t)gwarp * 2 * RL.stride;
+    w.gwarp = gwarp; w.lane = lane;
+    const size_t geo_off_p = (size_t)n * m, geo_off_Q = geo_off_p + m, geo_off_Qrev = geo_off_Q + (size_t)m * m;
+    const size_t geo_off_Rm = geo_off_Qrev + (size_t)m * m, geo_off_QTp = geo_off_Rm + (size_t)n * n, geo_off_tmp = geo_off_QTp + m;
+    double *gown = (double *)(BP.geo + (size_t)gwarp * BP.geo_stride);
+    unsigned long long *sc = (unsigned long long *)(gown + geo_off_tmp + 2 * (size_t)m);
+    QCtl *q = BP.ctl + gwarp;
+    P.static_depth = 0; P.dynamic = 0; P.eager_max = 1;
     unsigned long long deadline = 0;
     if (BP.timeout_ns) deadline = gtimer() + BP.timeout_ns;
     deadline = __shfl_sync(FULLMASK, deadline, 0);
     unsigned long long t_nodes = 0, t_piv = 0, t_quick = 0, t_ref = 0, t_cold = 0;
+    int owning = -1;   // problem this warp owns and has not written the results of yet
+    int more = 1;      // the problem counter is not exhausted
+    int am_idle = 0;
     for (;;) {
-        int inst = 0;
-        if (lane == 0) inst = atomicAdd(BP.next, 1);
-        inst = __shfl_sync(FULLMASK, inst, 0);
-        if (inst >= BP.count) break;
-        const int64_t *lat = BP.lat + (size_t)inst * n * m, *con = BP.con + (size_t)inst * 2 * m;
-        int64_t *sol = BP.sol + (size_t)inst * n;
-        P.lat = lat; P.con = con; P.sol = sol;
-        P.radius = (double)(con[1] - con[0]) / 2.0;  // closest.cc:193-194: row 0 only
-#pragma unroll 1
-        for (int e = lane; e < (int)(sizeof(QCtl) / 8); e += 32) ((unsigned long long *)q)[e] = 0ull;
-#pragma unroll 1
-        for (int e = lane; e < n; e += 32) sol[e] = 0;
-        if (lane == 0) { P.best_valid[gwarp] = 0; sc[0] = sc[1] = sc[2] = sc[3] = 0; }
-        __syncwarp();
-        if (lane == 0) q->deadline_ns = deadline;
-        int st = BLTCU_STATUS_OK, fnd = 0;
-        unsigned long long c_niter = 0, c_nprune = 0;
-        const int r = setup_warp(lat, con, n, m, B, pc, Q, Qrev, Rm, QTp, tmp, wb, nextbuf, wsm, sc, lane);
-        if (r != 0) st = BLTCU_STATUS_LP_FAIL;  // dependent basis rows or a failed initial solve
-        else {
-#pragma unroll 1
-            for (int e = lane; e < m * LDQ_C; e += 32) {
-                const int j = e / LDQ_C, i = e - j * LDQ_C;
-                Qs[e] = i < m ? Qrev[(size_t)j * m + i] : 0.0;
-            }
-            WS s;
-            unsigned int *hist = carve_fixed<MC>(s, wsm);
-            s.Wpar = wb; s.Wg_a = wb + (size_t)m * m; s.Wg_b = s.Wg_a + (size_t)m * P.LDG; s.tmpA = s.Wg_b + (size_t)m * P.LDG;
-            s.LDS = LDS_C; s.LDG = P.LDG; s.QS = QS_MAX;
-            s.Qsm = Qs; s.LDQsm = LDQ_C;
-            s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
-            s.repairs = 0; s.failcode = 0;
-            if (lane < C_COUNT) s.ctr[lane] = 0ull;
-            use_side<false>(s, 0);
-#pragma unroll 1
-            for (int e = lane; e <= n; e += 32) hist[e] = 0;
-            Arena A;
-            A.base = P.arena + (size_t)gwarp * P.arena_stride;
-            A.offs = (int *)(A.base + P.arena_bytes);
-            A.cap = P.arena_bytes; A.slots = P.arena_slots; A.acount = 0; A.abot = 0;
-            if (lane == 0) A.offs[0] = 0;
-            __syncwarp();
-            int nextsel = 0, have_next = 1;  // setup_warp left the top-level record in the first buffer
-            for (;;) {
-                const unsigned char *R;
-                if (have_next) { R = nextbuf + (size_t)nextsel * RL.stride; nextsel ^= 1; have_next = 0; }
-                else if (A.acount > 0) { A.acount--; R = A.base + A.offs[A.acount]; }
-                else break;
-                int ab = 0;
-                if (lane == 0) ab = *(volatile int *)&q->abort;
-                if (__shfl_sync(FULLMASK, ab, 0)) break;
-                have_next = expand(P, s, R, -1, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
-                __syncwarp();
-            }
-            __threadfence();
-            int fi = 0;
-            if (lane == 0) { st = *(volatile int *)&q->status; fnd = *(volatile int *)&q->found; fi = *(volatile int *)&q->fail_info; }
-            st = __shfl_sync(FULLMASK, st, 0); fnd = __shfl_sync(FULLMASK, fnd, 0); fi = __shfl_sync(FULLMASK, fi, 0);
-            if (!fnd && fi && st == BLTCU_STATUS_OK) st = BLTCU_STATUS_LP_FAIL;
-            if (!fnd) {  // the last recorded candidate (uhat), as the reference returns it
-                int bv = 0;
-                if (lane == 0) bv = P.best_valid[gwarp];
-                bv = __shfl_sync(FULLMASK, bv, 0);
-                if (bv) {
-#pragma unroll 1
-                    for (int e = lane; e < n; e += 32) sol[e] = P.best_u[(size_t)gwarp * n + e];
+        int owner = -1, have_next = 0;
+        // ---- 1. results of the own problem, once everything handed over has come back ----
+        if (owning >= 0) {
+            int pend = 0;
+            if (lane == 0) pend = *(volatile int *)&q->pending;
+            if (__shfl_sync(FULLMASK, pend, 0) == 0) {
+                __threadfence();
+                int st = 0, fnd = 0, fi = 0, helped = 0;
+                unsigned long long h[7] = {0, 0, 0, 0, 0, 0, 0};
+                if (lane == 0) {
+                    st = *(volatile int *)&q->status; fnd = *(volatile int *)&q->found; fi = *(volatile int *)&q->fail_info;
+                    helped = *(volatile int *)&q->helped;
+                    h[0] = *(volatile unsigned long long *)&q->niter; h[1] = *(volatile unsigned long long *)&q->nprune;
+                    h[2] = *(volatile unsigned long long *)&q->nodes; h[3] = *(volatile unsigned long long *)&q->pivots;
+                    h[4] = *(volatile unsigned long long *)&q->colds; h[5] = *(volatile unsigned long long *)&q->refactors;
+                    h[6] = *(volatile unsigned long long *)&q->quick;
                 }
-            }
-            __syncwarp();
-            c_niter = s.ctr[C_NITER]; c_nprune = s.ctr[C_NPRUNE];
-            t_nodes += s.ctr[C_NODES] + 1; t_piv += s.ctr[C_PIVOTS] + sc[0]; t_cold += s.ctr[C_COLDS] + sc[1];
-            t_ref += s.ctr[C_REFAC] + sc[2]; t_quick += s.ctr[C_QUICK] + sc[3];
+                st = __shfl_sync(FULLMASK, st, 0); fnd = __shfl_sync(FULLMASK, fnd, 0); fi = __shfl_sync(FULLMASK, fi, 0);
+                if (!fnd && fi && st == BLTCU_STATUS_OK) st = BLTCU_STATUS_LP_FAIL;
+                int64_t *sol = BP.sol + (size_t)owning * n;
+                if (!fnd) {  // the last recorded candidate (uhat), as the reference returns it
+                    int bv = 0;
+                    if (lane == 0) bv = *(volatile int *)&BP.sbest_valid[gwarp];
+                    if (__shfl_sync(FULLMASK, bv, 0)) {
 #pragma unroll 1
-            for (int e = lane; e <= n; e += 32) if (hist[e]) atomicAdd(&BP.totals[5 + e], (unsigned long long)hist[e]);
-            if (lane == 0) atomicAdd(&BP.totals[5 + n], 1ull);
+                        for (int e = lane; e < n; e += 32) sol[e] = BP.sbest_u[(size_t)gwarp * n + e];
+                    }
+                }
+                if (lane == 0) {
+                    t_nodes += h[2] + 1; t_piv += h[3] + sc[0]; t_cold += h[4] + sc[1]; t_ref += h[5] + sc[2]; t_quick += h[6] + sc[3];
+                    BP.status[owning] = st; BP.found[owning] = fnd; BP.niter[owning] = h[0]; BP.nprune[owning] = h[1];
+                    BP.helped[owning] = helped;
+                    atomicAdd(&BP.totals[5 + n], 1ull);
+                    __threadfence();
+                    atomicSub(&BP.gq->active, 1);
+                }
+                __syncwarp();
+                owning = -1;
+            }
         }
-        if (lane == 0) { BP.status[inst] = st; BP.found[inst] = fnd; BP.niter[inst] = c_niter; BP.nprune[inst] = c_nprune; }
+        // ---- 2. a new problem of its own ----
+        if (owning < 0 && more) {
+            int inst = 0;
+            if (lane == 0) inst = atomicAdd(BP.next, 1);
+            inst = __shfl_sync(FULLMASK, inst, 0);
+            if (inst >= BP.count) more = 0;
+            else {
+                const int64_t *lat = BP.lat + (size_t)inst * n * m, *con = BP.con + (size_t)inst * 2 * m;
+                int64_t *sol = BP.sol + (size_t)inst * n;
+#pragma unroll 1
+                for (int e = lane; e < (int)(sizeof(QCtl) / 8); e += 32) ((unsigned long long *)q)[e] = 0ull;
+#pragma unroll 1
+                for (int e = lane; e < n; e += 32) sol[e] = 0;
+                __syncwarp();
+                const double radius = (double)(con[1] - con[0]) / 2.0;  // closest.cc:193-194: row 0 only
+                if (lane == 0) {
+                    sc[0] = sc[1] = sc[2] = sc[3] = 0; BP.sbest_valid[gwarp] = 0;
+                    q->deadline_ns = deadline; q->owner_inst = inst; q->radius_b = radius; q->pending = 1;  // 1 = the own share
+                }
+                __syncwarp();
+                __threadfence();
+                const int r = setup_warp(lat, con, n, m, gown, gown + geo_off_p, gown + geo_off_Q, gown + geo_off_Qrev, gown + geo_off_Rm,
+                                         gown + geo_off_QTp, gown + geo_off_tmp, w.wb, w.nextbuf, w.wsm, sc, lane);
+                if (r != 0) {  // dependent basis rows or a failed initial solve
+                    if (lane == 0) {
+                        BP.status[inst] = BLTCU_STATUS_LP_FAIL; BP.found[inst] = 0; BP.niter[inst] = 0; BP.nprune[inst] = 0; BP.helped[inst] = 0;
+                        __threadfence();
+                        atomicSub(&BP.gq->active, 1);
+                    }
+                    __syncwarp();
+                    continue;
+                }
+                owning = inst; owner = gwarp; have_next = 1;  // setup_warp left the top-level record in the first buffer
+            }
+        }
+        // ---- 3. otherwise a subtree somebody handed over ----
+        if (owner < 0) {
+            int slot = -1, stop = 0;
+            if (lane == 0) {
+                if (BP.allow_help) slot = ring_pop(BP.gq, &BP.gq->head, &BP.gq->tail, BP.hring, BP.hmask);
+                if (slot < 0) {
+                    if (owning < 0 && !more && (!BP.allow_help || *(volatile int *)&BP.gq->active == 0)) stop = 1;
+                    else {
+                        if (!am_idle && BP.allow_help) { atomicAdd(&BP.gq->idle, 1); am_idle = 1; }
+                        __nanosleep(1000);
+                        if (deadline && gtimer() > deadline) stop = 1;
+                    }
+                } else if (am_idle) { atomicSub(&BP.gq->idle, 1); am_idle = 0; }
+            }
+            stop = __shfl_sync(FULLMASK, stop, 0);
+            slot = __shfl_sync(FULLMASK, slot, 0);
+            if (stop) break;
+            if (slot < 0) continue;
+            // the record moves into this warp's first buffer, the pool slot is free again
+            const unsigned char *R = BP.hpool + (size_t)slot * RL.stride;
+            owner = ((const int *)R)[9];
+            const int k0 = ((const int *)R)[0], fl = ((const int *)R)[1];
+            const size_t bytes = (fl & REC_CONT) ? (size_t)((const int *)R)[8] : rec_bytes(RL, m, k0);
+            copy_words(w.nextbuf, R, (bytes + 7) / 8 * 8, lane);
+            __syncwarp();
+            __threadfence();
+            if (lane == 0) ring_push(BP.gq, &BP.gq->ftail, BP.hfring, BP.hmask, slot);
+            have_next = 1;
+        } else if (lane == 0 && am_idle) {
+            atomicSub(&BP.gq->idle, 1);
+            am_idle = 0;
+        }
+        // ---- 4. the search itself: geometry, bounds and control block are the owner's ----
+        QCtl *oq = BP.ctl + owner;
+        {
+            double *g = (double *)(BP.geo + (size_t)owner * BP.geo_stride);
+            P.B = g; P.p = g + geo_off_p; P.Qrev = g + geo_off_Qrev; P.Rm = g + geo_off_Rm; P.QTp = g + geo_off_QTp;
+            int inst = 0;
+            double radius = 0.0;
+            if (lane == 0) { inst = *(volatile int *)&oq->owner_inst; radius = *(volatile double *)&oq->radius_b; }
+            inst = __shfl_sync(FULLMASK, inst, 0);
+            radius = __shfl_sync(FULLMASK, radius, 0);
+            P.lat = BP.lat + (size_t)inst * n * m; P.con = BP.con + (size_t)inst * 2 * m; P.sol = BP.sol + (size_t)inst * n;
+            P.radius = radius;
+            P.q = oq;
+        }
+        WS s;
+        Arena A;
+        unsigned int *hist = batch_prepare<MC>(P, s, A, w);
+        batch_run<MC>(BP, P, s, A, w, RL, have_next, owner, hist);
+        __syncwarp();
+        // ---- 5. fold this unit into the owner's block ----
+        if (lane == 0) {
+            atomicAdd(&oq->niter, s.ctr[C_NITER]); atomicAdd(&oq->nprune, s.ctr[C_NPRUNE]); atomicAdd(&oq->nodes, s.ctr[C_NODES]);
+            atomicAdd(&oq->pivots, s.ctr[C_PIVOTS]); atomicAdd(&oq->quick, s.ctr[C_QUICK]); atomicAdd(&oq->refactors, s.ctr[C_REFAC]);
+            atomicAdd(&oq->colds, s.ctr[C_COLDS]);
+        }
+#pragma unroll 1
+        for (int e = lane; e <= n; e += 32) if (hist[e]) atomicAdd(&BP.totals[5 + e], (unsigned long long)hist[e]);
+        batch_merge_best(BP, P, oq, owner, gwarp, lane);
+        __threadfence();
+        if (lane == 0) atomicSub(&oq->pending, 1);
         __syncwarp();
     }
     if (lane == 0) {
+        if (am_idle) atomicSub(&BP.gq->idle, 1);
         atomicAdd(&BP.totals[0], t_nodes); atomicAdd(&BP.totals[1], t_piv); atomicAdd(&BP.totals[2], t_quick);
         atomicAdd(&BP.totals[3], t_ref); atomicAdd(&BP.totals[4], t_cold);
     }
@@ -2154,28 +2339,12 @@ extern "C" int bltcu_closest(const int64_t *lat, const int64_t *con, int n, int 
     return rc;
 }
 
-// Batch form of the search seam (SURVEY.md section 8b: "arrays of problems, one status per problem").
-extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n, int m, const bltcu_opts *opts,
-                                   int64_t *sol, int *status, uint64_t *niter, uint64_t *nprune, int *found,
-                                   bltcu_stats *stats) {
-    const auto t0 = std::chrono::steady_clock::now();
-    if (count < 0) return BLTCU_STATUS_INPUT_ERROR;
-    const int v = validate(n, m);
-    if (v != BLTCU_STATUS_OK) return v;
-    if (stats) memset(stats, 0, sizeof *stats);
-    if (count == 0) return BLTCU_STATUS_OK;
-    if (!lat || !con || !sol || !status) return BLTCU_STATUS_INPUT_ERROR;
-    bltcu_opts o;
-    memset(&o, 0, sizeof o);
-    if (opts) o = *opts;
-    const int world = o.world > 1 ? o.world : 1, rank = world > 1 ? o.rank : 0;
-    if (rank < 0 || rank >= world) return BLTCU_STATUS_INPUT_ERROR;
-    const int lo = (int)((long long)count * rank / world), hi = (int)((long long)count * (rank + 1) / world);
-    const int mine = hi - lo;
-    if (mine == 0) return BLTCU_STATUS_OK;
-    std::lock_guard<std::mutex> lk(g_mu);
-    DevWs *w = nullptr;
-    if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
+// One launch of the batch kernel over `mine` problems (host pointers already offset to them).  allow_help: warps
+// that run out of problems take subtrees of the problems still running; helped[i] then says whether problem i was
+// searched by more than one warp.  *stats is accumulated into.
+static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mine, int n, int m, const bltcu_opts &o, int64_t *sol,
+                        int *status, uint64_t *niter, uint64_t *nprune, int *found, int *helped, int allow_help, bltcu_stats *stats) {
+    const int lo = 0;
 
     const int KQS = QS_MAX, LDS = LDS_C, LDG = m | 1, LDQ = LDQ_C;
     const size_t warp_bytes = fixed_warp_bytes(size_class(m));
@@ -2206,6 +2375,11 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     const size_t o_nrec = carve((size_t)nwarps * 2 * RL.stride), o_arena = carve((size_t)nwarps * arena_stride);
     const size_t o_lat = carve((size_t)mine * n * m * 8), o_con = carve((size_t)mine * 2 * m * 8), o_sol = carve((size_t)mine * n * 8);
     const size_t o_st = carve((size_t)mine * 4), o_fd = carve((size_t)mine * 4), o_ni = carve((size_t)mine * 8), o_np = carve((size_t)mine * 8);
+    int hpool_cap = 2048;  // handed-over records in flight (power of two)
+    while ((size_t)hpool_cap * RL.stride > ((size_t)1 << 30) && hpool_cap > 64) hpool_cap >>= 1;
+    const size_t o_gq = carve(sizeof(QCtl)), o_hring = carve((size_t)hpool_cap * 4), o_hfring = carve((size_t)hpool_cap * 4);
+    const size_t o_hpool = carve((size_t)hpool_cap * RL.stride), o_sbu = carve((size_t)nwarps * n * 8), o_sbk = carve((size_t)nwarps * n);
+    const size_t o_sbv = carve((size_t)nwarps * 4), o_hl = carve((size_t)mine * 4);
     if (ws_reserve(w, off)) return BLTCU_STATUS_ERROR;
     unsigned char *base = (unsigned char *)w->buf;
     cudaStream_t st = w->stream;
@@ -2238,6 +2412,24 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     }
     BP.warp_doubles = per_warp / 8;
     const size_t smem_bytes = (size_t)wpc * per_warp;
+    BP.allow_help = allow_help && nwarps > 1;
+    BP.gq = (QCtl *)(base + o_gq); BP.hring = (int *)(base + o_hring); BP.hfring = (int *)(base + o_hfring);
+    BP.hmask = (unsigned int)hpool_cap - 1; BP.hpool = base + o_hpool;
+    BP.sbest_u = (int64_t *)(base + o_sbu); BP.sbest_key = base + o_sbk; BP.sbest_valid = (int *)(base + o_sbv);
+    BP.helped = (int *)(base + o_hl);
+    {
+        QCtl hg;
+        memset(&hg, 0, sizeof hg);
+        hg.ftail = (unsigned int)hpool_cap;  // every slot is free
+        hg.active = mine;
+        std::vector<int> ring((size_t)hpool_cap, -1), fring((size_t)hpool_cap);
+        for (int i = 0; i < hpool_cap; ++i) fring[i] = i;
+        CK(cudaMemcpyAsync(BP.gq, &hg, sizeof hg, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(BP.hring, ring.data(), (size_t)hpool_cap * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(BP.hfring, fring.data(), (size_t)hpool_cap * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(BP.helped, 0, (size_t)mine * 4, st));
+        CK(cudaStreamSynchronize(st));  // the host images above go out of scope
+    }
 
     CK(cudaMemcpyAsync(base + o_lat, lat + (size_t)lo * n * m, (size_t)mine * n * m * 8, cudaMemcpyHostToDevice, st));
     CK(cudaMemcpyAsync(base + o_con, con + (size_t)lo * 2 * m, (size_t)mine * 2 * m * 8, cudaMemcpyHostToDevice, st));
@@ -2247,7 +2439,8 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     CK(launch_batch(m, ctas, wpc * 32, smem_bytes, st, BP));
     CK(cudaEventRecord(w->e1, st));
     std::vector<unsigned long long> tot(5 + MAXD + 1), hni(mine), hnp(mine);
-    std::vector<int> hfd(mine);
+    std::vector<int> hfd(mine), hhl(mine);
+    CK(cudaMemcpyAsync(hhl.data(), base + o_hl, (size_t)mine * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(sol + (size_t)lo * n, base + o_sol, (size_t)mine * n * 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(status + lo, base + o_st, (size_t)mine * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hfd.data(), base + o_fd, (size_t)mine * 4, cudaMemcpyDeviceToHost, st));
@@ -2257,20 +2450,87 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     CK(cudaStreamSynchronize(st));
     float ms = 0.f;
     CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
+    if (getenv("BLTCU_VERBOSE")) fprintf(stderr, "bltcu: batch launch of %d problems (help %d): %.3f ms, %d warps\n", mine, BP.allow_help, ms, nwarps);
     unsigned long long sni = 0, snp = 0;
     int nfound = 0;
     for (int i = 0; i < mine; ++i) {
         if (niter) niter[lo + i] = hni[i];
         if (nprune) nprune[lo + i] = hnp[i];
         if (found) found[lo + i] = hfd[i];
+        if (helped) helped[i] = hhl[i];
         sni += hni[i]; snp += hnp[i]; nfound += hfd[i] ? 1 : 0;
     }
     if (stats) {
-        stats->niter = sni; stats->nprune = snp; stats->nodes = tot[0]; stats->pivots = tot[1]; stats->quick_prunes = tot[2];
-        stats->refactors = tot[3]; stats->cold_starts = tot[4];
-        for (int i = 0; i <= n; ++i) stats->hist[i] = tot[5 + i];
-        stats->kernel_ms = ms; stats->found = nfound; stats->launches = 1; stats->warps = nwarps; stats->ctas = ctas;
+        stats->niter += sni; stats->nprune += snp; stats->nodes += tot[0]; stats->pivots += tot[1]; stats->quick_prunes += tot[2];
+        stats->refactors += tot[3]; stats->cold_starts += tot[4];
+        for (int i = 0; i <= n; ++i) stats->hist[i] += tot[5 + i];
+        stats->kernel_ms += ms; stats->found += nfound; stats->launches += 1; stats->warps = nwarps; stats->ctas = ctas;
         stats->scratch_bytes = off;
+    }
+    return BLTCU_STATUS_OK;
+}
+
+// Batch form of the search seam (SURVEY.md section 8b: "arrays of problems, one status per problem").
+extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n, int m, const bltcu_opts *opts,
+                                   int64_t *sol, int *status, uint64_t *niter, uint64_t *nprune, int *found,
+                                   bltcu_stats *stats) {
+    const auto t0 = std::chrono::steady_clock::now();
+    if (count < 0) return BLTCU_STATUS_INPUT_ERROR;
+    const int v = validate(n, m);
+    if (v != BLTCU_STATUS_OK) return v;
+    if (stats) memset(stats, 0, sizeof *stats);
+    if (count == 0) return BLTCU_STATUS_OK;
+    if (!lat || !con || !sol || !status) return BLTCU_STATUS_INPUT_ERROR;
+    bltcu_opts o;
+    memset(&o, 0, sizeof o);
+    if (opts) o = *opts;
+    const int world = o.world > 1 ? o.world : 1, rank = world > 1 ? o.rank : 0;
+    if (rank < 0 || rank >= world) return BLTCU_STATUS_INPUT_ERROR;
+    const int lo = (int)((long long)count * rank / world), hi = (int)((long long)count * (rank + 1) / world);
+    const int mine = hi - lo;
+    if (mine == 0) return BLTCU_STATUS_OK;
+    std::lock_guard<std::mutex> lk(g_mu);
+    DevWs *w = nullptr;
+    if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
+    const size_t nm = (size_t)n * m;
+    std::vector<uint64_t> ni(mine), np(mine);
+    std::vector<int> fd(mine), hl(mine);
+    const int allow_help = getenv("BLTCU_BATCH_NO_HELP") ? 0 : 1;
+    int rc = batch_launch(w, lat + lo * nm, con + (size_t)lo * 2 * m, mine, n, m, o, sol + (size_t)lo * n, status + lo, ni.data(),
+                          np.data(), fd.data(), hl.data(), allow_help, stats);
+    if (rc != BLTCU_STATUS_OK) return rc;
+    // A problem that was shared between warps AND has a point inside the box is searched again by one warp alone:
+    // the point and the counters are then those of the depth-first order, as for every other problem of the batch.
+    std::vector<int> again;
+    for (int i = 0; i < mine; ++i) if (hl[i] && fd[i]) again.push_back(i);
+    if (!again.empty()) {
+        const int k = (int)again.size();
+        std::vector<int64_t> l2(k * nm), c2((size_t)k * 2 * m), s2((size_t)k * n);
+        std::vector<int> st2(k), f2(k);
+        std::vector<uint64_t> ni2(k), np2(k);
+        for (int j = 0; j < k; ++j) {
+            memcpy(&l2[j * nm], lat + (lo + again[j]) * nm, nm * 8);
+            memcpy(&c2[(size_t)j * 2 * m], con + (size_t)(lo + again[j]) * 2 * m, (size_t)2 * m * 8);
+        }
+        if (stats) {  // the first attempt at these problems does not count
+            for (int j = 0; j < k; ++j) { stats->niter -= ni[again[j]]; stats->nprune -= np[again[j]]; stats->found -= 1; }
+        }
+        rc = batch_launch(w, l2.data(), c2.data(), k, n, m, o, s2.data(), st2.data(), ni2.data(), np2.data(), f2.data(), nullptr, 0, stats);
+        if (rc != BLTCU_STATUS_OK) return rc;
+        for (int j = 0; j < k; ++j) {
+            const int i = again[j];
+            memcpy(sol + (size_t)(lo + i) * n, &s2[(size_t)j * n], (size_t)n * 8);
+            status[lo + i] = st2[j]; ni[i] = ni2[j]; np[i] = np2[j]; fd[i] = f2[j];
+        }
+    }
+    for (int i = 0; i < mine; ++i) {
+        if (niter) niter[lo + i] = ni[i];
+        if (nprune) nprune[lo + i] = np[i];
+        if (found) found[lo + i] = fd[i];
+    }
+    if (stats) {
+        stats->donated = 0;
+        for (int i = 0; i < mine; ++i) stats->donated += hl[i] ? 1 : 0;  // problems searched by more than one warp
         stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
     return BLTCU_STATUS_OK;

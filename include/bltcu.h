@@ -77,8 +77,10 @@ int bltcu_closest_dev(const int64_t *d_lat, const int64_t *d_con, int n, int m, 
 /* Batch form of the same seam: `count` independent problems of one shape.
  * lat: count x n x m, con: count x m x 2, sol: count x n, status/found/niter/nprune: count entries each (niter, nprune,
  * found and stats may be NULL).  status[i] is what bltcu_closest() would return for problem i alone.  Each problem is
- * searched by one warp in the reference's own depth-first order (closest.cc:208-318), so for SAT problems too sol,
- * niter and nprune are those of the sequential search.  With opts->world > 1 only problems
+ * searched in the reference's own depth-first order (closest.cc:208-318), so for SAT problems too sol, niter and
+ * nprune are those of the sequential search: a problem starts on one warp; warps that run out of problems take over
+ * subtrees of the ones still running (counts do not depend on who searches what), and a problem that was shared and
+ * turns out to have a point is searched once more by one warp alone (stats->donated = problems that were shared).  With opts->world > 1 only problems
  * [count*rank/world, count*(rank+1)/world) are searched and written.  stats->found = number of problems with a point;
  * the other counters are sums.  Returns BLT_STATUS_OK unless the call itself failed. */
 int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n, int m, const bltcu_opts *opts,
