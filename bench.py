@@ -115,7 +115,7 @@ def batch_supplement(blt_b200):
     dt = time.perf_counter() - t0
     ok = bool((r["niter"] == np.tile(z["niter"], reps)).all() and (r["nprune"] == np.tile(z["nprune"], reps)).all()
               and (r["status"] == np.tile(z["rc"], reps)).all())
-    return {"workload": "config 5: 4000 dense 20x20 instances (tests/golden/batch20.npz x10), one warp per instance",
+    return {"workload": "config 5: 4000 dense 20x20 instances (tests/golden/batch20.npz x10), a warp per instance plus helpers",
             "instances_per_s": len(lats) / dt, "nodes_per_s": r["nodes"] / dt, "kernel_ms": r["kernel_ms"],
             "e2e_ms": 1e3 * dt, "count_ok": ok}
 

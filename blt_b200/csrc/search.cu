@@ -1616,7 +1616,8 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
             int dslot = -1;
             if (lane == 0) {
                 const int idle = *(volatile int *)&BP.gq->idle;
-                if (idle > 0) {
+                // a record near the leaves is less work than handing it over
+                if (idle > 0 && ((const int *)(A.base + A.offs[A.abot]))[0] >= P.donate_min_level) {
                     const int qlen = (int)(*(volatile unsigned int *)&BP.gq->tail - *(volatile unsigned int *)&BP.gq->head);
                     if (qlen < idle) dslot = ring_pop(BP.gq, &BP.gq->fhead, &BP.gq->ftail, BP.hfring, BP.hmask);
                 }
@@ -1669,7 +1670,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
     int more = 1;      // the problem counter is not exhausted
     int am_idle = 0;
     for (;;) {
-        int owner = -1, have_next = 0;
+        int owner = -1, have_next = 0, am_idle_unit = 0;  // am_idle_unit: this unit came from the help ring
         // ---- 1. results of the own problem, once everything handed over has come back ----
         if (owning >= 0) {
             int pend = 0;
@@ -1771,7 +1772,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
             __syncwarp();
             __threadfence();
             if (lane == 0) ring_push(BP.gq, &BP.gq->ftail, BP.hfring, BP.hmask, slot);
-            have_next = 1;
+            have_next = 1; am_idle_unit = 1;
         } else if (lane == 0 && am_idle) {
             atomicSub(&BP.gq->idle, 1);
             am_idle = 0;
@@ -1789,6 +1790,9 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
             P.lat = BP.lat + (size_t)inst * n * m; P.con = BP.con + (size_t)inst * 2 * m; P.sol = BP.sol + (size_t)inst * n;
             P.radius = radius;
             P.q = oq;
+            // a handed-over subtree belongs to a shared problem: its order no longer matters (see the second pass on the
+            // host), so it is expanded eagerly, which produces the records other idle warps are waiting for
+            P.eager_max = (owner == gwarp && owning >= 0 && have_next && !am_idle_unit) ? 1 : EAGER_MAX;
         }
         WS s;
         Arena A;
@@ -2356,13 +2360,15 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
         return BLTCU_STATUS_ERROR;
     }
     int ctas = o.ctas > 0 ? o.ctas : w->sms;
-    ctas = std::max(1, std::min(ctas, (mine + wpc - 1) / wpc));
+    if (!allow_help) ctas = std::max(1, std::min(ctas, (mine + wpc - 1) / wpc));  // with helping, warps without a problem of their own are useful
     const int nwarps = ctas * wpc;
     const RecLayout RL = rec_layout(n, m);
     size_t arena_bytes = RL.stride;
     for (int k0 = 2; k0 <= n; ++k0) arena_bytes += 2 * cont_layout(RL, m, k0).bytes;  // parks when half full
+    // handed-over subtrees are expanded eagerly (several children per loop): a stack like the one-problem search's
+    if (allow_help) arena_bytes = std::max(arena_bytes, (size_t)48 * RL.stride);
     arena_bytes = align_up(arena_bytes, 256);
-    const int arena_slots = 2 * n + 16;
+    const int arena_slots = allow_help ? 1024 : 2 * n + 16;
     const size_t arena_stride = align_up(arena_bytes + (size_t)arena_slots * 4, 256);
     const size_t wbuf_stride = align_up((size_t)2 * m * m + (size_t)2 * m * LDG, 32);
     const size_t geo_stride = align_up(((size_t)n * m + 4 * (size_t)m + 2 * (size_t)m * m + (size_t)n * n) * 8 + 32, 256);
@@ -2397,6 +2403,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     P.warps_per_cta = wpc;
     P.warp_smem_doubles = warp_bytes / 8;
     P.eager_max = 1;
+    P.donate_min_level = std::min(6, std::max(2, n / 3));
     BP.lat = (const int64_t *)(base + o_lat); BP.con = (const int64_t *)(base + o_con);
     BP.count = mine;
     BP.next = (int *)(base + o_next);
