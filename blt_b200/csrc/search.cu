@@ -2263,10 +2263,16 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         std::vector<int> bv(nwarps);
         CK(cudaMemcpy(bv.data(), P.best_valid, (size_t)nwarps * 4, cudaMemcpyDeviceToHost));
         int bestw = -1;
-        std::vector<unsigned char> bkey(n), key(n);
+        std::vector<unsigned char> bkey(n), key(n), keys;
+        bool any = false;
+        for (int i = 0; i < nwarps; ++i) any = any || bv[i];
+        if (any) {  // all keys in one copy
+            keys.resize((size_t)nwarps * n);
+            CK(cudaMemcpy(keys.data(), P.best_key, (size_t)nwarps * n, cudaMemcpyDeviceToHost));
+        }
         for (int i = 0; i < nwarps; ++i) {
             if (!bv[i]) continue;
-            CK(cudaMemcpy(key.data(), P.best_key + (size_t)i * n, n, cudaMemcpyDeviceToHost));
+            key.assign(keys.begin() + (size_t)i * n, keys.begin() + (size_t)(i + 1) * n);
             std::reverse(key.begin(), key.end());
             if (bestw < 0 || key >= bkey) { bestw = i; bkey = key; }
         }
