@@ -52,3 +52,43 @@ def closest_sharded(lat, con, split_depth: int = 6, **opts) -> dict:
     world = dist.get_world_size() if dist.is_initialized() else 1
     local = blt_b200.closest(lat, con, rank=rank, world=world, split_depth=split_depth if world > 1 else 0, **opts)
     return reduce_results(local, np.asarray(lat).shape[0])
+
+
+def gather_batch(local: dict, count: int, group=None, device=None) -> dict:
+    """Every rank has searched its contiguous share [count*rank/world, count*(rank+1)/world) of a batch (the entries of
+    the other problems are untouched placeholders); returns the complete per-problem arrays on every rank.  One
+    all-reduce per array: the shares are disjoint, so a sum over ranks of the masked arrays is the gather."""
+    import torch
+    import torch.distributed as dist
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    if world == 1:
+        return dict(local)
+    rank = dist.get_rank(group)
+    dev = device if device is not None else ("cuda" if dist.get_backend(group) == "nccl" else "cpu")
+    lo, hi = count * rank // world, count * (rank + 1) // world
+    out = dict(local)
+    for key in ("status", "sol", "niter", "nprune", "found"):
+        a = np.asarray(local[key])
+        masked = np.zeros(a.shape, dtype=np.int64)
+        masked[lo:hi] = a[lo:hi].astype(np.int64)
+        t = torch.from_numpy(masked).to(dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        out[key] = t.cpu().numpy().astype(a.dtype)
+    ms = torch.tensor([float(local.get("kernel_ms", 0.0))], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX, group=group)
+    out["kernel_ms"] = float(ms.item())
+    return out
+
+
+def closest_batch_sharded(lats, cons, **opts) -> dict:
+    """closest_batch() over all ranks of the default process group: rank r searches the r-th contiguous share of the
+    problems on its GPU, then the per-problem results are gathered on every rank."""
+    import torch.distributed as dist
+
+    import blt_b200
+
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    world = dist.get_world_size() if dist.is_initialized() else 1
+    local = blt_b200.closest_batch(lats, cons, rank=rank, world=world, **opts)
+    return gather_batch(local, len(np.asarray(lats)))

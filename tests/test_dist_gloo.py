@@ -44,3 +44,51 @@ def test_two_rank_reduction():
         assert hist == [1, 3, 5, 7, 9, 11]
         assert ms == 2.5 and found and rc == 0
         assert sol == [0, 2, 4, 6, 8]  # rank 1 is the only finder: every rank ends with its point
+
+
+def _batch_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+
+    from blt_b200.dist import gather_batch
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    count, n = 7, 3
+    lo, hi = count * rank // world, count * (rank + 1) // world
+    # what bltcu_closest_batch leaves on a rank: its own share filled in, placeholders elsewhere
+    status = np.full(count, -1, dtype=np.int32)
+    status[lo:hi] = 0
+    sol = np.zeros((count, n), dtype=np.int64)
+    sol[lo:hi] = -(np.arange(lo, hi)[:, None] * 10 + np.arange(n)[None, :])
+    niter = np.zeros(count, dtype=np.uint64)
+    niter[lo:hi] = np.arange(lo, hi) + 100
+    nprune = np.zeros(count, dtype=np.uint64)
+    nprune[lo:hi] = 2 * np.arange(lo, hi)
+    found = np.zeros(count, dtype=bool)
+    found[lo:hi] = (np.arange(lo, hi) % 2 == 0)
+    out = gather_batch(dict(status=status, sol=sol, niter=niter, nprune=nprune, found=found, kernel_ms=3.0 + rank), count)
+    q.put((rank, out["status"].tolist(), out["sol"].tolist(), out["niter"].tolist(), out["nprune"].tolist(),
+           out["found"].tolist(), out["kernel_ms"]))
+    dist.destroy_process_group()
+
+
+def test_two_rank_batch_gather():
+    """Config 5 shards whole problems: every rank ends with the results of all of them."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29900 + os.getpid() % 90
+    procs = [ctx.Process(target=_batch_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, status, sol, niter, nprune, found, ms in res:
+        assert status == [0] * 7
+        assert sol == [[-(i * 10 + j) for j in range(3)] for i in range(7)]
+        assert niter == [100 + i for i in range(7)] and nprune == [2 * i for i in range(7)]
+        assert found == [i % 2 == 0 for i in range(7)]
+        assert ms == 4.0
