@@ -128,3 +128,18 @@ def test_batch_edge_cases(gpu):
     assert got["found"][0] and got["found"][2] and not got["found"][1]
     ref = oracle.closest(good, box)
     assert (got["sol"][0] == ref["sol"]).all() and got["niter"][0] == ref["niter"] and got["nprune"][0] == ref["nprune"]
+
+
+def test_batch_of_large_problems_is_shared_between_warps(gpu):
+    """Three copies of the 1.8 M-node n = m = 60 instance: far more warps than problems, so almost all of the work is
+    done by helpers on handed-over subtrees -- counts, histogram total and the returned vector still equal the
+    oracle's stored values."""
+    z = np.load(os.path.join(GOLDEN, "bench_dense60.npz"))
+    lats = np.stack([z["lat"]] * 3)
+    cons = np.stack([z["con"]] * 3)
+    got = gpu.closest_batch(lats, cons, timeout_ms=300000)
+    assert got["rc"] == 0 and (got["status"] == 0).all() and not got["found"].any()
+    assert (got["niter"] == int(z["niter"])).all() and (got["nprune"] == int(z["nprune"])).all()
+    assert (got["sol"] == z["sol"]).all()
+    assert got["nodes"] == 3 * int(z["nodes"]) and got["pivots"] == 3 * int(z["pivots"])
+    assert got["donated"] == 3  # all three were shared
