@@ -1,7 +1,8 @@
 """Parity of the batch form of the search seam (bltcu_closest_batch) with the oracle.
 
-Every problem of a batch is searched by one warp in the reference's own depth-first order, so the bar is bit-exact
-for SAT problems too: status, decision, niter, nprune and the returned vector equal the sequential oracle's.
+Every problem of a batch is searched in the reference's own depth-first order (idle warps help with subtrees; a
+shared problem that turns out SAT is searched again by one warp alone), so the bar is bit-exact for SAT problems too:
+status, decision, niter, nprune and the returned vector equal the sequential oracle's.
 """
 import os
 
