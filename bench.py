@@ -135,7 +135,7 @@ def run_reference(args, rank, world):
     if rank != 0:
         return 0
     wl = load_workload()
-    sample_nodes = 60000
+    sample_nodes = int(os.environ.get("BLT_BENCH_REF_NODES", "60000"))
     for _ in range(args.warmup):
         cpu_sample(wl, 5000)
     tot_nodes, tot_t = 0, 0.0
