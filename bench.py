@@ -124,7 +124,17 @@ def batch_supplement(blt_b200):
     dt_l = time.perf_counter() - t1
     lll = {"workload": "4000 exact LLL reductions of 20x20 integer bases, entries in [-100, 100], one warp each",
            "problems_per_s": len(Bs) / dt_l, "kernel_ms": linfo["kernel_ms"], "e2e_ms": 1e3 * dt_l, "on_host": linfo["on_host"]}
-    return {"lll_batch": lll,
+    # time-to-decision on the reference's own SAT regression fixtures (64 x 64, LLL-reduced; SURVEY.md 8d metric ii)
+    sat = []
+    zj = np.load(os.path.join(ROOT, "tests", "golden", "jpeg_reduced.npz"))
+    for name in ("test_95", "test_50", "test_50_8"):
+        la, co = zj[f"lat_{name}"], zj[f"con_{name}"]
+        blt_b200.closest(la, co, timeout_ms=60000)
+        t1 = time.perf_counter()
+        g = blt_b200.closest(la, co, timeout_ms=60000)
+        sat.append({"instance": name, "found": bool(g["found"]), "gpu_ms": 1e3 * (time.perf_counter() - t1),
+                    "gpu_nodes": int(g["nodes"]), "cpu_port_nodes": int(zj[f"nodes_{name}"])})
+    return {"lll_batch": lll, "sat_time_to_decision": sat,
             "workload": "config 5: 4000 dense 20x20 instances (tests/golden/batch20.npz x10), a warp per instance plus helpers",
             "instances_per_s": len(lats) / dt,
             "nodes_per_s": (int(r["niter"].sum()) + int(r["nprune"].sum()) + len(lats)) / dt, "kernel_ms": r["kernel_ms"],

@@ -556,11 +556,13 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
 #pragma unroll 1
             for (int i = 0; i < qd; ++i) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
         }
-    } else {
+    } else {  // lanes over the columns (two or three per lane), rows in a loop
 #pragma unroll 1
-        for (int x = s.lane; x < qd * qd; x += 32) {
-            const int i = x / qd, c = x - i * qd;
-            if (i != pe) H[(size_t)i * LD + c] = fma(-s.w[i], s.v[c], H[(size_t)i * LD + c]);
+        for (int c = s.lane; c < qd; c += 32) {
+            const double vc = s.v[c];
+            double *Hc = H + c;
+#pragma unroll 1
+            for (int i = 0; i < qd; ++i) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
         }
     }
     __syncwarp();
@@ -821,9 +823,12 @@ __device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, si
 #pragma unroll 1
             for (int i = 0; i < q; ++i) dst[(size_t)i * q] = src[(size_t)i * LD];
         }
-    } else {
+    } else {  // rows one after the other, lanes over the columns: no index division either
 #pragma unroll 1
-        for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; dH[x] = s.W[(size_t)i * LD + c]; }
+        for (int i = 0; i < q; ++i) {
+#pragma unroll 1
+            for (int c = s.lane; c < q; c += 32) dH[(size_t)i * q + c] = s.W[(size_t)i * LD + c];
+        }
     }
 #pragma unroll 1
     for (int p = s.lane; p < q; p += 32) dI[p] = s.zrow[p];
@@ -843,7 +848,10 @@ __device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *d
         }
     } else {
 #pragma unroll 1
-        for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
+        for (int i = 0; i < q; ++i) {
+#pragma unroll 1
+            for (int c = s.lane; c < q; c += 32) s.W[(size_t)i * LD + c] = dH[(size_t)i * q + c];
+        }
     }
 #pragma unroll 1
     for (int j = s.lane; j < s.m; j += 32) { s.sg[j] = dB[j]; s.pos[j] = 0; }
