@@ -80,8 +80,10 @@ struct QCtl {
     unsigned int out_count;     // static split: number of collected subtrees
     int timed_out;              // watchdog fired: 1 node loop, 2 idle loop, 3 pop spin, 4 push spin
     int fail_info;              // failcode | level << 8 of the first LP failure (diagnostics)
+    int dive_state;             // first descent of the search: 0 not started, 1 under way (the other warps wait), 2 over
     unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
     unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated;
+    unsigned long long dive_end_ns;  // %globaltimer when the first descent ended (diagnostics)
     unsigned long long idle_ns, busy_ns;  // summed over warps: time spent waiting for work / expanding records
     unsigned long long hist[MAXD + 1];
     long long fail_u[MAXD];     // coefficients of the node whose LP failed first (diagnostics)
@@ -127,6 +129,7 @@ struct Params {
     int donate_min_level;
     int lowwater;
     int no_early_exit;
+    int dive_hold;          // 1 = the other warps wait while the first descent is under way
     int eager_max;          // explored children a sibling loop produces before it is parked (1 = the reference's depth-first order)
     int warps_per_cta;
     size_t warp_smem_doubles;
@@ -556,13 +559,11 @@ __device__ __forceinline__ int lp_replace(WS &s, int pe, int l, int se) {
 #pragma unroll 1
             for (int i = 0; i < qd; ++i) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
         }
-    } else {  // lanes over the columns (two or three per lane), rows in a loop
+    } else {
 #pragma unroll 1
-        for (int c = s.lane; c < qd; c += 32) {
-            const double vc = s.v[c];
-            double *Hc = H + c;
-#pragma unroll 1
-            for (int i = 0; i < qd; ++i) Hc[(size_t)i * LD] = fma(-s.w[i], vc, Hc[(size_t)i * LD]);
+        for (int x = s.lane; x < qd * qd; x += 32) {
+            const int i = x / qd, c = x - i * qd;
+            if (i != pe) H[(size_t)i * LD + c] = fma(-s.w[i], s.v[c], H[(size_t)i * LD + c]);
         }
     }
     __syncwarp();
@@ -823,12 +824,9 @@ __device__ __forceinline__ void chain_store(const WS &s, double *dH, int *dI, si
 #pragma unroll 1
             for (int i = 0; i < q; ++i) dst[(size_t)i * q] = src[(size_t)i * LD];
         }
-    } else {  // rows one after the other, lanes over the columns: no index division either
+    } else {
 #pragma unroll 1
-        for (int i = 0; i < q; ++i) {
-#pragma unroll 1
-            for (int c = s.lane; c < q; c += 32) dH[(size_t)i * q + c] = s.W[(size_t)i * LD + c];
-        }
+        for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; dH[x] = s.W[(size_t)i * LD + c]; }
     }
 #pragma unroll 1
     for (int p = s.lane; p < q; p += 32) dI[p] = s.zrow[p];
@@ -848,10 +846,7 @@ __device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *d
         }
     } else {
 #pragma unroll 1
-        for (int i = 0; i < q; ++i) {
-#pragma unroll 1
-            for (int c = s.lane; c < q; c += 32) s.W[(size_t)i * LD + c] = dH[(size_t)i * q + c];
-        }
+        for (int x = s.lane; x < q * q; x += 32) { const int i = x / q, c = x - i * q; s.W[(size_t)i * LD + c] = dH[x]; }
     }
 #pragma unroll 1
     for (int j = s.lane; j < s.m; j += 32) { s.sg[j] = dB[j]; s.pos[j] = 0; }
@@ -1372,8 +1367,14 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
                 if (have_token) { __threadfence(); atomicSub(&q->pending, 1); }
                 if (*(volatile int *)&q->abort) stop = 1;
                 else {
-                    slot = ring_pop(q, &q->head, &q->tail, P.ring, P.ring_mask);
-                    if (slot < 0) {
+                    // While the first descent is under way the other warps stay out of its way: it decides how fast a
+                    // problem with a point near the Babai point is answered, and it takes n node latencies at most.
+                    const bool hold = P.dive_hold && *(volatile int *)&q->dive_state == 1;
+                    if (hold) { __nanosleep(500); if (overdue(q, 2)) stop = 1; }
+                    else slot = ring_pop(q, &q->head, &q->tail, P.ring, P.ring_mask);
+                    if (slot >= 0 && (((const int *)(P.pool + (size_t)slot * RL.stride))[1] & REC_DIVE)) q->dive_state = 1;
+                    if (hold) {}
+                    else if (slot < 0) {
                         if (*(volatile int *)&q->pending == 0) stop = 1;
                         else {
                             if (!am_idle) { atomicAdd(&q->idle, 1); am_idle = true; }
@@ -1394,16 +1395,23 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         // a popped stack record sits where new children would be pushed: expand() copies what it needs first, and the
         // stack top was lowered above, so the children overwrite it only after it is dead
         { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_IDLE_NS] += t - t_mark; t_mark = t; }
+        const int was_dive = ((const int *)R)[1] & REC_DIVE;
         have_next = expand(P, s, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
         __syncwarp();
+        int burst = 0;  // the first descent just ended: its parked loops go to the waiting warps all at once
+        if (was_dive && !(have_next && (((const int *)(nextbuf + (size_t)nextsel * RL.stride))[1] & REC_DIVE))) {
+            if (lane == 0) { q->dive_end_ns = gtimer(); q->dive_state = 2; __threadfence(); }  // everybody in
+            burst = P.dive_hold;
+        }
         { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_BUSY_NS] += t - t_mark; t_mark = t; }
         // hand the oldest pending record to an idle warp
-        if (P.dynamic && A.acount > A.abot) {
+#pragma unroll 1
+        for (int rounds = burst ? A.acount - A.abot : 1; rounds > 0 && P.dynamic && A.acount > A.abot; --rounds) {
             int want = 0, dslot = -1;
             if (lane == 0) {
                 const int idle = *(volatile int *)&q->idle;
                 const int qlen = (int)(*(volatile unsigned int *)&q->tail - *(volatile unsigned int *)&q->head);
-                want = (idle > 0 && qlen < idle + P.lowwater) ? 1 : 0;
+                want = (burst || (idle > 0 && qlen < idle + P.lowwater)) ? 1 : 0;
                 if (want) dslot = ring_pop(q, &q->fhead, &q->ftail, P.fring, P.ring_mask);
             }
             dslot = __shfl_sync(FULLMASK, dslot, 0);
@@ -2033,6 +2041,7 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
     P.warp_smem_doubles = L.warp_bytes / 8;
     P.lowwater = std::min(L.nwarps, L.pool_cap / 4);
     P.eager_max = EAGER_MAX;
+    P.dive_hold = getenv("BLTCU_NO_DIVE_HOLD") ? 0 : 1;
 }
 }  // namespace
 
@@ -2173,7 +2182,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
         kernel_ms += ms;
         launches++;
-        if (verbose) fprintf(stderr, "bltcu: search launch %d (static depth %d): %.3f ms, %llu nodes, %u subtrees published\n", launches, P.static_depth, ms, (unsigned long long)hq.nodes, hq.out_count);
+        if (verbose) fprintf(stderr, "bltcu: search launch %d (static depth %d): %.3f ms, %llu nodes, %u subtrees published, first descent over after %.3f ms\n", launches, P.static_depth, ms, (unsigned long long)hq.nodes, hq.out_count, hq.dive_end_ns ? (double)(hq.dive_end_ns - now_rc[0]) * 1e-6 : -1.0);
         if (hq.fail_info) lp_failed = true;
         if (hq.fail_info && verbose) {
             fprintf(stderr, "bltcu: LP failure code %d at level k=%d (basis size %d), u =", hq.fail_info & 255, (hq.fail_info >> 8) & 255, hq.fail_info >> 16);
