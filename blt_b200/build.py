@@ -17,15 +17,32 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
               "-Xcompiler", "-fPIC", "-shared"]
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    os.makedirs(os.path.dirname(OUT), exist_ok=True)
-    deps = SRC + [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h")]
-    if not force and os.path.exists(OUT) and all(os.path.getmtime(OUT) >= os.path.getmtime(d) for d in deps):
-        build_host()
-        return OUT
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT] + SRC
+def _obj(src: str) -> str:
+    return os.path.join(HERE, "lib", "obj", os.path.basename(src) + ".o")
+
+
+def _compile(src: str, verbose: bool) -> None:
+    cmd = ["nvcc"] + [f for f in NVCC_FLAGS if f != "-shared"] + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", _obj(src), src]
     subprocess.check_call(cmd)
-    build_host(force=True)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Every source is compiled to its own object (in parallel, only when stale), then linked into libbltcu.so."""
+    from concurrent.futures import ThreadPoolExecutor
+
+    os.makedirs(os.path.join(HERE, "lib", "obj"), exist_ok=True)
+    hdrs = [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h")]
+    newest_hdr = max(os.path.getmtime(h) for h in hdrs)
+    stale = [src for src in SRC if force or not os.path.exists(_obj(src))
+             or os.path.getmtime(_obj(src)) < max(os.path.getmtime(src), newest_hdr)]
+    if stale:
+        with ThreadPoolExecutor(max_workers=len(stale)) as ex:
+            list(ex.map(lambda src: _compile(src, verbose), stale))
+    if stale or not os.path.exists(OUT):
+        subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", OUT] + [_obj(src) for src in SRC])
+        build_host(force=True)
+    else:
+        build_host()
     return OUT
 
 

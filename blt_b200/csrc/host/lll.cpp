@@ -5,8 +5,9 @@
 // dependent moved to the front.  On return the first (r - rank) rows of B are zero, the last `rank` rows are the
 // reduced basis and U * B_in = B_out; entries are narrowed to int64 the way NTL's to_long() does (low 64 bits).
 //
-// Round 1: this is the exact host implementation (own multiprecision integers; no GMP/NTL in the image).  It is the
-// certified path a batched device kernel will fall back to; it never calls into oracle/.
+// This is the exact host implementation (own multiprecision integers; no GMP/NTL in the image): fixed-capacity
+// arithmetic first (lll_fixed.h, shared with the batched device kernel), arbitrary precision when a number outgrows
+// it.  The batched kernel falls back to it; it never calls into oracle/.
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
@@ -314,7 +315,37 @@ struct LLLState {
 
 // LLL(B, U): libblt/ntl_wrapper.h:20, libblt/ntl_wrapper.cc:37-52.  B: r x c row-major, reduced in place; U: r x r out
 // (may be NULL).  *rank receives the rank.  Returns BLT_STATUS_OK or BLT_STATUS_INPUT_ERROR.
+// the arbitrary-precision path on its own (also a test seam: the fixed-capacity code is pinned against it)
+extern "C" int bltcu_lll_arbitrary(int64_t *B, int64_t *U, int r, int c, int *rank);
+
+// First the fixed-capacity arithmetic of lll_fixed.h with 512-bit, then with 1024-bit numbers (no allocation per
+// operation: about twice as fast as the vectors below); it reports an overflow instead of truncating, and only then the
+// arbitrary-precision integers take over.  All three perform the same operations, so the result does not depend on
+// which one finished.
 extern "C" int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank) {
+    if (!B || r <= 0 || c <= 0 || !rank) return BLTCU_STATUS_INPUT_ERROR;
+    if ((long)r * c <= 128 * 128) {
+        std::vector<int64_t> b((size_t)r * c), u((size_t)r * r);
+        for (int pass = 0; pass < 2; ++pass) {
+            const long bytes = pass == 0 ? lllfix::bytes_needed<16>(r, c) : lllfix::bytes_needed<32>(r, c);
+            void *work = malloc((size_t)bytes);
+            if (!work) break;
+            std::copy(B, B + (size_t)r * c, b.begin());
+            const int rk = pass == 0 ? lllfix::reduce_one<16, lllfix::OneLane>(b.data(), u.data(), r, c, work)
+                                     : lllfix::reduce_one<32, lllfix::OneLane>(b.data(), u.data(), r, c, work);
+            free(work);
+            if (rk >= 0) {
+                memcpy(B, b.data(), b.size() * 8);
+                if (U) memcpy(U, u.data(), u.size() * 8);
+                *rank = rk;
+                return BLTCU_STATUS_OK;
+            }
+        }
+    }
+    return bltcu_lll_arbitrary(B, U, r, c, rank);
+}
+
+extern "C" int bltcu_lll_arbitrary(int64_t *B, int64_t *U, int r, int c, int *rank) {
     if (!B || r <= 0 || c <= 0 || !rank) return BLTCU_STATUS_INPUT_ERROR;
     LLLState S;
     S.m = r; S.n = c;

@@ -54,6 +54,8 @@ def lib() -> ctypes.CDLL:
         L.bltcu_lll_batch.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int),
                                       ctypes.c_int, ctypes.POINTER(Stats)]
         L.bltcu_lll_batch.restype = ctypes.c_int
+        L.bltcu_lll_arbitrary.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+        L.bltcu_lll_arbitrary.restype = ctypes.c_int
         L.bltcu_lll_fixed_host.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
         L.bltcu_lll_fixed_host.restype = ctypes.c_int
         L.bltcu_check_soln.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
@@ -243,3 +245,15 @@ def lll_fixed_host(B, limbs: int = 16):
     rk = ctypes.c_int(0)
     rc = lib().bltcu_lll_fixed_host(_p(B, ctypes.c_int64), _p(U, ctypes.c_int64), r, c, ctypes.byref(rk), limbs)
     return rc, int(rk.value), B, U
+
+
+def lll_arbitrary(B):
+    """Test seam: the arbitrary-precision LLL alone (lll() tries the fixed-capacity arithmetic first).  (rank, B, U)."""
+    B = _i64(B).copy()
+    r, c = B.shape
+    U = np.zeros((r, r), dtype=np.int64)
+    rk = ctypes.c_int(0)
+    rc = lib().bltcu_lll_arbitrary(_p(B, ctypes.c_int64), _p(U, ctypes.c_int64), r, c, ctypes.byref(rk))
+    if rc != BLT_STATUS_OK:
+        raise RuntimeError(f"bltcu_lll_arbitrary failed with status {rc}")
+    return int(rk.value), B, U

@@ -71,7 +71,9 @@ def test_fixed_capacity_lll_equals_arbitrary_precision():
         cases.append(rng.integers(-100, 101, size=(40, 20)))
     fitted = 0
     for B in cases:
-        rk0, B0, U0 = blt_b200.lll(B)
+        rk0, B0, U0 = blt_b200.lll_arbitrary(B)
+        rkd, Bd, Ud = blt_b200.lll(B)  # the default entry point: whichever arithmetic finished, the same answer
+        assert rkd == rk0 and (Bd == B0).all() and (Ud == U0).all()
         for limbs in (16, 32):
             rc, rk1, B1, U1 = blt_b200.lll_fixed_host(B, limbs)
             if rc != blt_b200.BLT_STATUS_OK:
