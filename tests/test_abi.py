@@ -38,3 +38,28 @@ def test_no_gpu_fails_loudly():
         return
     r = blt_b200.closest(np.array([[1, 0], [-1, 2]]), np.array([[2, 3], [2, 3]]))
     assert r["rc"] == blt_b200.BLT_STATUS_ERROR
+
+
+def test_ctypes_mirrors_have_the_header_layout(tmp_path):
+    """The Python mirrors of bltcu_opts and bltcu_stats must have the sizes and field offsets the C header gives them
+    (a drifted mirror would make every option silently mean something else)."""
+    import subprocess
+
+    from blt_b200 import search
+
+    fields_o = [f[0] for f in search.Opts._fields_]
+    fields_s = [f[0] for f in search.Stats._fields_]
+    src = tmp_path / "sz.c"
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "bltcu.h"', 'int main(void) {',
+             '  printf("%zu %zu\\n", sizeof(bltcu_opts), sizeof(bltcu_stats));']
+    lines += [f'  printf("%zu\\n", offsetof(bltcu_opts, {f}));' for f in fields_o]
+    lines += [f'  printf("%zu\\n", offsetof(bltcu_stats, {f}));' for f in fields_s]
+    lines += ['  return 0;', '}']
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "sz"
+    subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)])
+    out = subprocess.check_output([str(exe)], text=True).split()
+    assert int(out[0]) == ctypes.sizeof(search.Opts) and int(out[1]) == ctypes.sizeof(search.Stats)
+    offs = list(map(int, out[2:]))
+    assert offs[:len(fields_o)] == [getattr(search.Opts, f).offset for f in fields_o]
+    assert offs[len(fields_o):] == [getattr(search.Stats, f).offset for f in fields_s]
