@@ -187,3 +187,33 @@ def test_check_batch_equals_single_checks(api):
     for ctx in ctxs:
         ctx.free()
     assert api.check_batch([]) == []
+
+
+def test_zero_is_feasible_means_sat(api):
+    """test/QCTests.hs:48-115: random systems up to 12 x 12 whose bounds [-b, -1] ... [1, b] all contain 0 must come
+    back SAT with a model inside the bounds -- here all of them in one blt_check_batch call (many shapes at once)."""
+    rng = np.random.default_rng(48)
+    systems = []
+    for _ in range(36):
+        nv, nr = int(rng.integers(1, 13)), int(rng.integers(1, 13))
+        A = rng.integers(-9, 10, size=(nr, nv))
+        for r in range(nr):
+            if not A[r].any():
+                A[r, int(rng.integers(0, nv))] = 1
+        lo = -rng.integers(1, 11, size=nr)
+        hi = rng.integers(1, 11, size=nr)
+        names = [f"v{i}" for i in range(nv)]
+        rows = [(int(lo[r]), [int(x) for x in A[r]], int(hi[r]), 0) for r in range(nr)]
+        # every variable must occur in some row, or it is not part of the lattice (context.cc:336-377)
+        used = A.any(axis=0)
+        names = [nm for nm, u in zip(names, used) if u]
+        rows = [(l, [c for c, u in zip(cf, used) if u], h, k) for l, cf, h, k in rows]
+        systems.append((rows, names))
+    ctxs = [_system(api, rows, names) for rows, names in systems]
+    got = api.check_batch(ctxs)
+    for (rows, names), ctx, g in zip(systems, ctxs, got):
+        assert g == SAT
+        x = [ctx.model(nm)[1] for nm in names]
+        for lo, coef, hi, const in rows:
+            assert lo <= sum(c * xi for c, xi in zip(coef, x)) + const <= hi
+        ctx.free()
