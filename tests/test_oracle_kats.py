@@ -220,3 +220,36 @@ def test_quickcheck_zero_feasible():  # test/QCTests.hs:48-115
         assert r["rc"] == oracle.BLT_CHECK_SAT
         v = A @ np.array(r["model"], dtype=np.int64)
         assert (C[:, 0] <= v).all() and (v <= C[:, 1]).all()
+
+
+# ---- libblt/test_compare_glpk_yices.cc:47-104 in spirit: the layer distance against an independent LP solver ----------
+def test_infdist_agrees_with_an_independent_lp_solver():
+    """Random instances in 2 to 12 dimensions: min_x max_j |sum_{i<k} x_i B_ij + sum_{i>=k} u_i B_ij - p_j| from the oracle's
+    dual simplex equals the optimum of the same LP handed to SciPy's HiGHS (relative 1e-7), and the returned x attains it."""
+    from scipy.optimize import linprog
+
+    rng = np.random.default_rng(2024)
+    checked = 0
+    for trial in range(150):
+        n = int(rng.integers(2, 13))
+        m = n + int(rng.integers(0, 4))
+        B = rng.integers(-50, 51, size=(n, m)).astype(np.float64)
+        if np.linalg.matrix_rank(B) < n:
+            continue
+        k = int(rng.integers(0, n + 1))
+        u = np.zeros(n, dtype=np.int64)
+        u[k:] = rng.integers(-5, 6, size=n - k)
+        p = rng.integers(-200, 201, size=m).astype(np.float64) / 2.0
+        rc, d, x = oracle.infdist(B, u, k, p)
+        assert rc == 0
+        c = p - u[k:].astype(np.float64) @ B[k:]          # target of the free part
+        # variables (x_0..x_{k-1}, t): minimise t subject to |c_j - sum_i x_i B_ij| <= t
+        A_ub = np.vstack([np.hstack([-B[:k].T, -np.ones((m, 1))]), np.hstack([B[:k].T, -np.ones((m, 1))])])
+        b_ub = np.concatenate([-c, c])
+        res = linprog(np.r_[np.zeros(k), 1.0], A_ub=A_ub, b_ub=b_ub, bounds=[(None, None)] * k + [(0, None)], method="highs")
+        assert res.status == 0
+        assert abs(d - res.fun) <= 1e-7 * max(1.0, abs(res.fun))
+        if k:
+            assert abs(np.max(np.abs(c - x @ B[:k])) - d) <= 1e-7 * max(1.0, d)
+        checked += 1
+    assert checked >= 120
