@@ -1,6 +1,7 @@
 // blt_api.cpp -- the twelve functions of blt.h (reference: libblt/blt.cc:22-120), same ownership rules:
 // every CExpr is owned by the library and freed by blt_free(); callers never free.
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -8,10 +9,15 @@
 #include "../../../include/codes.h"
 #include "context.h"
 
+// The reference's pools are unlocked globals (blt.cc:22-23), which forbids contexts on different threads; here the
+// maps are guarded, so distinct contexts may be built, checked and freed concurrently (one context is still
+// single-threaded, like every object of the API).
+static std::mutex pool_mu;
 static std::map<CContext, std::vector<Expr *>> e_pool;
 static std::map<CContext, std::vector<SolvState *>> s_pool;
 
 static CExpr keep(CContext ctx, Expr *e) {
+    std::lock_guard<std::mutex> lk(pool_mu);
     e_pool[ctx].push_back(e);
     return reinterpret_cast<CExpr>(e);
 }
@@ -59,6 +65,7 @@ int blt_model(const CContext ctx, const char *name, int64 *val) {
 
 CSolvState blt_save(CContext ctx) {
     SolvState *s = new SolvState(reinterpret_cast<Context *>(ctx)->save_state());
+    std::lock_guard<std::mutex> lk(pool_mu);
     s_pool[ctx].push_back(s);  // the reference leaks these (blt.cc:96-99); pooling them is invisible to callers
     return reinterpret_cast<CSolvState>(s);
 }
@@ -68,10 +75,15 @@ int blt_backtrack(CContext ctx, CSolvState sav) {
 }
 
 void blt_free(CContext ctx) {
-    for (Expr *e : e_pool[ctx]) delete e;
-    e_pool.erase(ctx);
-    for (SolvState *s : s_pool[ctx]) delete s;
-    s_pool.erase(ctx);
+    std::vector<Expr *> es;
+    std::vector<SolvState *> ss;
+    {
+        std::lock_guard<std::mutex> lk(pool_mu);
+        es.swap(e_pool[ctx]); e_pool.erase(ctx);
+        ss.swap(s_pool[ctx]); s_pool.erase(ctx);
+    }
+    for (Expr *e : es) delete e;
+    for (SolvState *s : ss) delete s;
     delete reinterpret_cast<Context *>(ctx);
 }
 

@@ -18,7 +18,6 @@
 #include "../../../include/codes.h"
 #include "context.h"
 
-extern "C" int blt_b200_last_stats(CContext, uint64_t *, uint64_t *, int *, double *, double *);
 
 static void print_usage(char *argv[]) {
     std::cout << "Usage: " << argv[0] << " [options]  <input>\n\n  [options]\n"

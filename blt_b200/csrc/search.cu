@@ -55,6 +55,8 @@
 #define MAXD BLTCU_MAX_DIM
 #define QS_MAX 24  // largest basis kept in shared memory (larger ones live in the per-warp global buffers)
 #define LDS_C 26   // row stride of the shared-memory matrices: ld_vec(QS_MAX)
+typedef unsigned short ord_t;  // sibling ordinal on one level of a path key (saturates at ORD_MAX)
+#define ORD_MAX 65535
 #define LDQ_C 26   // row stride of the shared-memory copy of the first QS_MAX + 1 columns of Q: ld_vec(QS_MAX + 1)
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
@@ -121,7 +123,7 @@ struct Params {
     int arena_slots;        // entries of the offset table
     int64_t *sol;           // n, written by the finder
     int64_t *best_u;        // per warp: n (last recorded candidate)
-    unsigned char *best_key;// per warp: n
+    ord_t *best_key;        // per warp: n
     int *best_valid;        // per warp
     int *out_list;          // static split output (record indices)
     int static_depth;       // records shallower than this emit every child; children at this depth are collected
@@ -148,7 +150,7 @@ __host__ __device__ inline RecLayout rec_layout(int n, int m) {
     RecLayout L;
     size_t o = 48;  // header: int k, int flags, double xc, double gbase, int step, int state, int bytes, pad
     L.off_u = o; o += (size_t)8 * n;
-    L.off_ord = o; o += al8((size_t)n);
+    L.off_ord = o; o += al8(sizeof(ord_t) * (size_t)n);
     L.off_cpar = o; o += (size_t)8 * m;
     L.off_chat = o; o += (size_t)8 * (m + 1);
     L.off_sg = o; o += al8((size_t)m);
@@ -191,7 +193,8 @@ struct WS {
     double *chat, *val, *w, *a, *v, *r, *c, *cpar, *chatpar, *brow;
     int *zrow;
     long long *u;
-    unsigned char *pos, *ord;
+    unsigned char *pos;
+    ord_t *ord;
     signed char *sg;
     const double *Qs;  // Qrev in shared memory, leading dimension LDQ
     int LDQ, n, m, qd, lane;
@@ -946,7 +949,7 @@ __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL
     const int n = P.n, m = P.m, lane = s.lane, qd = s.qd;
     if (lane == 0) { ((int *)C)[0] = k - 1; ((int *)C)[1] = 0; ((double *)C)[1] = xlast; ((double *)C)[2] = gn; ((int *)C)[6] = 0; ((int *)C)[7] = 0; }
 #pragma unroll 1
-    for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
+    for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; ((ord_t *)(C + RL.off_ord))[e] = s.ord[e]; }
 #pragma unroll 1
     for (int j = lane; j < m; j += 32) ((double *)(C + RL.off_cpar))[j] = s.c[j];
 #pragma unroll 1
@@ -974,7 +977,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     if (BIG) { s.Qs = P.Qrev; s.LDQ = m; } else { s.Qs = s.Qsm; s.LDQ = s.LDQsm; }
     // ---- take what is needed out of the record; afterwards the record is dead ----
 #pragma unroll 1
-    for (int e = lane; e < n; e += 32) { s.u[e] = ((const long long *)(R + RL.off_u))[e]; s.ord[e] = (R + RL.off_ord)[e]; }
+    for (int e = lane; e < n; e += 32) { s.u[e] = ((const long long *)(R + RL.off_u))[e]; s.ord[e] = ((const ord_t *)(R + RL.off_ord))[e]; }
 #pragma unroll 1
     for (int j = lane; j < m; j += 32) s.cpar[j] = ((const double *)(R + RL.off_cpar))[j];
     if (qpar > 0 && k0 > 1) {
@@ -1143,7 +1146,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         } else {
             // leaf: record, closest.cc:300-312
             {
-                unsigned char *bk = P.best_key + (size_t)gwarp * n;
+                ord_t *bk = P.best_key + (size_t)gwarp * n;
                 int64_t *bu = P.best_u + (size_t)gwarp * n;
                 bool newer = true;
                 int bvld = 0;
@@ -1180,7 +1183,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
         }
         // next sibling, closest.cc:118-121
         ucur += step; step = -step - (step > 0 ? 1 : -1);
-        if (lane == 0) { s.u[kk] = ucur; if (s.ord[kk] < 255) s.ord[kk]++; }
+        if (lane == 0) { s.u[kk] = ucur; if (s.ord[kk] < ORD_MAX) s.ord[kk]++; }
         __syncwarp();
         // Wide level or little stack space left: park the rest of this loop and go down into the first child, the way
         // the depth-first order would.  The parked loop is a record like any other (it can even be donated).
@@ -1202,7 +1205,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 ((int *)C)[6] = step; ((int *)C)[7] = (pruned ? 1 : 0) | (inited << 1); ((int *)C)[8] = (int)CL.bytes;
             }
 #pragma unroll 1
-            for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; (C + RL.off_ord)[e] = s.ord[e]; }
+            for (int e = lane; e < n; e += 32) { ((long long *)(C + RL.off_u))[e] = s.u[e]; ((ord_t *)(C + RL.off_ord))[e] = s.ord[e]; }
 #pragma unroll 1
             for (int j = lane; j < m; j += 32) { ((double *)(C + RL.off_cpar))[j] = s.cpar[j]; ((signed char *)(C + RL.off_sg))[j] = s.psg[j]; }
 #pragma unroll 1
@@ -1252,7 +1255,7 @@ __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, 
     s.pos_a = bb; bb += nb; s.pos_b = bb; bb += nb;
     s.sg_a = (signed char *)bb; bb += nb; s.sg_b = (signed char *)bb; bb += nb;
     s.psg = (signed char *)bb; bb += nb;
-    s.ord = bb;
+    s.ord = (ord_t *)bb;
     s.chatpar = nullptr;
     return hist;
 }
@@ -1261,7 +1264,7 @@ __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS)
     const size_t d = 2 * (size_t)QS * LDS + 5 * M1 + 6 * (size_t)m + n + C_COUNT;
     const size_t i = 3 * M1 + (size_t)(n + 1);
     const size_t nb = (size_t)((n > m ? n : m) + 8) / 8 * 8;
-    return (d * 8 + i * 4 + 6 * nb + 15) / 16 * 16;
+    return (d * 8 + i * 4 + 7 * nb + 15) / 16 * 16;
 }
 
 // Compile-time layout of the same block for the search kernels.  MC is the size class of the problem (m <= MC): every
@@ -1277,7 +1280,7 @@ struct SL {
     static constexpr int o_ctr = o_u + MC;       // C_COUNT counters
     static constexpr int o_int = o_ctr + C_COUNT; // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
     static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
-    static constexpr size_t bytes = ((size_t)o_byte * 8 + 6 * NB + 15) / 16 * 16;
+    static constexpr size_t bytes = ((size_t)o_byte * 8 + 7 * NB + 15) / 16 * 16;
 };
 template <int MC>
 __device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
@@ -1294,7 +1297,7 @@ __device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
     unsigned char *bb = (unsigned char *)(base + L::o_byte);
     s.pos_a = bb; s.pos_b = bb + L::NB;
     s.sg_a = (signed char *)(bb + 2 * L::NB); s.sg_b = (signed char *)(bb + 3 * L::NB); s.psg = (signed char *)(bb + 4 * L::NB);
-    s.ord = bb + 5 * L::NB;
+    s.ord = (ord_t *)(bb + 5 * L::NB);
     s.chatpar = nullptr;
     return hist;
 }
@@ -1543,7 +1546,7 @@ struct BatchParams {
     unsigned int hmask;
     unsigned char *hpool;      // records handed over
     int64_t *sbest_u;          // per owner warp: the problem's shared best candidate, its key and validity
-    unsigned char *sbest_key;
+    ord_t *sbest_key;
     int *sbest_valid;
     int *helped;               // count: 1 if the problem was searched by more than one warp
 };
@@ -1585,15 +1588,15 @@ __device__ __forceinline__ void batch_merge_best(const BatchParams &BP, const Pa
     int bv = 0;
     if (lane == 0) bv = P.best_valid[gwarp];
     if (!__shfl_sync(FULLMASK, bv, 0)) return;
-    const unsigned char *mk = P.best_key + (size_t)gwarp * n;
-    unsigned char *sk = BP.sbest_key + (size_t)owner * n;
+    const ord_t *mk = P.best_key + (size_t)gwarp * n;
+    ord_t *sk = BP.sbest_key + (size_t)owner * n;
     int newer = 1;
     if (lane == 0) {
         while (atomicCAS(&oq->lock, 0, 1) != 0) __nanosleep(50);
         __threadfence();
         if (*(volatile int *)&BP.sbest_valid[owner]) {
             int cmp = 0;
-            for (int e = n - 1; e >= 0 && cmp == 0; --e) cmp = (int)mk[e] - (int)((volatile unsigned char *)sk)[e];
+            for (int e = n - 1; e >= 0 && cmp == 0; --e) cmp = (int)mk[e] - (int)((volatile ord_t *)sk)[e];
             newer = cmp >= 0;
         }
     }
@@ -1837,11 +1840,11 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
 
 // static split: collects the path keys of the published subtrees into one contiguous buffer (one copy to the host)
 __global__ void bltcu_gather_keys_kernel(const unsigned char *pool, size_t stride, size_t off_ord, const int *out_list,
-                                         int count, int n, unsigned char *keys) {
+                                         int count, int n, ord_t *keys) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count * n) return;
     const int r = i / n, e = i - r * n;
-    keys[i] = pool[(size_t)out_list[r] * stride + off_ord + (n - 1 - e)];  // top level first
+    keys[i] = ((const ord_t *)(pool + (size_t)out_list[r] * stride + off_ord))[n - 1 - e];  // top level first
 }
 __global__ void bltcu_check_kernel(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok) {
     Params P; P.n = n; P.m = m; P.lat = lat; P.con = con;
@@ -1976,7 +1979,15 @@ struct Layout {
         o_wbuf, o_next, o_arena, total;
     RecLayout RL;
 };
-// arena_recs: size of each warp's private stack in units of the largest record
+// Bytes of private stack with which a warp never has to publish a record for lack of room, whatever the tree: a
+// loop parks after every explored child once the stack is half full, so from there on each level adds one suspended
+// loop at most (batch_launch sizes its stacks the same way).
+size_t arena_worst_case(const RecLayout &RL, int n, int m) {
+    size_t b = RL.stride;
+    for (int k0 = 2; k0 <= n; ++k0) b += 2 * cont_layout(RL, m, k0).bytes;
+    return b;
+}
+// arena_recs: size of each warp's private stack in units of the largest record (0: the worst-case size above)
 int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_wpc, int want_ctas, int max_wpc, int pool_cap,
                 int arena_recs) {
     L.KQS = QS_MAX; L.LDS = LDS_C; L.LDG = m | 1; L.LDQ = LDQ_C;
@@ -1995,7 +2006,7 @@ int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_w
     while ((size_t)L.pool_cap * L.RL.stride > ((size_t)3 << 30) && L.pool_cap > 256) L.pool_cap >>= 1;
     L.wbuf_stride = align_up((size_t)2 * m * m + (size_t)2 * m * L.LDG, 32);
     L.arena_slots = 1024;
-    L.arena_bytes = align_up((size_t)arena_recs * L.RL.stride, 256);
+    L.arena_bytes = align_up(arena_recs > 0 ? (size_t)arena_recs * L.RL.stride : arena_worst_case(L.RL, n, m), 256);
     L.arena_stride = align_up(L.arena_bytes + (size_t)L.arena_slots * 4, 256);
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
@@ -2014,7 +2025,7 @@ int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_w
     L.o_out = carve((size_t)L.pool_cap * 4);
     L.o_sol = carve((size_t)n * 8 + 8);
     L.o_bu = carve((size_t)L.nwarps * n * 8);
-    L.o_bk = carve((size_t)L.nwarps * n);
+    L.o_bk = carve((size_t)L.nwarps * n * sizeof(ord_t));
     L.o_bv = carve((size_t)L.nwarps * 4);
     L.o_pool = carve((size_t)L.pool_cap * L.RL.stride);
     L.o_wbuf = carve((size_t)L.nwarps * L.wbuf_stride * 8);
@@ -2035,7 +2046,7 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
     P.nextrec = base + L.o_next;
     P.arena = base + L.o_arena; P.arena_stride = L.arena_stride; P.arena_bytes = L.arena_bytes; P.arena_slots = L.arena_slots;
     P.sol = (int64_t *)(base + L.o_sol);
-    P.best_u = (int64_t *)(base + L.o_bu); P.best_key = base + L.o_bk; P.best_valid = (int *)(base + L.o_bv);
+    P.best_u = (int64_t *)(base + L.o_bu); P.best_key = (ord_t *)(base + L.o_bk); P.best_valid = (int *)(base + L.o_bv);
     P.out_list = (int *)(base + L.o_out);
     P.warps_per_cta = L.wpc;
     P.warp_smem_doubles = L.warp_bytes / 8;
@@ -2086,6 +2097,7 @@ static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaS
 static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
                        int64_t *sol, bltcu_stats *stats) {
     const auto t_start = std::chrono::steady_clock::now();
+    if (stats) memset(stats, 0, sizeof *stats);  // every early return leaves zeros, not the caller's stack
     bltcu_opts o;
     memset(&o, 0, sizeof o);
     if (opts) o = *opts;
@@ -2233,16 +2245,16 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         std::vector<int> out(hq.out_count);
         if (hq.out_count) CK(cudaMemcpy(out.data(), P.out_list, (size_t)hq.out_count * 4, cudaMemcpyDeviceToHost));
         // order the collected subtrees by their path (DFS order) so that every rank deals the same hands
-        std::vector<std::vector<unsigned char>> keys(out.size(), std::vector<unsigned char>(n));
+        std::vector<std::vector<ord_t>> keys(out.size(), std::vector<ord_t>(n));
         if (!out.empty()) {
             // the per-warp buffers are idle between the two phases: borrow them for the gathered keys
-            unsigned char *dkeys = (unsigned char *)P.wbuf;
-            if ((size_t)out.size() * n > (size_t)nwarps * P.wbuf_stride * 8) return BLTCU_STATUS_ERROR;
+            ord_t *dkeys = (ord_t *)P.wbuf;
+            if ((size_t)out.size() * n * sizeof(ord_t) > (size_t)nwarps * P.wbuf_stride * 8) return BLTCU_STATUS_ERROR;
             const int total = (int)out.size() * n;
             bltcu_gather_keys_kernel<<<(total + 255) / 256, 256, 0, st>>>(P.pool, RL.stride, RL.off_ord, P.out_list, (int)out.size(), n, dkeys);
             CK(cudaGetLastError());
-            std::vector<unsigned char> flat((size_t)total);
-            CK(cudaMemcpyAsync(flat.data(), dkeys, (size_t)total, cudaMemcpyDeviceToHost, st));
+            std::vector<ord_t> flat((size_t)total);
+            CK(cudaMemcpyAsync(flat.data(), dkeys, (size_t)total * sizeof(ord_t), cudaMemcpyDeviceToHost, st));
             CK(cudaStreamSynchronize(st));
             launches++;
             for (size_t i = 0; i < out.size(); ++i) keys[i].assign(flat.begin() + i * n, flat.begin() + (i + 1) * n);
@@ -2274,18 +2286,20 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (!found && lp_failed && status == BLTCU_STATUS_OK) status = BLTCU_STATUS_LP_FAIL;
     // ---- result: the point found, else the last recorded candidate in DFS order (uhat) ----
     std::vector<int64_t> hsol(n, 0);
+    bool have_key = false;
+    std::vector<ord_t> best_path;  // top level first
     if (found) {
         CK(cudaMemcpy(hsol.data(), P.sol, (size_t)n * 8, cudaMemcpyDeviceToHost));
     } else {
         std::vector<int> bv(nwarps);
         CK(cudaMemcpy(bv.data(), P.best_valid, (size_t)nwarps * 4, cudaMemcpyDeviceToHost));
         int bestw = -1;
-        std::vector<unsigned char> bkey(n), key(n), keys;
+        std::vector<ord_t> bkey(n), key(n), keys;
         bool any = false;
         for (int i = 0; i < nwarps; ++i) any = any || bv[i];
         if (any) {  // all keys in one copy
             keys.resize((size_t)nwarps * n);
-            CK(cudaMemcpy(keys.data(), P.best_key, (size_t)nwarps * n, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(keys.data(), P.best_key, (size_t)nwarps * n * sizeof(ord_t), cudaMemcpyDeviceToHost));
         }
         for (int i = 0; i < nwarps; ++i) {
             if (!bv[i]) continue;
@@ -2294,6 +2308,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
             if (bestw < 0 || key >= bkey) { bestw = i; bkey = key; }
         }
         if (bestw >= 0) CK(cudaMemcpy(hsol.data(), P.best_u + (size_t)bestw * n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+        if (bestw >= 0) { have_key = true; best_path = bkey; }
     }
     if (sol) memcpy(sol, hsol.data(), (size_t)n * 8);
     if (stats) {
@@ -2308,6 +2323,8 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         stats->launches = launches;
         stats->warps = nwarps; stats->ctas = ctas;
         stats->scratch_bytes = L.total;
+        stats->best_valid = have_key ? 1 : 0;
+        if (have_key) for (int i = 0; i < n; ++i) stats->best_key[i] = best_path[i];
         stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
     }
     return status;
@@ -2357,7 +2374,7 @@ extern "C" int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, i
 
 extern "C" int bltcu_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter,
                              uint64_t *nprune) {
-    bltcu_stats st;
+    bltcu_stats st = {};
     const int rc = bltcu_closest_ex(lat, con, n, m, nullptr, sol, &st);
     if (rc == BLTCU_STATUS_OK || rc == BLTCU_STATUS_LP_FAIL) {
         if (niter) *niter = st.niter;
@@ -2399,7 +2416,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     size_t off = 0;
     auto carve = [&](size_t bytes) { size_t r = off; off = align_up(off + bytes, 256); return r; };
     const size_t o_ctl = carve((size_t)nwarps * sizeof(QCtl)), o_next = carve(64), o_tot = carve((5 + MAXD + 1) * 8);
-    const size_t o_geo = carve((size_t)nwarps * geo_stride), o_bu = carve((size_t)nwarps * n * 8), o_bk = carve((size_t)nwarps * n);
+    const size_t o_geo = carve((size_t)nwarps * geo_stride), o_bu = carve((size_t)nwarps * n * 8), o_bk = carve((size_t)nwarps * n * sizeof(ord_t));
     const size_t o_bv = carve((size_t)nwarps * 4), o_wbuf = carve((size_t)nwarps * wbuf_stride * 8);
     const size_t o_nrec = carve((size_t)nwarps * 2 * RL.stride), o_arena = carve((size_t)nwarps * arena_stride);
     const size_t o_lat = carve((size_t)mine * n * m * 8), o_con = carve((size_t)mine * 2 * m * 8), o_sol = carve((size_t)mine * n * 8);
@@ -2407,7 +2424,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     int hpool_cap = 2048;  // handed-over records in flight (power of two)
     while ((size_t)hpool_cap * RL.stride > ((size_t)1 << 30) && hpool_cap > 64) hpool_cap >>= 1;
     const size_t o_gq = carve(sizeof(QCtl)), o_hring = carve((size_t)hpool_cap * 4), o_hfring = carve((size_t)hpool_cap * 4);
-    const size_t o_hpool = carve((size_t)hpool_cap * RL.stride), o_sbu = carve((size_t)nwarps * n * 8), o_sbk = carve((size_t)nwarps * n);
+    const size_t o_hpool = carve((size_t)hpool_cap * RL.stride), o_sbu = carve((size_t)nwarps * n * 8), o_sbk = carve((size_t)nwarps * n * sizeof(ord_t));
     const size_t o_sbv = carve((size_t)nwarps * 4), o_hl = carve((size_t)mine * 4);
     if (ws_reserve(w, off)) return BLTCU_STATUS_ERROR;
     unsigned char *base = (unsigned char *)w->buf;
@@ -2421,7 +2438,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     P.wbuf = (double *)(base + o_wbuf); P.wbuf_stride = wbuf_stride;
     P.nextrec = base + o_nrec;
     P.arena = base + o_arena; P.arena_stride = arena_stride; P.arena_bytes = arena_bytes; P.arena_slots = arena_slots;
-    P.best_u = (int64_t *)(base + o_bu); P.best_key = base + o_bk; P.best_valid = (int *)(base + o_bv);
+    P.best_u = (int64_t *)(base + o_bu); P.best_key = (ord_t *)(base + o_bk); P.best_valid = (int *)(base + o_bv);
     P.no_early_exit = o.no_early_exit;
     P.warps_per_cta = wpc;
     P.warp_smem_doubles = warp_bytes / 8;
@@ -2445,7 +2462,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     BP.allow_help = allow_help && nwarps > 1;
     BP.gq = (QCtl *)(base + o_gq); BP.hring = (int *)(base + o_hring); BP.hfring = (int *)(base + o_hfring);
     BP.hmask = (unsigned int)hpool_cap - 1; BP.hpool = base + o_hpool;
-    BP.sbest_u = (int64_t *)(base + o_sbu); BP.sbest_key = base + o_sbk; BP.sbest_valid = (int *)(base + o_sbv);
+    BP.sbest_u = (int64_t *)(base + o_sbu); BP.sbest_key = (ord_t *)(base + o_sbk); BP.sbest_valid = (int *)(base + o_sbv);
     BP.helped = (int *)(base + o_hl);
     {
         QCtl hg;
@@ -2465,6 +2482,16 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     CK(cudaMemcpyAsync(base + o_con, con + (size_t)lo * 2 * m, (size_t)mine * 2 * m * 8, cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(base + o_next, 0, 64, st));
     CK(cudaMemsetAsync(base + o_tot, 0, (5 + MAXD + 1) * 8, st));
+    // a problem whose owner stops on the watchdog never writes its results: they must not be the last batch's
+    {
+        std::vector<int> err((size_t)mine, BLTCU_STATUS_ERROR);
+        CK(cudaMemcpyAsync(base + o_st, err.data(), (size_t)mine * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemsetAsync(base + o_fd, 0, (size_t)mine * 4, st));
+        CK(cudaMemsetAsync(base + o_ni, 0, (size_t)mine * 8, st));
+        CK(cudaMemsetAsync(base + o_np, 0, (size_t)mine * 8, st));
+        CK(cudaMemsetAsync(base + o_sol, 0, (size_t)mine * n * 8, st));
+        CK(cudaStreamSynchronize(st));
+    }
     CK(cudaEventRecord(w->e0, st));
     CK(launch_batch(m, ctas, wpc * 32, smem_bytes, st, BP));
     CK(cudaEventRecord(w->e1, st));
@@ -2648,7 +2675,6 @@ extern "C" const char *bltcu_version(void) { return "blt-b200 0.2 (sm_100a)"; }
 #define BLTCU_NOALLOC_WPC 1       // warps per CTA of this variant (fixed so that the per-warp stacks have a fixed size)
 #define BLTCU_NOALLOC_CTAS 148    // at most this many CTAs
 #define BLTCU_NOALLOC_POOL 256    // subtree records (power of two)
-#define BLTCU_NOALLOC_ARENA_RECS 6 // private stack of each warp, in units of the largest record
 #define BLTCU_NOALLOC_MAXDEV 64
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[BLTCU_NOALLOC_BYTES];
@@ -2715,10 +2741,16 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     }
     unsigned char *base = g_noalloc_dev[device];
     // same shared-memory and workspace layout as search_impl(), but inside the fixed array
+    // Every warp's private stack has the worst-case size of a depth-first path (one suspended loop per level), so a
+    // search never depends on the small shared pool for room; the number of CTAs is what gives way: as many as fit.
     Layout L;
-    if (make_layout(L, n, m, g_noalloc_smem[device], std::min(g_noalloc_sms[device], BLTCU_NOALLOC_CTAS), BLTCU_NOALLOC_WPC, 0,
-                    BLTCU_NOALLOC_WPC, BLTCU_NOALLOC_POOL, BLTCU_NOALLOC_ARENA_RECS))
-        return BLTCU_STATUS_ERROR;
+    int ctas_fit = std::min(g_noalloc_sms[device], BLTCU_NOALLOC_CTAS);
+    for (;; --ctas_fit) {
+        if (ctas_fit < 1 || make_layout(L, n, m, g_noalloc_smem[device], ctas_fit, BLTCU_NOALLOC_WPC, ctas_fit, BLTCU_NOALLOC_WPC,
+                                        BLTCU_NOALLOC_POOL, 0))
+            return BLTCU_STATUS_ERROR;
+        if (L.total <= (size_t)BLTCU_NOALLOC_BYTES) break;
+    }
     if (L.total > (size_t)BLTCU_NOALLOC_BYTES) {
         fprintf(stderr, "bltcu_closest_noalloc: internal layout (%zu bytes) exceeds the scratch array\n", L.total);
         return BLTCU_STATUS_ERROR;
@@ -2755,20 +2787,23 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     bltcu_noalloc_init_kernel<<<1, 256, 0, st>>>(P, deadline_ns, nwarps);  // one block: its barrier orders the clears
     CK(cudaGetLastError());
     CK(launch_search(m, ctas, wpc * 32, smem_bytes, st, P));
-    static QCtl hq;  // host copies live in static storage: no heap use on the host either
-    static int64_t h_bu[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * BLTCU_NOALLOC_MAX_DIM];
-    static unsigned char h_bk[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * BLTCU_NOALLOC_MAX_DIM];
-    static int h_bv[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC];
+    // host copies live in static storage: no heap use on the host either.  The result slot, the per-warp candidates,
+    // their keys and flags are adjacent in the layout: one copy brings them all.
+    static QCtl hq;
+    static unsigned char h_res[BLTCU_NOALLOC_CTAS * BLTCU_NOALLOC_WPC * (BLTCU_NOALLOC_MAX_DIM * (8 + sizeof(ord_t)) + 4) + 4096];
+    const size_t res_bytes = L.o_bv + (size_t)nwarps * 4 - L.o_sol;
+    if (res_bytes > sizeof h_res) return BLTCU_STATUS_ERROR;
     CK(cudaMemcpyAsync(&hq, P.q, sizeof hq, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_res, base + L.o_sol, res_bytes, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     if (hq.timed_out) fprintf(stderr, "bltcu_closest_noalloc: watchdog fired (where=%d)\n", hq.timed_out);
+    const int64_t *h_sol = (const int64_t *)h_res, *h_bu = (const int64_t *)(h_res + (L.o_bu - L.o_sol));
+    const ord_t *h_bk = (const ord_t *)(h_res + (L.o_bk - L.o_sol));
+    const int *h_bv = (const int *)(h_res + (L.o_bv - L.o_sol));
     int64_t hsol[BLTCU_NOALLOC_MAX_DIM] = {0};
     if (hq.found) {
-        CK(cudaMemcpy(hsol, P.sol, (size_t)n * 8, cudaMemcpyDeviceToHost));
+        for (int e = 0; e < n; ++e) hsol[e] = h_sol[e];
     } else {  // last recorded candidate in depth-first order, as the reference returns on UNSAT
-        CK(cudaMemcpy(h_bv, P.best_valid, (size_t)nwarps * 4, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(h_bk, P.best_key, (size_t)nwarps * n, cudaMemcpyDeviceToHost));
-        CK(cudaMemcpy(h_bu, P.best_u, (size_t)nwarps * n * 8, cudaMemcpyDeviceToHost));
         int bestw = -1;
         for (int i = 0; i < nwarps; ++i) {
             if (!h_bv[i]) continue;

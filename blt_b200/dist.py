@@ -26,19 +26,41 @@ def reduce_results(local: dict, n: int, group=None, device=None) -> dict:
                         dtype=torch.float64, device=dev)
     dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=group)
     dist.all_reduce(maxs, op=dist.ReduceOp.MAX, group=group)
-    # the solution comes from the lowest rank that found one
     rank = dist.get_rank(group)
+    sol = torch.from_numpy(np.asarray(local["sol"], dtype=np.int64).copy()).to(dev)
+
+    def _bcast(src_rank):
+        dist.broadcast(sol, src=dist.get_global_rank(group, src_rank) if group is not None else src_rank, group=group)
+
+    # SAT: the point of the lowest rank that found one.  UNSAT: the reference returns the last leaf it recorded in
+    # depth-first order (closest.cc:300-303), so the rank whose candidate has the lexicographically last path key
+    # (bltcu_stats.best_key, top level first) provides `sol`; without any recorded leaf every rank keeps zeros.
     finder = torch.tensor([rank if local["found"] else world], dtype=torch.int64, device=dev)
     dist.all_reduce(finder, op=dist.ReduceOp.MIN, group=group)
-    sol = torch.from_numpy(np.asarray(local["sol"], dtype=np.int64).copy()).to(dev)
     if int(finder.item()) < world:
-        dist.broadcast(sol, src=dist.get_global_rank(group, int(finder.item())) if group is not None else int(finder.item()),
-                       group=group)
+        _bcast(int(finder.item()))
+    else:
+        key = local.get("best_key")
+        mine = torch.full((n + 1,), -1, dtype=torch.int64, device=dev)
+        if key is not None:
+            mine[0] = 1
+            mine[1:] = torch.as_tensor(np.asarray(key, dtype=np.int64), device=dev)
+        allk = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allk, mine, group=group)
+        cands = [(tuple(int(x) for x in k[1:].tolist()), r) for r, k in enumerate(allk) if int(k[0].item()) == 1]
+        if cands:
+            _bcast(max(cands)[1])
+        else:
+            sol.zero_()
     s = sums.cpu().numpy()
     out = dict(local)
     out.update(niter=int(s[0]), nprune=int(s[1]), nodes=int(s[2]), pivots=int(s[3]), donated=int(s[4]),
                hist=s[5:].astype(np.uint64), kernel_ms=float(maxs[0].item()), rc=int(maxs[1].item()),
                found=bool(maxs[2].item() > 0), sol=sol.cpu().numpy())
+    # an LP failure in one rank's share is irrelevant once a point was found anywhere (bltcu_closest_ex does the same
+    # for its own warps); a hard error on any rank stays an error
+    if out["found"] and out["rc"] == 2:
+        out["rc"] = 0
     return out
 
 

@@ -8,6 +8,15 @@
 
 #define __BLT_VERSION "1.0.0"
 
+/* machine word size, as the reference defines it (libblt/blt.h:18-26); its C client test keys on ENVIRONMENT_64 */
+#if INTPTR_MAX == INT32_MAX
+#define ENVIRONMENT_32
+#elif INTPTR_MAX == INT64_MAX
+#define ENVIRONMENT_64
+#else
+#error "Platform is not 32 or 64-bit."
+#endif
+
 typedef int64_t int64;
 
 typedef struct Context_internal_ *CContext;     /* a problem context */
@@ -51,6 +60,12 @@ void blt_free(CContext);
  * blt_model() works on every context afterwards as after blt_check().  Returns BLT_STATUS_OK unless the arguments
  * are unusable. */
 int blt_check_batch(CContext *ctxs, int count, int *results);
+
+/* Extension, no counterpart in the reference (SolverStats stays private there, libblt/context.cc:235-238, and run_blt
+ * prints XXX for the counters, run_blt.cc:173-175): counters and phase times of the context's last blt_check().
+ * niter/nprune are SolverStats of libblt/closest.h:14-17, rank is what LLL() returned, lll_ms and search_ms are wall
+ * times of the two seams.  Any pointer may be NULL. */
+int blt_b200_last_stats(CContext ctx, uint64_t *niter, uint64_t *nprune, int *rank, double *lll_ms, double *search_ms);
 
 #ifdef __cplusplus
 }

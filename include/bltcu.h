@@ -56,6 +56,11 @@ typedef struct bltcu_stats {
     int warps, ctas;       /* launch shape */
     uint64_t scratch_bytes;/* global scratch used (per-warp stacks + subtree pool) */
     double busy_frac;      /* share of warp time spent expanding records (the rest waits for work) */
+    /* Position of the returned candidate in the reference's depth-first order when no point was found: the ordinal of
+     * the sibling taken on every level, top level first.  A caller that splits one search over several ranks returns
+     * the `sol` of the rank whose key is lexicographically last (closest.cc:300-303 keeps the last recorded leaf). */
+    uint16_t best_key[BLTCU_MAX_DIM];
+    int best_valid;        /* 1 = a leaf was recorded by this rank (best_key and sol are meaningful) */
 } bltcu_stats;
 
 /* closest(): libblt/closest.h:50-54, libblt/closest.cc:166-327.
@@ -113,7 +118,10 @@ int bltcu_infdist(const double *B, int n, int m, const int64_t *u, int k, const 
  * the library until the process exits).  n, m <= BLTCU_NOALLOC_MAX_DIM, otherwise BLT_STATUS_INPUT_ERROR and a
  * message on stderr.  The first call on a device resolves the array's device address: make it before any stream
  * capture.  All calls share the array, so calls that overlap on one GPU race: serialise them.  Pointers are host
- * pointers with the meaning they have in bltcu_closest(); found receives 1 if a lattice point was found. */
+ * pointers with the meaning they have in bltcu_closest(); found receives 1 if a lattice point was found.
+ * Each warp's record stack inside the array has the worst-case size of a depth-first path, and the number of CTAs is
+ * reduced until everything fits (about 90 at 20 x 20), so a hard instance cannot run out of room.  There is no
+ * timeout argument: the environment variable BLTCU_TIMEOUT_MS is the only watchdog of this entry point. */
 #define BLTCU_NOALLOC_MAX_DIM 20
 int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int n, int m, int device, int64_t *sol,
                           uint64_t *niter, uint64_t *nprune, int *found);

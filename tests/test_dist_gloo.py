@@ -46,6 +46,41 @@ def test_two_rank_reduction():
         assert sol == [0, 2, 4, 6, 8]  # rank 1 is the only finder: every rank ends with its point
 
 
+def _unsat_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as dist
+
+    from blt_b200.dist import reduce_results
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n = 4
+    # nobody found a point; rank 0 recorded the leaf with path (0, 2, 1, 300), rank 1 the earlier (0, 1, 7, 0); an LP
+    # failure on rank 1 must survive (no point was found)
+    keys = [np.array([0, 2, 1, 300]), np.array([0, 1, 7, 0])]
+    local = dict(rc=(2 if rank == 1 else 0), found=False, sol=np.full(n, 10 + rank, dtype=np.int64), niter=1, nprune=2, nodes=5,
+                 pivots=1, donated=0, hist=np.zeros(n + 1, dtype=np.uint64), kernel_ms=1.0, best_key=keys[rank])
+    out = reduce_results(local, n)
+    q.put((rank, list(map(int, out["sol"])), out["rc"], out["found"]))
+    dist.destroy_process_group()
+
+
+def test_two_rank_unsat_returns_the_depth_first_last_candidate():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29300 + os.getpid() % 150
+    procs = [ctx.Process(target=_unsat_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, sol, rc, found in res:
+        assert sol == [10] * 4 and rc == 2 and not found  # rank 0's leaf comes later in depth-first order
+
+
 def _batch_worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
     import torch.distributed as dist

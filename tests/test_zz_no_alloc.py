@@ -28,13 +28,14 @@ def gpu():
 def _same_as_regular(gpu, lat, con):
     ref = gpu.closest(lat, con)
     got = gpu.closest_noalloc(lat, con)
-    assert got["rc"] == ref["rc"] == 0
-    assert got["found"] == ref["found"]
+    orc = oracle.closest(lat, con)   # the CPU restatement of closest(): the parity reference of both entry points
+    assert got["rc"] == ref["rc"] == orc["rc"] == 0
+    assert got["found"] == ref["found"] == oracle.check_soln(lat, con, orc["sol"])
     if got["found"]:
         assert oracle.check_soln(lat, con, got["sol"])
     else:
-        assert got["niter"] == ref["niter"] and got["nprune"] == ref["nprune"]
-        assert (got["sol"] == ref["sol"]).all()
+        assert got["niter"] == ref["niter"] == orc["niter"] and got["nprune"] == ref["nprune"] == orc["nprune"]
+        assert (got["sol"] == ref["sol"]).all() and (got["sol"] == orc["sol"]).all()
     return got
 
 
@@ -48,6 +49,17 @@ def test_two_calls_in_a_row_match_regular_entry_point(gpu):
     third = _same_as_regular(gpu, big, con_big)
     assert not first["found"] and (first["niter"], first["nprune"]) == (third["niter"], third["nprune"])
     assert first["niter"] > 100 and second["rc"] == 0
+
+
+def test_hard_instance_at_the_size_limit(gpu):
+    """156,563 nodes at the largest admitted shape (20 x 20): every warp is busy and its stack of suspended sibling
+    loops is deep.  The stacks inside the fixed array are sized for the worst depth-first path, so the search must not
+    depend on the small shared record pool (it used to: the pool could run dry with BLT_STATUS_ERROR)."""
+    A, C = dense_bilp(20, 140, 48)
+    lat, con, _ = reduced_search_input(A, C)
+    for _ in range(2):
+        got = _same_as_regular(gpu, lat, con)
+        assert not got["found"] and got["niter"] + got["nprune"] + 2 == 156563
 
 
 def test_sat_instance_twice(gpu):
