@@ -43,6 +43,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         build_host(force=True)
     else:
         build_host()
+    build_ref_client()
     return OUT
 
 
@@ -59,6 +60,28 @@ def build_host(force: bool = False) -> str:
     subprocess.check_call(cxx + ["-o", RUN_BLT, os.path.join(HERE, "csrc", "host", "run_blt.cpp")] +
                           ["-L" + libdir, "-lblt", "-lbltcu", "-Wl,-rpath,$ORIGIN"])
     return LIBBLT
+
+
+REF_CLIENT_SRC = "/root/reference/libblt/test_blt.c"
+REF_CLIENT = os.path.join(HERE, "..", "oracle", "_ref", "test_blt")
+
+
+def build_ref_client() -> str | None:
+    """The reference's own C client test (libblt/test_blt.c) compiled UNCHANGED, from where it lies, against this
+    repository's include/blt.h + include/codes.h and linked with libblt.so.  The source is fed through stdin so that
+    its `#include "blt.h"` resolves to include/ (a file's own directory would win otherwise); only test_blt.h comes
+    from the reference tree.  Built where /root/reference exists (the GPU box runs the prebuilt binary)."""
+    if not os.path.exists(REF_CLIENT_SRC):
+        return REF_CLIENT if os.path.exists(REF_CLIENT) else None
+    os.makedirs(os.path.dirname(REF_CLIENT), exist_ok=True)
+    if os.path.exists(REF_CLIENT) and os.path.getmtime(REF_CLIENT) >= max(os.path.getmtime(LIBBLT), os.path.getmtime(REF_CLIENT_SRC)):
+        return REF_CLIENT
+    inc = os.path.join(HERE, "..", "include")
+    with open(REF_CLIENT_SRC, "rb") as f:
+        subprocess.run(["gcc", "-x", "c", "-O1", "-I", inc, "-I", os.path.dirname(REF_CLIENT_SRC), "-o", REF_CLIENT, "-",
+                        "-L" + os.path.dirname(OUT), "-lblt", "-lbltcu", "-Wl,-rpath,$ORIGIN/../../blt_b200/lib"],
+                       stdin=f, check=True)
+    return REF_CLIENT
 
 
 if __name__ == "__main__":

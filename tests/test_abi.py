@@ -63,3 +63,19 @@ def test_ctypes_mirrors_have_the_header_layout(tmp_path):
     offs = list(map(int, out[2:]))
     assert offs[:len(fields_o)] == [getattr(search.Opts, f).offset for f in fields_o]
     assert offs[len(fields_o):] == [getattr(search.Stats, f).offset for f in fields_s]
+
+
+def test_reference_c_client_compiles_against_our_headers():
+    """The reference's test_blt.c builds unchanged against include/blt.h (ENVIRONMENT_64 and all twelve prototypes);
+    it is run on the GPU box by tests/test_gpu_blt_api.py."""
+    from blt_b200 import build
+
+    if not os.path.exists(build.REF_CLIENT_SRC):
+        return
+    exe = build.build_ref_client()
+    assert exe and os.path.exists(exe)
+    import subprocess
+
+    syms = subprocess.check_output(["nm", "-D", "--undefined-only", exe], text=True)
+    for nm in ("blt_init", "blt_var", "blt_assume", "blt_check", "blt_model", "blt_free"):
+        assert nm in syms

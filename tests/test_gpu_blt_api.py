@@ -217,3 +217,16 @@ def test_zero_is_feasible_means_sat(api):
         for lo, coef, hi, const in rows:
             assert lo <= sum(c * xi for c, xi in zip(coef, x)) + const <= hi
         ctx.free()
+
+
+def test_reference_c_client_unchanged():
+    """libblt/test_blt.c, the reference's own plain-C client of blt.h, compiled unchanged against include/blt.h +
+    include/codes.h and linked with libblt.so (blt_b200.build.build_ref_client, built where /root/reference exists):
+    its three systems (one SAT with a printed model, two UNSAT parallelograms, the first needing genuine 64-bit
+    coefficients behind #ifdef ENVIRONMENT_64, test_blt.c:15-18) must pass on the GPU path."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "test_blt")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/test_blt was not built (no /root/reference at build time)")
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Tests pass!" in r.stdout

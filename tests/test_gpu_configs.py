@@ -1,0 +1,202 @@
+"""BASELINE.json configs 2, 3 and 4 on the GPU through the C ABI, against the CPU oracle.
+
+config 4  dense UNSAT n = m = 80 (closest.cc:166-327 at the largest named shape): full count parity on the 93 k-node
+          fixture, schedule independence and two-rank shares on the 1e7-node one
+config 3  Lagarias-Odlyzko subset-sum lattice, dimension 60 (tests/golden/subset_sum60.npz): SAT, model re-checked in
+          exact integers against the weights
+config 2  40 variables x 20 rows through blt_check and blt_check_batch (context.cc:139-280)
+plus a level with more than 255 visited siblings (path keys are 16 bits wide).
+"""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import context
+from tests.instances import dense_bilp, reduced_search_input, subset_sum
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def gpu():
+    import blt_b200
+    return blt_b200
+
+
+def _same_counts(got, z):
+    assert got["rc"] == 0 and not got["found"]
+    assert got["niter"] == int(z["niter"]) and got["nprune"] == int(z["nprune"]) and got["nodes"] == int(z["nodes"])
+    assert (got["hist"] == z["hist"]).all() and got["pivots"] == int(z["pivots"])
+    assert (got["sol"] == z["sol"]).all()
+
+
+# ---- config 4: n = m = 80 ---------------------------------------------------------------------------------------
+def test_dense80_full_parity(gpu, golden):
+    z = np.load(f"{golden}/bench_dense80_w75.npz")
+    assert z["lat"].shape == (80, 80)
+    _same_counts(gpu.closest(z["lat"], z["con"], timeout_ms=300000), z)
+    # one warp alone, a small grid, static splits: the same tree
+    for opts in (dict(ctas=1, warps_per_cta=1), dict(ctas=5, warps_per_cta=3), dict(split_depth=1), dict(split_depth=4),
+                 dict(split_depth=8)):
+        _same_counts(gpu.closest(z["lat"], z["con"], timeout_ms=300000, **opts), z)
+
+
+def test_dense80_large_schedules_and_shares(gpu, golden):
+    path = f"{golden}/bench_dense80_w105.npz"
+    if not os.path.exists(path):
+        pytest.skip("bench_dense80_w105.npz not generated")
+    z = np.load(path)
+    _same_counts(gpu.closest(z["lat"], z["con"], timeout_ms=600000), z)
+    for depth in (1, 4, 8):
+        _same_counts(gpu.closest(z["lat"], z["con"], split_depth=depth, timeout_ms=600000), z)
+    tot = dict(niter=0, nprune=0, nodes=0)
+    for r in range(2):
+        g = gpu.closest(z["lat"], z["con"], rank=r, world=2, split_depth=6, timeout_ms=600000)
+        assert g["rc"] == 0 and not g["found"]
+        for k in tot:
+            tot[k] += g[k]
+    assert (tot["niter"], tot["nprune"], tot["nodes"]) == (int(z["niter"]), int(z["nprune"]), int(z["nodes"]))
+
+
+# ---- config 3: subset-sum lattice, dimension 60 -------------------------------------------------------------------
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_subset_sum60(gpu, golden, seed):
+    """60 weights of 45 bits, hidden 0/1 solution with 30 ones (tests/golden/make_sat_fixtures.py).  Where the oracle
+    decides the instance within its node budget the GPU must agree with it on everything the reference pins (seeds 1
+    and 2 end at the top level's first prune, closest.cc:280-286: the reference's own incompleteness, reproduced);
+    otherwise the GPU must find a point, and the point is re-checked in exact integers against the weights."""
+    z = np.load(f"{golden}/subset_sum60.npz")
+    lat, con, xs = z[f"lat{seed}"], z[f"con{seed}"], z[f"xs{seed}"]
+    A, C, xs2 = subset_sum(60, 45, seed)
+    assert (xs == xs2).all()
+    a = A[60] // 2
+    s = int(a.astype(object) @ xs.astype(object))
+    ref = oracle.closest(lat, con, max_nodes=200000)
+    got = gpu.closest(lat, con, timeout_ms=int(os.environ.get("BLT_SS_TIMEOUT_MS", "240000")))
+    if ref["rc"] != oracle.ORACLE_TRUNCATED:
+        assert got["rc"] == ref["rc"]
+        assert got["found"] == oracle.check_soln(lat, con, ref["sol"])
+        if not got["found"]:
+            assert (got["niter"], got["nprune"]) == (ref["niter"], ref["nprune"]) and (got["sol"] == ref["sol"]).all()
+            return
+    assert got["rc"] == 0 and got["found"], f"no point found: rc {got['rc']} after {got['nodes']} nodes"
+    assert oracle.check_soln(lat, con, got["sol"]) and gpu.check_soln(lat, con, got["sol"])
+    pt = got["sol"].astype(object) @ lat.astype(object)          # the lattice point (2 x_1 .. 2 x_60 | 2 a.x)
+    x = np.array([int(v) // 2 for v in pt[:60]], dtype=object)
+    assert all(int(v) in (0, 2) for v in pt[:60]) and int(pt[60]) == 2 * s
+    assert int(a.astype(object) @ x) == s                           # a genuine subset with the target sum
+
+
+# ---- config 2: 40 variables x 20 rows through the plugin call ------------------------------------------------------
+def _bilp_context(api, A, C):
+    """run_blt's framing (libblt/run_blt.cc:151-166): variables "0".."n-1", one blt_assume per row."""
+    ctx = api.Context()
+    v = [ctx.var(str(j)) for j in range(A.shape[1])]
+    for i in range(A.shape[0]):
+        e = ctx.const(0)
+        for j in range(A.shape[1]):
+            e = e + int(A[i, j]) * v[j]
+        assert ctx.assume(int(C[i, 0]), e, int(C[i, 1])) == 0
+    return ctx
+
+
+def _check_against_oracle(ctx, rc, A, C, ref):
+    assert rc == ref["rc"]
+    st = ctx.last_stats()
+    assert st["rank"] == ref["rank"]
+    if rc == 10:
+        x = np.array([ctx.model(str(j))[1] for j in range(A.shape[1])], dtype=object)
+        z = A.astype(object) @ x
+        assert all(int(C[i, 0]) <= int(z[i]) <= int(C[i, 1]) for i in range(A.shape[0]))
+        # one warp in the reference's order finds the reference's own point with the reference's counts
+        assert list(map(int, x)) == [int(v) for v in ref["model"]]
+    assert (st["niter"], st["nprune"]) == (ref["niter"], ref["nprune"])
+
+
+@pytest.mark.parametrize("w", [1, 8, 64])
+def test_config2_through_blt_check_batch(w):
+    """A in Z^{20 x 40}, common width w, ten seeds.  The generating set has 40 vectors of
+    rank 20 (dependent-row branch of the LLL, ntl_wrapper.cc:37-52); decision, model, rank and counters of every
+    instance equal oracle.context.check's, through blt_check_batch (batched LLL + batched search)."""
+    from blt_b200 import api
+    sys_ = [dense_bilp(40, w, seed, m=20) for seed in range(10)]
+    refs = [context.check_bilp(A, C) for A, C in sys_]
+    ctxs = [_bilp_context(api, A, C) for A, C in sys_]
+    res = api.check_batch(ctxs)
+    for (A, C), ctx, rc, ref in zip(sys_, ctxs, res, refs):
+        _check_against_oracle(ctx, rc, A, C, ref)
+        ctx.free()
+
+
+def test_config2_through_blt_check():
+    """The same systems one at a time through blt_check (host LLL seam + the search kernel with all warps): decision
+    and rank equal the oracle's, the model is valid (a parallel search may return another point of the box)."""
+    from blt_b200 import api
+    for w in (1, 8, 64):
+        for seed in range(3):
+            A, C = dense_bilp(40, w, seed, m=20)
+            ref = context.check_bilp(A, C)
+            ctx = _bilp_context(api, A, C)
+            rc = ctx.check()
+            assert rc == ref["rc"] and ctx.last_stats()["rank"] == ref["rank"] == 20
+            if rc == 10:
+                x = np.array([ctx.model(str(j))[1] for j in range(40)], dtype=object)
+                z = A.astype(object) @ x
+                assert all(int(C[i, 0]) <= int(z[i]) <= int(C[i, 1]) for i in range(20))
+            else:
+                st = ctx.last_stats()
+                assert (st["niter"], st["nprune"]) == (ref["niter"], ref["nprune"])
+            ctx.free()
+
+
+def _twin(seed, w, noise):
+    """20 variables, 40 rows whose bounds sit around a common integer point (independent random bounds on 40 rows of a
+    20-dimensional lattice are refuted at the root)."""
+    rng = np.random.default_rng(1000 + seed)
+    A = rng.integers(-100, 101, size=(40, 20))
+    x0 = rng.integers(-50, 51, size=20)
+    c = A @ x0 + rng.integers(-noise, noise + 1, size=40) - w // 2
+    return A.astype(np.int64), np.stack([c, c + w], axis=1).astype(np.int64)
+
+
+def test_config2_overdetermined_twin(gpu):
+    """20 variables, 40 rows (n = 20, m = 40): bases of up to 40 rows, i.e. the large-basis path of the kernel; a mix of
+    UNSAT trees (up to 17 k nodes) and SAT instances."""
+    for seed in range(4):
+        for w, noise in ((300, 200), (400, 250), (500, 300)):
+            A, C = _twin(seed, w, noise)
+            lat, con, _ = reduced_search_input(A, C)
+            assert lat.shape == (20, 40)
+            ref = oracle.closest(lat, con)
+            got = gpu.closest(lat, con, timeout_ms=120000)
+            assert got["rc"] == ref["rc"] == 0
+            assert got["found"] == oracle.check_soln(lat, con, ref["sol"])
+            if got["found"]:
+                assert oracle.check_soln(lat, con, got["sol"])
+            else:
+                assert (got["niter"], got["nprune"], got["pivots"]) == (ref["niter"], ref["nprune"], ref["pivots"])
+                assert (got["hist"] == ref["hist"]).all() and (got["sol"] == ref["sol"]).all()
+
+
+# ---- a level with more than 255 visited siblings ------------------------------------------------------------------
+def test_wide_levels_keep_unique_path_keys(gpu):
+    """A box 300 wide over unit steps: 302 siblings at the top level, ~150 at the next.  Path keys hold 16-bit sibling
+    ordinals, so the published subtrees of a static split sort into the same order on every rank and three ranks'
+    shares add up to the oracle's counts (8-bit ordinals saturated here and dealt some subtrees twice or never)."""
+    W = 300
+    lat = np.array([[1000, 0, 0], [0, 1, 0], [0, 5, 1]], dtype=np.int64)
+    con = np.array([[200, 200 + W], [-150, -150 + W], [10, 10 + W]], dtype=np.int64)
+    ref = oracle.closest(lat, con)
+    assert ref["rc"] == 0 and ref["hist"][2] > 256 and not oracle.check_soln(lat, con, ref["sol"])
+    one = gpu.closest(lat, con)
+    assert (one["rc"], one["niter"], one["nprune"]) == (0, ref["niter"], ref["nprune"]) and (one["hist"] == ref["hist"]).all()
+    for depth in (1, 2):
+        tot = dict(niter=0, nprune=0, nodes=0)
+        for r in range(3):
+            g = gpu.closest(lat, con, rank=r, world=3, split_depth=depth)
+            assert g["rc"] == 0 and not g["found"]
+            for k in tot:
+                tot[k] += g[k]
+        assert (tot["niter"], tot["nprune"], tot["nodes"]) == (ref["niter"], ref["nprune"], ref["nodes"])

@@ -1,7 +1,10 @@
-"""The batched GPU LLL (bltcu_lll_batch) against the host implementation (bltcu_lll), which tests/test_host_layer.py pins
-bit for bit against the oracle's exact LLL: same rank, same reduced basis, same transform for every problem."""
+"""The batched GPU LLL (bltcu_lll_batch) against the oracle's exact LLL (oracle/lll.py, the restatement of
+NTL::LLL(det2, B, U), libblt/ntl_wrapper.cc:37-52) and against the host implementation (bltcu_lll): same rank, same
+reduced basis, same transform for every problem."""
 import numpy as np
 import pytest
+
+from oracle.lll import lll as oracle_lll
 
 pytestmark = pytest.mark.gpu
 
@@ -12,13 +15,17 @@ def gpu():
     return blt_b200
 
 
-def _compare(gpu, Bs, exact_u=True):
+def _compare(gpu, Bs, exact_u=True, oracle_first=10**9):
     ranks, Rs, Us, info = gpu.lll_batch(Bs)
     for i, B in enumerate(Bs):
         rk, Br, U = gpu.lll(B)
         assert ranks[i] == rk
         assert (Rs[i] == Br).all()
         assert (Us[i] == U).all()
+        if i < oracle_first:  # the CPU oracle itself, not only the product's host routine
+            ork, oB, oU = oracle_lll([[int(x) for x in row] for row in B])
+            wrap = lambda M: np.array([[((int(x) + 2**63) % 2**64) - 2**63 for x in row] for row in M], dtype=np.int64)
+            assert ranks[i] == ork and (Rs[i] == wrap(oB)).all() and (Us[i] == wrap(oU)).all()
         if exact_u:  # U * B_in = B_out in exact integers (when the entries of U fit int64, see below)
             assert (Us[i].astype(object) @ B.astype(object) == Rs[i].astype(object)).all()
     return info
