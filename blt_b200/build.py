@@ -31,14 +31,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
     from concurrent.futures import ThreadPoolExecutor
 
     os.makedirs(os.path.join(HERE, "lib", "obj"), exist_ok=True)
-    hdrs = [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h")]
+    hdrs = [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h"),
+            os.path.join(HERE, "csrc", "lp_reg.cuh")]
     newest_hdr = max(os.path.getmtime(h) for h in hdrs)
     stale = [src for src in SRC if force or not os.path.exists(_obj(src))
              or os.path.getmtime(_obj(src)) < max(os.path.getmtime(src), newest_hdr)]
     if stale:
         with ThreadPoolExecutor(max_workers=len(stale)) as ex:
             list(ex.map(lambda src: _compile(src, verbose), stale))
-    if stale or not os.path.exists(OUT):
+    if stale or not os.path.exists(OUT) or any(os.path.getmtime(_obj(src)) > os.path.getmtime(OUT) for src in SRC):
         subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", OUT] + [_obj(src) for src in SRC])
         build_host(force=True)
     else:

@@ -53,6 +53,10 @@
 #define PIV_REL 1.0e-9
 #define STALL_MAX 40
 #define MAXD BLTCU_MAX_DIM
+#ifndef BLTCU_THREADS
+#define BLTCU_THREADS 512  // threads per CTA the search kernels are compiled for (register budget = 65536 / this)
+#endif
+#define BLTCU_MAX_WPC (BLTCU_THREADS / 32)
 #define QS_MAX 24  // largest basis kept in shared memory (larger ones live in the per-warp global buffers)
 #define LDS_C 26   // row stride of the shared-memory matrices: ld_vec(QS_MAX)
 typedef unsigned short ord_t;  // sibling ordinal on one level of a path key (saturates at ORD_MAX)
@@ -203,7 +207,8 @@ struct WS {
     int failcode;  // why the last NODE_FAIL happened (diagnostics)
     unsigned int repairs;
     // the two sides of the level being expanded, and the parent's vertex
-    double *Ws_a, *Ws_b, *Wg_a, *Wg_b;
+    double *park, *Wg_a, *Wg_b;  // park: one shared-memory matrix (the side not in registers, lp_reg.cuh)
+    double *ybuf, *rbuf, *vbuf;   // shared-memory mirrors of row 0, of the leaving row, and the scaled leaving row
     const double *Qsm;  // the first QS+1 columns of Qrev in shared memory (leading dimension LDQsm); larger bases read Qrev itself
     int LDQsm;
     int *zrow_a, *zrow_b;
@@ -934,7 +939,8 @@ __device__ __forceinline__ void fail_search(const Params &P, int lane, int statu
 // The choice is a template parameter so that in the common case every access to H compiles to LDS/STS.
 template <bool BIG>
 __device__ __forceinline__ void use_side(WS &s, int side) {
-    if (BIG) { s.W = side ? s.Wg_b : s.Wg_a; s.LD = s.LDG; } else { s.W = side ? s.Ws_b : s.Ws_a; s.LD = s.LDS; }
+    static_assert(BIG, "small bases are handled by expand_reg (lp_reg.cuh)");
+    s.W = side ? s.Wg_b : s.Wg_a; s.LD = s.LDG;
     s.zrow = side ? s.zrow_b : s.zrow_a; s.pos = side ? s.pos_b : s.pos_a; s.sg = side ? s.sg_b : s.sg_a;
 }
 __device__ __forceinline__ void copy_words(void *dst, const void *src, size_t bytes, int lane) {  // bytes % 8 == 0
@@ -961,7 +967,7 @@ __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL
 // Expands record R.  Returns the number of children left for this warp in `next` (0 or 1); others went to the arena,
 // the queue or the static-split output.
 template <bool BIG>
-__device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
+__device__ __noinline__ int expand_impl(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
                       int gwarp, unsigned int *hist) {
     const int n = P.n, m = P.m, lane = s.lane;
     const RecLayout RL = rec_layout(n, m);
@@ -1230,18 +1236,59 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
     }
 }
 
-__device__ __forceinline__ int expand(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
-                                      int gwarp, unsigned int *hist) {
+// Compile-time layout of the same block for the search kernels.  MC is the size class of the problem (m <= MC): every
+// array sits at a constant offset from the warp's base, so the compiler addresses all of them off ONE register with
+// immediate offsets instead of keeping (or recomputing) thirty pointers.
+template <int MC>
+struct SL {
+    static constexpr int V = MC + 2;             // doubles per vector (even, so everything stays 16-byte aligned)
+    static constexpr int H = QS_MAX * LDS_C;     // doubles per matrix
+    static constexpr int NB = MC + 8;            // bytes per byte array
+    static constexpr int SV = QS_MAX + 2;        // doubles per small vector (ybuf rbuf vbuf)
+    static constexpr int o_vec = H;              // chat val w a v r c cpar brow al be
+    static constexpr int o_sm = o_vec + 11 * V;
+    static constexpr int o_u = o_sm + 3 * SV;
+    static constexpr int o_ctr = o_u + MC;       // C_COUNT counters
+    static constexpr int o_int = o_ctr + C_COUNT; // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
+    static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
+    static constexpr size_t bytes = ((size_t)o_byte * 8 + 7 * NB + 15) / 16 * 16;
+};
+template <int MC>
+__device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
+    typedef SL<MC> L;
+    s.park = base;
+    s.ybuf = base + L::o_sm; s.rbuf = s.ybuf + L::SV; s.vbuf = s.rbuf + L::SV;
+    double *v = base + L::o_vec;
+    s.chat = v; s.val = v + L::V; s.w = v + 2 * L::V; s.a = v + 3 * L::V; s.v = v + 4 * L::V; s.r = v + 5 * L::V;
+    s.c = v + 6 * L::V; s.cpar = v + 7 * L::V; s.brow = v + 8 * L::V; s.al = v + 9 * L::V; s.be = v + 10 * L::V;
+    s.u = (long long *)(base + L::o_u);
+    s.ctr = (unsigned long long *)(base + L::o_ctr);
+    int *ib = (int *)(base + L::o_int);
+    s.zrow_a = ib; s.zrow_b = ib + L::V; s.pzrow = ib + 2 * L::V;
+    unsigned int *hist = (unsigned int *)(ib + 3 * L::V);
+    unsigned char *bb = (unsigned char *)(base + L::o_byte);
+    s.pos_a = bb; s.pos_b = bb + L::NB;
+    s.sg_a = (signed char *)(bb + 2 * L::NB); s.sg_b = (signed char *)(bb + 3 * L::NB); s.psg = (signed char *)(bb + 4 * L::NB);
+    s.ord = (ord_t *)(bb + 5 * L::NB);
+    s.chatpar = nullptr;
+    return hist;
+}
+#include "lp_reg.cuh"
+
+template <int MC>
+__device__ __forceinline__ int expand(const Params &P, WS &s, const W<MC> &w, const unsigned char *R, int pool_slot, unsigned char *next,
+                                      Arena &A, int gwarp, unsigned int *hist) {
     const int k0 = ((const int *)R)[0];
-    if (P.m - k0 + 1 <= QS_MAX) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, hist);
+    const int qd0 = P.m - k0 + 1;
+    if (k0 > 1 && qd0 >= 2 && qd0 <= QS_MAX) return expand_reg<QS_MAX, MC>(P, w, R, pool_slot, next, A, gwarp, hist);
     return expand_impl<true>(P, s, R, pool_slot, next, A, gwarp, hist);
 }
 
 // carves the per-warp shared-memory block; returns the node histogram
 __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, int m, int QS, int LDS) {
     const int M1 = m + 1;
-    s.Ws_a = base; base += (size_t)QS * LDS;
-    s.Ws_b = base; base += (size_t)QS * LDS;
+    s.park = base; base += (size_t)QS * LDS;
+    s.ybuf = base; base += QS + 2; s.rbuf = base; base += QS + 2; s.vbuf = base; base += QS + 2;
     s.chat = base; base += M1; s.val = base; base += M1; s.w = base; base += M1; s.a = base; base += M1; s.v = base; base += M1;
     s.r = base; base += m; s.c = base; base += m; s.cpar = base; base += m; s.brow = base; base += m;
     s.al = base; base += m; s.be = base; base += m;
@@ -1261,46 +1308,12 @@ __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, 
 }
 __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS) {
     const size_t M1 = (size_t)m + 1;
-    const size_t d = 2 * (size_t)QS * LDS + 5 * M1 + 6 * (size_t)m + n + C_COUNT;
+    const size_t d = (size_t)QS * LDS + 3 * (size_t)(QS + 2) + 5 * M1 + 6 * (size_t)m + n + C_COUNT;
     const size_t i = 3 * M1 + (size_t)(n + 1);
     const size_t nb = (size_t)((n > m ? n : m) + 8) / 8 * 8;
     return (d * 8 + i * 4 + 7 * nb + 15) / 16 * 16;
 }
 
-// Compile-time layout of the same block for the search kernels.  MC is the size class of the problem (m <= MC): every
-// array sits at a constant offset from the warp's base, so the compiler addresses all of them off ONE register with
-// immediate offsets instead of keeping (or recomputing) thirty pointers.
-template <int MC>
-struct SL {
-    static constexpr int V = MC + 2;             // doubles per vector (even, so everything stays 16-byte aligned)
-    static constexpr int H = QS_MAX * LDS_C;     // doubles per matrix
-    static constexpr int NB = MC + 8;            // bytes per byte array
-    static constexpr int o_vec = 2 * H;          // chat val w a v r c cpar brow al be
-    static constexpr int o_u = o_vec + 11 * V;
-    static constexpr int o_ctr = o_u + MC;       // C_COUNT counters
-    static constexpr int o_int = o_ctr + C_COUNT; // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
-    static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
-    static constexpr size_t bytes = ((size_t)o_byte * 8 + 7 * NB + 15) / 16 * 16;
-};
-template <int MC>
-__device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
-    typedef SL<MC> L;
-    s.Ws_a = base; s.Ws_b = base + L::H;
-    double *v = base + L::o_vec;
-    s.chat = v; s.val = v + L::V; s.w = v + 2 * L::V; s.a = v + 3 * L::V; s.v = v + 4 * L::V; s.r = v + 5 * L::V;
-    s.c = v + 6 * L::V; s.cpar = v + 7 * L::V; s.brow = v + 8 * L::V; s.al = v + 9 * L::V; s.be = v + 10 * L::V;
-    s.u = (long long *)(base + L::o_u);
-    s.ctr = (unsigned long long *)(base + L::o_ctr);
-    int *ib = (int *)(base + L::o_int);
-    s.zrow_a = ib; s.zrow_b = ib + L::V; s.pzrow = ib + 2 * L::V;
-    unsigned int *hist = (unsigned int *)(ib + 3 * L::V);
-    unsigned char *bb = (unsigned char *)(base + L::o_byte);
-    s.pos_a = bb; s.pos_b = bb + L::NB;
-    s.sg_a = (signed char *)(bb + 2 * L::NB); s.sg_b = (signed char *)(bb + 3 * L::NB); s.psg = (signed char *)(bb + 4 * L::NB);
-    s.ord = (ord_t *)(bb + 5 * L::NB);
-    s.chatpar = nullptr;
-    return hist;
-}
 __host__ inline int size_class(int m) { return m <= 32 ? 32 : (m <= 64 ? 64 : 96); }
 __host__ inline size_t fixed_warp_bytes(int mc) { return mc == 32 ? SL<32>::bytes : (mc == 64 ? SL<64>::bytes : SL<96>::bytes); }
 
@@ -1308,7 +1321,7 @@ __host__ inline size_t fixed_warp_bytes(int mc) { return mc == 32 ? SL<32>::byte
 // The persistent kernel
 // ------------------------------------------------------------------------------------------------------------
 template <int MC>
-__global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
+__global__ void __launch_bounds__(BLTCU_THREADS, 1) bltcu_search_kernel(const Params P) {
     extern __shared__ __align__(16) double smem[];
     const int n = P.n, m = P.m;
     double *Qs = smem;
@@ -1334,7 +1347,10 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.repairs = 0; s.failcode = 0;
     if (lane < C_COUNT) s.ctr[lane] = 0ull;
-    use_side<false>(s, 0);
+    side_arrays(s, 0); s.W = s.park; s.LD = LDS_C;
+    W<MC> rw;  // the register engine's view of the same block (lp_reg.cuh)
+    rw.b = smem + (size_t)m * LDQ_C + (size_t)warp * (SL<MC>::bytes / 8); rw.Q = Qs;
+    rw.Wpar = s.Wpar; rw.Wg_a = s.Wg_a; rw.Wg_b = s.Wg_b; rw.tmpA = s.tmpA; rw.LDG = P.LDG; rw.lane = lane; rw.n = n; rw.m = m;
 #pragma unroll 1
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     Arena A;
@@ -1347,6 +1363,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     int nextsel = 0, have_next = 0;
     QCtl *q = P.q;
     bool am_idle = false, have_token = false;
+    unsigned int tasks = 0;
     unsigned long long t_mark = gtimer();
     for (;;) {
         const unsigned char *R = nullptr;
@@ -1399,7 +1416,13 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         // stack top was lowered above, so the children overwrite it only after it is dead
         { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_IDLE_NS] += t - t_mark; t_mark = t; }
         const int was_dive = ((const int *)R)[1] & REC_DIVE;
-        have_next = expand(P, s, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
+        // the watchdog must reach warps that never run dry: one look at the clock every 16 tasks
+        if ((++tasks & 15u) == 0) {
+            int od = 0;
+            if (lane == 0) od = overdue(q, 1) ? 1 : 0;
+            if (__shfl_sync(FULLMASK, od, 0)) break;
+        }
+        have_next = expand<MC>(P, s, rw, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
         __syncwarp();
         int burst = 0;  // the first descent just ended: its parked loops go to the waiting warps all at once
         if (was_dive && !(have_next && (((const int *)(nextbuf + (size_t)nextsel * RL.stride))[1] & REC_DIVE))) {
@@ -1572,7 +1595,7 @@ __device__ __forceinline__ unsigned int *batch_prepare(const Params &P, WS &s, A
     s.Qs = w.Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.repairs = 0; s.failcode = 0;
     if (lane < C_COUNT) s.ctr[lane] = 0ull;
-    use_side<false>(s, 0);
+    side_arrays(s, 0); s.W = s.park; s.LD = LDS_C;
 #pragma unroll 1
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     A.base = P.arena + (size_t)w.gwarp * P.arena_stride;
@@ -1618,6 +1641,10 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
     const int lane = w.lane;
     QCtl *oq = P.q;
     int nextsel = 0;
+    unsigned int tasks = 0;
+    W<MC> rw;  // the register engine's view of the warp's block (lp_reg.cuh)
+    rw.b = w.wsm; rw.Q = w.Qs;
+    rw.Wpar = s.Wpar; rw.Wg_a = s.Wg_a; rw.Wg_b = s.Wg_b; rw.tmpA = s.tmpA; rw.LDG = P.LDG; rw.lane = lane; rw.n = P.n; rw.m = P.m;
     for (;;) {
         const unsigned char *R;
         if (have_next) { R = w.nextbuf + (size_t)nextsel * RL.stride; nextsel ^= 1; have_next = 0; }
@@ -1629,7 +1656,12 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
         int ab = 0;
         if (lane == 0) ab = *(volatile int *)&oq->abort;
         if (__shfl_sync(FULLMASK, ab, 0)) break;
-        have_next = expand(P, s, R, -1, w.nextbuf + (size_t)nextsel * RL.stride, A, w.gwarp, hist);
+        if ((++tasks & 15u) == 0) {  // the watchdog must reach warps that never run dry
+            int od = 0;
+            if (lane == 0) od = overdue(oq, 1) ? 1 : 0;
+            if (__shfl_sync(FULLMASK, od, 0)) break;
+        }
+        have_next = expand<MC>(P, s, rw, R, -1, w.nextbuf + (size_t)nextsel * RL.stride, A, w.gwarp, hist);
         __syncwarp();
         if (BP.allow_help && A.acount > A.abot) {
             int dslot = -1;
@@ -1662,7 +1694,7 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
 // counters and its last recorded leaf into the owner's control block; the owner writes the problem's results when
 // its own share and all handed-over subtrees are in (pending == 0).
 template <int MC>
-__global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams BP) {
+__global__ void __launch_bounds__(BLTCU_THREADS, 1) bltcu_batch_kernel(const BatchParams BP) {
     extern __shared__ __align__(16) double smem[];
     Params P = BP.P;
     const int n = P.n, m = P.m;
@@ -2059,6 +2091,12 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
 // the kernels are compiled once per size class of m (32, 64, 96): see SL<MC>
 static cudaError_t launch_search(int m, int ctas, int threads, size_t smem, cudaStream_t st, const Params &P) {
     cudaError_t e;
+#ifdef BLTCU_FAST_BUILD  // developer builds: only the 64 size class of the search kernel is compiled
+    if ((e = cudaFuncSetAttribute(bltcu_search_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
+    if (size_class(m) != 64) return cudaErrorInvalidValue;
+    bltcu_search_kernel<64><<<ctas, threads, smem, st>>>(P);
+    return cudaGetLastError();
+#else
     switch (size_class(m)) {
     case 32:
         if ((e = cudaFuncSetAttribute(bltcu_search_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
@@ -2074,9 +2112,13 @@ static cudaError_t launch_search(int m, int ctas, int threads, size_t smem, cuda
         break;
     }
     return cudaGetLastError();
+#endif
 }
 static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaStream_t st, const BatchParams &BP) {
     cudaError_t e;
+#ifdef BLTCU_FAST_BUILD
+    return cudaErrorInvalidValue;
+#else
     switch (size_class(m)) {
     case 32:
         if ((e = cudaFuncSetAttribute(bltcu_batch_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
@@ -2092,6 +2134,7 @@ static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaS
         break;
     }
     return cudaGetLastError();
+#endif
 }
 
 static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
@@ -2107,7 +2150,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
     Layout L;
-    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 12, 16384, 64)) {
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, BLTCU_MAX_WPC, 16384, 64)) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }
@@ -2393,7 +2436,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     const int KQS = QS_MAX, LDS = LDS_C, LDG = m | 1, LDQ = LDQ_C;
     const size_t warp_bytes = fixed_warp_bytes(size_class(m));
     const size_t per_warp = align_up((size_t)m * LDQ * 8 + warp_bytes, 16);
-    int wpc = (int)std::min<size_t>(12, w->smem_optin / per_warp);
+    int wpc = (int)std::min<size_t>(BLTCU_MAX_WPC, w->smem_optin / per_warp);
     if (o.warps_per_cta > 0 && o.warps_per_cta < wpc) wpc = o.warps_per_cta;
     if (wpc < 1) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);

@@ -35,7 +35,7 @@ def lib() -> ctypes.CDLL:
     """Loads blt_b200/lib/libbltcu.so.  Fails loudly when the CUDA library has not been built."""
     global _LIB
     if _LIB is None:
-        path = os.path.join(_HERE, "lib", "libbltcu.so")
+        path = os.environ.get("BLTCU_LIB") or os.path.join(_HERE, "lib", "libbltcu.so")  # BLTCU_LIB: developer builds
         if not os.path.exists(path):
             raise RuntimeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                                "(nvcc, sm_100a).  blt_b200 has no CPU fallback.")

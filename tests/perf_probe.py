@@ -20,4 +20,4 @@ for wpc in wpcs:
     busy_us = r["kernel_ms"] * 1e3 * r["warps"] * r["busy_frac"] / r["nodes"]
     print(f"wpc {wpc:2d} rc {r['rc']} nodes {r['nodes']} warps {r['warps']} ms {r['kernel_ms']:.2f} "
           f"Mnodes/s {r['nodes'] / r['kernel_ms'] / 1e3:.2f} busy {r['busy_frac']:.2f} busy-us/node/warp {busy_us:.1f} "
-          f"donated {r['donated']}", flush=True)
+          f"donated {r['donated']} counts_ok {r['nodes'] == int(z['nodes']) and r['pivots'] == int(z['pivots']) and (r['sol'] == z['sol']).all()}", flush=True)
