@@ -41,6 +41,7 @@
 #include <algorithm>
 #include <chrono>
 #include <mutex>
+#include <thread>
 #include <vector>
 
 #include "../../include/bltcu.h"
@@ -53,10 +54,6 @@
 #define PIV_REL 1.0e-9
 #define STALL_MAX 40
 #define MAXD BLTCU_MAX_DIM
-#ifndef BLTCU_THREADS
-#define BLTCU_THREADS 512  // threads per CTA the search kernels are compiled for (register budget = 65536 / this)
-#endif
-#define BLTCU_MAX_WPC (BLTCU_THREADS / 32)
 #define QS_MAX 24  // largest basis kept in shared memory (larger ones live in the per-warp global buffers)
 #define LDS_C 26   // row stride of the shared-memory matrices: ld_vec(QS_MAX)
 typedef unsigned short ord_t;  // sibling ordinal on one level of a path key (saturates at ORD_MAX)
@@ -207,8 +204,7 @@ struct WS {
     int failcode;  // why the last NODE_FAIL happened (diagnostics)
     unsigned int repairs;
     // the two sides of the level being expanded, and the parent's vertex
-    double *park, *Wg_a, *Wg_b;  // park: one shared-memory matrix (the side not in registers, lp_reg.cuh)
-    double *ybuf, *rbuf, *vbuf;   // shared-memory mirrors of row 0, of the leaving row, and the scaled leaving row
+    double *Ws_a, *Ws_b, *Wg_a, *Wg_b;
     const double *Qsm;  // the first QS+1 columns of Qrev in shared memory (leading dimension LDQsm); larger bases read Qrev itself
     int LDQsm;
     int *zrow_a, *zrow_b;
@@ -939,8 +935,7 @@ __device__ __forceinline__ void fail_search(const Params &P, int lane, int statu
 // The choice is a template parameter so that in the common case every access to H compiles to LDS/STS.
 template <bool BIG>
 __device__ __forceinline__ void use_side(WS &s, int side) {
-    static_assert(BIG, "small bases are handled by expand_reg (lp_reg.cuh)");
-    s.W = side ? s.Wg_b : s.Wg_a; s.LD = s.LDG;
+    if (BIG) { s.W = side ? s.Wg_b : s.Wg_a; s.LD = s.LDG; } else { s.W = side ? s.Ws_b : s.Ws_a; s.LD = s.LDS; }
     s.zrow = side ? s.zrow_b : s.zrow_a; s.pos = side ? s.pos_b : s.pos_a; s.sg = side ? s.sg_b : s.sg_a;
 }
 __device__ __forceinline__ void copy_words(void *dst, const void *src, size_t bytes, int lane) {  // bytes % 8 == 0
@@ -967,7 +962,7 @@ __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL
 // Expands record R.  Returns the number of children left for this warp in `next` (0 or 1); others went to the arena,
 // the queue or the static-split output.
 template <bool BIG>
-__device__ __noinline__ int expand_impl(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
+__device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
                       int gwarp, unsigned int *hist) {
     const int n = P.n, m = P.m, lane = s.lane;
     const RecLayout RL = rec_layout(n, m);
@@ -1236,59 +1231,18 @@ __device__ __noinline__ int expand_impl(const Params &P, WS &s, const unsigned c
     }
 }
 
-// Compile-time layout of the same block for the search kernels.  MC is the size class of the problem (m <= MC): every
-// array sits at a constant offset from the warp's base, so the compiler addresses all of them off ONE register with
-// immediate offsets instead of keeping (or recomputing) thirty pointers.
-template <int MC>
-struct SL {
-    static constexpr int V = MC + 2;             // doubles per vector (even, so everything stays 16-byte aligned)
-    static constexpr int H = QS_MAX * LDS_C;     // doubles per matrix
-    static constexpr int NB = MC + 8;            // bytes per byte array
-    static constexpr int SV = QS_MAX + 2;        // doubles per small vector (ybuf rbuf vbuf)
-    static constexpr int o_vec = H;              // chat val w a v r c cpar brow al be
-    static constexpr int o_sm = o_vec + 11 * V;
-    static constexpr int o_u = o_sm + 3 * SV;
-    static constexpr int o_ctr = o_u + MC;       // C_COUNT counters
-    static constexpr int o_int = o_ctr + C_COUNT; // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
-    static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
-    static constexpr size_t bytes = ((size_t)o_byte * 8 + 7 * NB + 15) / 16 * 16;
-};
-template <int MC>
-__device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
-    typedef SL<MC> L;
-    s.park = base;
-    s.ybuf = base + L::o_sm; s.rbuf = s.ybuf + L::SV; s.vbuf = s.rbuf + L::SV;
-    double *v = base + L::o_vec;
-    s.chat = v; s.val = v + L::V; s.w = v + 2 * L::V; s.a = v + 3 * L::V; s.v = v + 4 * L::V; s.r = v + 5 * L::V;
-    s.c = v + 6 * L::V; s.cpar = v + 7 * L::V; s.brow = v + 8 * L::V; s.al = v + 9 * L::V; s.be = v + 10 * L::V;
-    s.u = (long long *)(base + L::o_u);
-    s.ctr = (unsigned long long *)(base + L::o_ctr);
-    int *ib = (int *)(base + L::o_int);
-    s.zrow_a = ib; s.zrow_b = ib + L::V; s.pzrow = ib + 2 * L::V;
-    unsigned int *hist = (unsigned int *)(ib + 3 * L::V);
-    unsigned char *bb = (unsigned char *)(base + L::o_byte);
-    s.pos_a = bb; s.pos_b = bb + L::NB;
-    s.sg_a = (signed char *)(bb + 2 * L::NB); s.sg_b = (signed char *)(bb + 3 * L::NB); s.psg = (signed char *)(bb + 4 * L::NB);
-    s.ord = (ord_t *)(bb + 5 * L::NB);
-    s.chatpar = nullptr;
-    return hist;
-}
-#include "lp_reg.cuh"
-
-template <int MC>
-__device__ __forceinline__ int expand(const Params &P, WS &s, const W<MC> &w, const unsigned char *R, int pool_slot, unsigned char *next,
-                                      Arena &A, int gwarp, unsigned int *hist) {
+__device__ __forceinline__ int expand(const Params &P, WS &s, const unsigned char *R, int pool_slot, unsigned char *next, Arena &A,
+                                      int gwarp, unsigned int *hist) {
     const int k0 = ((const int *)R)[0];
-    const int qd0 = P.m - k0 + 1;
-    if (k0 > 1 && qd0 >= 2 && qd0 <= QS_MAX) return expand_reg<QS_MAX, MC>(P, w, R, pool_slot, next, A, gwarp, hist);
+    if (P.m - k0 + 1 <= QS_MAX) return expand_impl<false>(P, s, R, pool_slot, next, A, gwarp, hist);
     return expand_impl<true>(P, s, R, pool_slot, next, A, gwarp, hist);
 }
 
 // carves the per-warp shared-memory block; returns the node histogram
 __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, int m, int QS, int LDS) {
     const int M1 = m + 1;
-    s.park = base; base += (size_t)QS * LDS;
-    s.ybuf = base; base += QS + 2; s.rbuf = base; base += QS + 2; s.vbuf = base; base += QS + 2;
+    s.Ws_a = base; base += (size_t)QS * LDS;
+    s.Ws_b = base; base += (size_t)QS * LDS;
     s.chat = base; base += M1; s.val = base; base += M1; s.w = base; base += M1; s.a = base; base += M1; s.v = base; base += M1;
     s.r = base; base += m; s.c = base; base += m; s.cpar = base; base += m; s.brow = base; base += m;
     s.al = base; base += m; s.be = base; base += m;
@@ -1308,12 +1262,46 @@ __device__ __forceinline__ unsigned int *carve_warp(WS &s, double *base, int n, 
 }
 __host__ __device__ inline size_t warp_smem_bytes(int n, int m, int QS, int LDS) {
     const size_t M1 = (size_t)m + 1;
-    const size_t d = (size_t)QS * LDS + 3 * (size_t)(QS + 2) + 5 * M1 + 6 * (size_t)m + n + C_COUNT;
+    const size_t d = 2 * (size_t)QS * LDS + 5 * M1 + 6 * (size_t)m + n + C_COUNT;
     const size_t i = 3 * M1 + (size_t)(n + 1);
     const size_t nb = (size_t)((n > m ? n : m) + 8) / 8 * 8;
     return (d * 8 + i * 4 + 7 * nb + 15) / 16 * 16;
 }
 
+// Compile-time layout of the same block for the search kernels.  MC is the size class of the problem (m <= MC): every
+// array sits at a constant offset from the warp's base, so the compiler addresses all of them off ONE register with
+// immediate offsets instead of keeping (or recomputing) thirty pointers.
+template <int MC>
+struct SL {
+    static constexpr int V = MC + 2;             // doubles per vector (even, so everything stays 16-byte aligned)
+    static constexpr int H = QS_MAX * LDS_C;     // doubles per matrix
+    static constexpr int NB = MC + 8;            // bytes per byte array
+    static constexpr int o_vec = 2 * H;          // chat val w a v r c cpar brow al be
+    static constexpr int o_u = o_vec + 11 * V;
+    static constexpr int o_ctr = o_u + MC;       // C_COUNT counters
+    static constexpr int o_int = o_ctr + C_COUNT; // zrow_a zrow_b pzrow hist, V ints each = 2 V doubles
+    static constexpr int o_byte = o_int + 2 * V; // pos_a pos_b sg_a sg_b psg ord
+    static constexpr size_t bytes = ((size_t)o_byte * 8 + 7 * NB + 15) / 16 * 16;
+};
+template <int MC>
+__device__ __forceinline__ unsigned int *carve_fixed(WS &s, double *base) {
+    typedef SL<MC> L;
+    s.Ws_a = base; s.Ws_b = base + L::H;
+    double *v = base + L::o_vec;
+    s.chat = v; s.val = v + L::V; s.w = v + 2 * L::V; s.a = v + 3 * L::V; s.v = v + 4 * L::V; s.r = v + 5 * L::V;
+    s.c = v + 6 * L::V; s.cpar = v + 7 * L::V; s.brow = v + 8 * L::V; s.al = v + 9 * L::V; s.be = v + 10 * L::V;
+    s.u = (long long *)(base + L::o_u);
+    s.ctr = (unsigned long long *)(base + L::o_ctr);
+    int *ib = (int *)(base + L::o_int);
+    s.zrow_a = ib; s.zrow_b = ib + L::V; s.pzrow = ib + 2 * L::V;
+    unsigned int *hist = (unsigned int *)(ib + 3 * L::V);
+    unsigned char *bb = (unsigned char *)(base + L::o_byte);
+    s.pos_a = bb; s.pos_b = bb + L::NB;
+    s.sg_a = (signed char *)(bb + 2 * L::NB); s.sg_b = (signed char *)(bb + 3 * L::NB); s.psg = (signed char *)(bb + 4 * L::NB);
+    s.ord = (ord_t *)(bb + 5 * L::NB);
+    s.chatpar = nullptr;
+    return hist;
+}
 __host__ inline int size_class(int m) { return m <= 32 ? 32 : (m <= 64 ? 64 : 96); }
 __host__ inline size_t fixed_warp_bytes(int mc) { return mc == 32 ? SL<32>::bytes : (mc == 64 ? SL<64>::bytes : SL<96>::bytes); }
 
@@ -1321,7 +1309,7 @@ __host__ inline size_t fixed_warp_bytes(int mc) { return mc == 32 ? SL<32>::byte
 // The persistent kernel
 // ------------------------------------------------------------------------------------------------------------
 template <int MC>
-__global__ void __launch_bounds__(BLTCU_THREADS, 1) bltcu_search_kernel(const Params P) {
+__global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
     extern __shared__ __align__(16) double smem[];
     const int n = P.n, m = P.m;
     double *Qs = smem;
@@ -1347,10 +1335,7 @@ __global__ void __launch_bounds__(BLTCU_THREADS, 1) bltcu_search_kernel(const Pa
     s.Qs = Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.repairs = 0; s.failcode = 0;
     if (lane < C_COUNT) s.ctr[lane] = 0ull;
-    side_arrays(s, 0); s.W = s.park; s.LD = LDS_C;
-    W<MC> rw;  // the register engine's view of the same block (lp_reg.cuh)
-    rw.b = smem + (size_t)m * LDQ_C + (size_t)warp * (SL<MC>::bytes / 8); rw.Q = Qs;
-    rw.Wpar = s.Wpar; rw.Wg_a = s.Wg_a; rw.Wg_b = s.Wg_b; rw.tmpA = s.tmpA; rw.LDG = P.LDG; rw.lane = lane; rw.n = n; rw.m = m;
+    use_side<false>(s, 0);
 #pragma unroll 1
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     Arena A;
@@ -1422,7 +1407,7 @@ __global__ void __launch_bounds__(BLTCU_THREADS, 1) bltcu_search_kernel(const Pa
             if (lane == 0) od = overdue(q, 1) ? 1 : 0;
             if (__shfl_sync(FULLMASK, od, 0)) break;
         }
-        have_next = expand<MC>(P, s, rw, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
+        have_next = expand(P, s, R, slot, nextbuf + (size_t)nextsel * RL.stride, A, gwarp, hist);
         __syncwarp();
         int burst = 0;  // the first descent just ended: its parked loops go to the waiting warps all at once
         if (was_dive && !(have_next && (((const int *)(nextbuf + (size_t)nextsel * RL.stride))[1] & REC_DIVE))) {
@@ -1595,7 +1580,7 @@ __device__ __forceinline__ unsigned int *batch_prepare(const Params &P, WS &s, A
     s.Qs = w.Qs; s.LDQ = LDQ_C; s.n = n; s.m = m; s.qd = 0; s.lane = lane;
     s.repairs = 0; s.failcode = 0;
     if (lane < C_COUNT) s.ctr[lane] = 0ull;
-    side_arrays(s, 0); s.W = s.park; s.LD = LDS_C;
+    use_side<false>(s, 0);
 #pragma unroll 1
     for (int e = lane; e <= n; e += 32) hist[e] = 0;
     A.base = P.arena + (size_t)w.gwarp * P.arena_stride;
@@ -1642,9 +1627,6 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
     QCtl *oq = P.q;
     int nextsel = 0;
     unsigned int tasks = 0;
-    W<MC> rw;  // the register engine's view of the warp's block (lp_reg.cuh)
-    rw.b = w.wsm; rw.Q = w.Qs;
-    rw.Wpar = s.Wpar; rw.Wg_a = s.Wg_a; rw.Wg_b = s.Wg_b; rw.tmpA = s.tmpA; rw.LDG = P.LDG; rw.lane = lane; rw.n = P.n; rw.m = P.m;
     for (;;) {
         const unsigned char *R;
         if (have_next) { R = w.nextbuf + (size_t)nextsel * RL.stride; nextsel ^= 1; have_next = 0; }
@@ -1661,7 +1643,7 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
             if (lane == 0) od = overdue(oq, 1) ? 1 : 0;
             if (__shfl_sync(FULLMASK, od, 0)) break;
         }
-        have_next = expand<MC>(P, s, rw, R, -1, w.nextbuf + (size_t)nextsel * RL.stride, A, w.gwarp, hist);
+        have_next = expand(P, s, R, -1, w.nextbuf + (size_t)nextsel * RL.stride, A, w.gwarp, hist);
         __syncwarp();
         if (BP.allow_help && A.acount > A.abot) {
             int dslot = -1;
@@ -1694,7 +1676,7 @@ __device__ __forceinline__ void batch_run(const BatchParams &BP, const Params &P
 // counters and its last recorded leaf into the owner's control block; the owner writes the problem's results when
 // its own share and all handed-over subtrees are in (pending == 0).
 template <int MC>
-__global__ void __launch_bounds__(BLTCU_THREADS, 1) bltcu_batch_kernel(const BatchParams BP) {
+__global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams BP) {
     extern __shared__ __align__(16) double smem[];
     Params P = BP.P;
     const int n = P.n, m = P.m;
@@ -1974,13 +1956,16 @@ struct DevWs {  // cached per device, grow-only
     size_t cap = 0;
     int64_t *d_in = nullptr;  // staging for host lat/con
     size_t in_cap = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;  // stream2: small copies beside a running search kernel
+    int *pin = nullptr;                                // page-locked staging for them
     cudaEvent_t e0 = nullptr, e1 = nullptr;
+    std::mutex mu;  // one call at a time per device; different devices run concurrently (opts.gpus)
 };
 std::mutex g_mu;
 std::vector<DevWs *> g_ws;
 
 int get_ws(int device, DevWs **out) {
+    std::lock_guard<std::mutex> lk(g_mu);  // guards the list only
     for (auto *w : g_ws) if (w->device == device) { CK(cudaSetDevice(device)); *out = w; return 0; }
     CK(cudaSetDevice(device));
     DevWs *w = new DevWs();
@@ -1989,6 +1974,8 @@ int get_ws(int device, DevWs **out) {
     CK(cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, device)); w->sms = v;
     CK(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)); w->smem_optin = (size_t)v;
     CK(cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&w->stream2, cudaStreamNonBlocking));
+    CK(cudaHostAlloc((void **)&w->pin, 64, cudaHostAllocDefault));
     CK(cudaEventCreate(&w->e0)); CK(cudaEventCreate(&w->e1));
     g_ws.push_back(w);
     *out = w;
@@ -2091,12 +2078,6 @@ void fill_params(Params &P, const Layout &L, unsigned char *base, int n, int m) 
 // the kernels are compiled once per size class of m (32, 64, 96): see SL<MC>
 static cudaError_t launch_search(int m, int ctas, int threads, size_t smem, cudaStream_t st, const Params &P) {
     cudaError_t e;
-#ifdef BLTCU_FAST_BUILD  // developer builds: only the 64 size class of the search kernel is compiled
-    if ((e = cudaFuncSetAttribute(bltcu_search_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
-    if (size_class(m) != 64) return cudaErrorInvalidValue;
-    bltcu_search_kernel<64><<<ctas, threads, smem, st>>>(P);
-    return cudaGetLastError();
-#else
     switch (size_class(m)) {
     case 32:
         if ((e = cudaFuncSetAttribute(bltcu_search_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
@@ -2112,13 +2093,9 @@ static cudaError_t launch_search(int m, int ctas, int threads, size_t smem, cuda
         break;
     }
     return cudaGetLastError();
-#endif
 }
 static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaStream_t st, const BatchParams &BP) {
     cudaError_t e;
-#ifdef BLTCU_FAST_BUILD
-    return cudaErrorInvalidValue;
-#else
     switch (size_class(m)) {
     case 32:
         if ((e = cudaFuncSetAttribute(bltcu_batch_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) != cudaSuccess) return e;
@@ -2134,7 +2111,6 @@ static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaS
         break;
     }
     return cudaGetLastError();
-#endif
 }
 
 static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
@@ -2150,7 +2126,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     if (o.split_depth > n - 2) o.split_depth = std::max(0, n - 2);
 
     Layout L;
-    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, BLTCU_MAX_WPC, 16384, 64)) {
+    if (make_layout(L, n, m, w->smem_optin, w->sms, o.warps_per_cta, o.ctas, 12, 16384, 64)) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
         return BLTCU_STATUS_ERROR;
     }
@@ -2168,6 +2144,10 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     P.donate_min_level = o.donate_min_level > 0 ? std::max(2, o.donate_min_level) : std::min(6, std::max(2, n / 3));
     P.no_early_exit = o.no_early_exit;
     if (o.eager > 0) P.eager_max = o.eager;
+    // The stop word of a multi-rank search is plain host memory shared by the ranks' host threads (or processes).  GPUs
+    // never touch it: while its kernel runs, each rank's host thread looks at its own device's `found` through a second
+    // stream, raises the word when it is set, and writes `abort` into its device when somebody else raised the word.
+    volatile int *host_stop = (world > 1 && o.stop_flag && !o.no_early_exit) ? (volatile int *)o.stop_flag : nullptr;
 
     int launches = 0;
     const size_t setup_smem = warp_smem_bytes(n, m, 0, 1);
@@ -2231,8 +2211,25 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventRecord(w->e0, st));
         CK(launch_search(m, ctas, wpc * 32, smem_bytes, st, P));
         CK(cudaEventRecord(w->e1, st));
+        if (host_stop) {
+            bool told = false;
+            while (cudaEventQuery(w->e1) == cudaErrorNotReady) {
+                CK(cudaMemcpyAsync(w->pin, &P.q->found, 4, cudaMemcpyDeviceToHost, w->stream2));
+                CK(cudaStreamSynchronize(w->stream2));
+                if (w->pin[0]) *host_stop = 1;
+                if (*host_stop && !told) {
+                    w->pin[1] = 1;
+                    CK(cudaMemcpyAsync(&P.q->abort, w->pin + 1, 4, cudaMemcpyHostToDevice, w->stream2));
+                    CK(cudaStreamSynchronize(w->stream2));
+                    told = true;
+                }
+                std::this_thread::sleep_for(std::chrono::microseconds(100));
+            }
+            (void)cudaGetLastError();
+        }
         CK(cudaMemcpyAsync(&hq, P.q, sizeof hq, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
+        if (host_stop && hq.found) *host_stop = 1;
         float ms = 0.f;
         CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
         kernel_ms += ms;
@@ -2307,7 +2304,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         std::sort(idx.begin(), idx.end(), [&](int a, int b) { return keys[a] < keys[b]; });
         initial.clear();
         for (size_t i = 0; i < idx.size(); ++i) if ((int)(i % world) == rank) initial.push_back(out[idx[i]]);
-        const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0));
+        const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0)) || (host_stop && *host_stop);
         if (!stop && !initial.empty()) {
             if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
             if (found) { hq.found = 1; CK(cudaMemcpyAsync(P.q, &hq, sizeof hq, cudaMemcpyHostToDevice, st)); }
@@ -2366,6 +2363,8 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         stats->launches = launches;
         stats->warps = nwarps; stats->ctas = ctas;
         stats->scratch_bytes = L.total;
+        stats->stopped = (!found && host_stop && *host_stop) ? 1 : 0;
+        stats->gpus = 1;
         stats->best_valid = have_key ? 1 : 0;
         if (have_key) for (int i = 0; i < n; ++i) stats->best_key[i] = best_path[i];
         stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_start).count();
@@ -2386,21 +2385,18 @@ extern "C" int bltcu_closest_dev(const int64_t *d_lat, const int64_t *d_con, int
                                  int64_t *sol, bltcu_stats *stats) {
     const int v = validate(n, m);
     if (v != BLTCU_STATUS_OK) return v;
-    std::lock_guard<std::mutex> lk(g_mu);
     DevWs *w = nullptr;
     if (get_ws(opts ? opts->device : 0, &w)) return BLTCU_STATUS_ERROR;
+    std::lock_guard<std::mutex> lk(w->mu);
     return search_impl(w, d_lat, d_con, n, m, opts, sol, stats);
 }
 
-extern "C" int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts *opts,
-                                int64_t *sol, bltcu_stats *stats) {
-    const int v = validate(n, m);
-    if (v != BLTCU_STATUS_OK) return v;
-    if (!lat || !con) return BLTCU_STATUS_INPUT_ERROR;
+static int closest_one_device(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts *opts, int64_t *sol,
+                              bltcu_stats *stats) {
     const auto t0 = std::chrono::steady_clock::now();
-    std::lock_guard<std::mutex> lk(g_mu);
     DevWs *w = nullptr;
     if (get_ws(opts ? opts->device : 0, &w)) return BLTCU_STATUS_ERROR;
+    std::lock_guard<std::mutex> lk(w->mu);
     const size_t need = ((size_t)n * m + 2 * (size_t)m) * 8;
     if (need > w->in_cap) {
         if (w->d_in) CK(cudaFree(w->d_in));
@@ -2413,6 +2409,79 @@ extern "C" int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, i
     const int rc = search_impl(w, w->d_in, w->d_in + (size_t)n * m, n, m, opts, sol, stats);
     if (stats) stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     return rc;
+}
+
+// One search on several GPUs of this process (opts.gpus / BLT_GPUS): a host thread per device, each with the share
+// i % gpus of the deterministic static split (the same code path as one process per GPU with opts.rank / opts.world),
+// one stop word in host memory for the first point found (see search_impl), results merged here.  No collective: the ranks
+// exchange nothing but that word.
+static int closest_multi_device(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts &base, int gpus, int64_t *sol,
+                                bltcu_stats *stats) {
+    const auto t0 = std::chrono::steady_clock::now();
+    int flag_word = 0;
+    int *flag = &flag_word;
+    std::vector<bltcu_stats> st((size_t)gpus);
+    std::vector<std::vector<int64_t>> sols((size_t)gpus, std::vector<int64_t>((size_t)n, 0));
+    std::vector<int> rcs((size_t)gpus, BLTCU_STATUS_ERROR);
+    std::vector<std::thread> th;
+    for (int r = 0; r < gpus; ++r)
+        th.emplace_back([&, r]() {
+            bltcu_opts o = base;
+            o.device = base.device + r; o.rank = r; o.world = gpus; o.gpus = 1; o.stop_flag = flag;
+            rcs[r] = closest_one_device(lat, con, n, m, &o, sols[r].data(), &st[r]);
+        });
+    for (auto &t : th) t.join();
+    int rc = BLTCU_STATUS_OK, finder = -1, last = -1;
+    bool lp_fail = false;
+    for (int r = 0; r < gpus; ++r) {
+        if (rcs[r] == BLTCU_STATUS_ERROR || rcs[r] == BLTCU_STATUS_INPUT_ERROR) rc = rcs[r];
+        if (rcs[r] == BLTCU_STATUS_LP_FAIL) lp_fail = true;
+        if (st[r].found && finder < 0) finder = r;
+        // the reference returns the last leaf it recorded in depth-first order: the lexicographically last path key
+        if (st[r].best_valid && (last < 0 || !std::lexicographical_compare(st[r].best_key, st[r].best_key + n, st[last].best_key, st[last].best_key + n))) last = r;
+    }
+    if (rc == BLTCU_STATUS_OK && finder < 0 && lp_fail) rc = BLTCU_STATUS_LP_FAIL;
+    const int src = finder >= 0 ? finder : last;
+    if (sol) for (int e = 0; e < n; ++e) sol[e] = src >= 0 ? sols[src][e] : 0;
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        double busy = 0.0;
+        for (int r = 0; r < gpus; ++r) {
+            stats->niter += st[r].niter; stats->nprune += st[r].nprune; stats->nodes += st[r].nodes; stats->pivots += st[r].pivots;
+            stats->quick_prunes += st[r].quick_prunes; stats->refactors += st[r].refactors; stats->cold_starts += st[r].cold_starts;
+            stats->donated += st[r].donated; stats->launches += st[r].launches; stats->warps += st[r].warps; stats->ctas += st[r].ctas;
+            stats->scratch_bytes += st[r].scratch_bytes;
+            for (int i = 0; i <= n; ++i) stats->hist[i] += st[r].hist[i];
+            stats->kernel_ms = std::max(stats->kernel_ms, st[r].kernel_ms);
+            busy += st[r].busy_frac;
+        }
+        stats->busy_frac = busy / gpus;
+        stats->found = finder >= 0 ? 1 : 0;
+        stats->gpus = gpus;
+        if (finder < 0 && last >= 0) { stats->best_valid = 1; memcpy(stats->best_key, st[last].best_key, sizeof stats->best_key); }
+        stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return rc;
+}
+
+extern "C" int bltcu_closest_ex(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts *opts,
+                                int64_t *sol, bltcu_stats *stats) {
+    const int v = validate(n, m);
+    if (v != BLTCU_STATUS_OK) return v;
+    if (!lat || !con) return BLTCU_STATUS_INPUT_ERROR;
+    bltcu_opts o;
+    memset(&o, 0, sizeof o);
+    if (opts) o = *opts;
+    int gpus = o.gpus;
+    if (gpus <= 0) { const char *e = getenv("BLT_GPUS"); gpus = e ? atoi(e) : 1; }
+    if (o.world > 1) gpus = 1;  // the caller already runs one rank per GPU
+    if (gpus > 1) {
+        int have = 0;
+        CK(cudaGetDeviceCount(&have));
+        gpus = std::min(gpus, have - o.device);
+    }
+    if (gpus > 1 && n >= 4) return closest_multi_device(lat, con, n, m, o, gpus, sol, stats);
+    return closest_one_device(lat, con, n, m, &o, sol, stats);
 }
 
 extern "C" int bltcu_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter,
@@ -2436,7 +2505,7 @@ static int batch_launch(DevWs *w, const int64_t *lat, const int64_t *con, int mi
     const int KQS = QS_MAX, LDS = LDS_C, LDG = m | 1, LDQ = LDQ_C;
     const size_t warp_bytes = fixed_warp_bytes(size_class(m));
     const size_t per_warp = align_up((size_t)m * LDQ * 8 + warp_bytes, 16);
-    int wpc = (int)std::min<size_t>(BLTCU_MAX_WPC, w->smem_optin / per_warp);
+    int wpc = (int)std::min<size_t>(12, w->smem_optin / per_warp);
     if (o.warps_per_cta > 0 && o.warps_per_cta < wpc) wpc = o.warps_per_cta;
     if (wpc < 1) {
         fprintf(stderr, "bltcu: problem %d x %d does not fit the shared-memory budget (%zu bytes)\n", n, m, w->smem_optin);
@@ -2589,9 +2658,9 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
     const int lo = (int)((long long)count * rank / world), hi = (int)((long long)count * (rank + 1) / world);
     const int mine = hi - lo;
     if (mine == 0) return BLTCU_STATUS_OK;
-    std::lock_guard<std::mutex> lk(g_mu);
     DevWs *w = nullptr;
     if (get_ws(o.device, &w)) return BLTCU_STATUS_ERROR;
+    std::lock_guard<std::mutex> lk(w->mu);
     const size_t nm = (size_t)n * m;
     std::vector<uint64_t> ni(mine), np(mine);
     std::vector<int> fd(mine), hl(mine);
@@ -2638,9 +2707,9 @@ extern "C" int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int c
 
 extern "C" int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok) {
     if (n <= 0 || m <= 0 || !lat || !con || !u || !ok) return BLTCU_STATUS_INPUT_ERROR;
-    std::lock_guard<std::mutex> lk(g_mu);
     DevWs *w = nullptr;
     if (get_ws(0, &w)) return BLTCU_STATUS_ERROR;
+    std::lock_guard<std::mutex> lk(w->mu);
     const size_t bytes = ((size_t)n * m + 2 * (size_t)m + n + 1) * 8;
     int64_t *d = nullptr;
     CK(cudaMalloc((void **)&d, bytes));
@@ -2659,9 +2728,9 @@ extern "C" int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, i
 extern "C" int bltcu_infdist(const double *B, int n, int m, const int64_t *u, int k, const double *p, double *x,
                              double *dist) {
     if (n <= 0 || m <= 0 || k < 0 || k > n || k > m || n > MAXD || m > MAXD) return BLTCU_STATUS_INPUT_ERROR;
-    std::lock_guard<std::mutex> lk(g_mu);
     DevWs *w = nullptr;
     if (get_ws(0, &w)) return BLTCU_STATUS_ERROR;
+    std::lock_guard<std::mutex> lk(w->mu);
     const size_t smem = warp_smem_bytes(n, m, 0, 1);
     const size_t nb = (size_t)n * m, mm = (size_t)m * m;
     // doubles: B, p, x, dist+rc, Q, Qrev, Rm, QTp, Wg (m*LDG + m*m), tmp (2m); then u
@@ -2696,6 +2765,8 @@ extern "C" void bltcu_release(void) {
         if (w->e0) cudaEventDestroy(w->e0);
         if (w->e1) cudaEventDestroy(w->e1);
         if (w->stream) cudaStreamDestroy(w->stream);
+        if (w->stream2) cudaStreamDestroy(w->stream2);
+        if (w->pin) cudaFreeHost(w->pin);
         delete w;
     }
     g_ws.clear();

@@ -64,14 +64,72 @@ def reduce_results(local: dict, n: int, group=None, device=None) -> dict:
     return out
 
 
-def closest_sharded(lat, con, split_depth: int = 6, **opts) -> dict:
-    """closest() of libblt/closest.h:50-54 over all ranks of the default process group (one GPU each)."""
+class StopFlag:
+    """The stop word of a multi-rank search when the ranks are processes on one node: one int in a POSIX shared-memory
+    page (/dev/shm), mapped by every rank (bltcu_opts.stop_flag); each rank's host thread relays it to and from its GPU
+    while the search kernel runs.  The rank that finds a point sets it, the others stop within a millisecond: closest() returns
+    at the first point (closest.cc:300-312).  No collective is involved: torch.distributed only provides the barriers
+    around reset()."""
+
+    def __init__(self, name: str | None = None):
+        import ctypes
+        import mmap
+        import os
+
+        import torch.distributed as dist
+
+        self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.path = "/dev/shm/" + (name or f"bltcu_stop_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}")
+        if self.rank == 0:
+            fd = os.open(self.path, os.O_CREAT | os.O_RDWR | os.O_TRUNC, 0o600)
+            os.ftruncate(fd, mmap.PAGESIZE)
+        if dist.is_initialized():
+            dist.barrier()
+        if self.rank != 0:
+            fd = os.open(self.path, os.O_RDWR)
+        self._mm = mmap.mmap(fd, mmap.PAGESIZE)
+        os.close(fd)
+        self._word = ctypes.c_int.from_buffer(self._mm)
+        self.address = ctypes.addressof(self._word)
+
+    def reset(self):
+        """Zeroes the word; collective (every rank calls it before the search starts)."""
+        import torch.distributed as dist
+
+        if dist.is_initialized():
+            dist.barrier()
+        if self.rank == 0:
+            self._word.value = 0
+        if dist.is_initialized():
+            dist.barrier()
+
+    @property
+    def value(self) -> int:
+        return int(self._word.value)
+
+    def close(self):
+        import os
+
+        import torch.distributed as dist
+
+        if dist.is_initialized():
+            dist.barrier()
+        if self.rank == 0 and os.path.exists(self.path):
+            os.unlink(self.path)
+
+
+def closest_sharded(lat, con, split_depth: int = 6, stop: "StopFlag | None" = None, **opts) -> dict:
+    """closest() of libblt/closest.h:50-54 over all ranks of the default process group (one GPU each).  With `stop`
+    (a StopFlag every rank constructed) the first point found on any rank ends the search on all of them."""
     import torch.distributed as dist
 
     import blt_b200
 
     rank = dist.get_rank() if dist.is_initialized() else 0
     world = dist.get_world_size() if dist.is_initialized() else 1
+    if stop is not None:
+        stop.reset()
+        opts["stop_flag"] = stop.address
     local = blt_b200.closest(lat, con, rank=rank, world=world, split_depth=split_depth if world > 1 else 0, **opts)
     return reduce_results(local, np.asarray(lat).shape[0])
 

@@ -18,7 +18,7 @@ class Opts(ctypes.Structure):
     _fields_ = [("device", ctypes.c_int), ("rank", ctypes.c_int), ("world", ctypes.c_int),
                 ("split_depth", ctypes.c_int), ("donate_min_level", ctypes.c_int), ("no_early_exit", ctypes.c_int),
                 ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int), ("timeout_ms", ctypes.c_int),
-                ("eager", ctypes.c_int)]
+                ("eager", ctypes.c_int), ("gpus", ctypes.c_int), ("stop_flag", ctypes.c_void_p)]
 
 
 class Stats(ctypes.Structure):
@@ -28,7 +28,8 @@ class Stats(ctypes.Structure):
                 ("hist", ctypes.c_uint64 * (MAX_DIM + 1)), ("kernel_ms", ctypes.c_double),
                 ("total_ms", ctypes.c_double), ("found", ctypes.c_int), ("launches", ctypes.c_int),
                 ("warps", ctypes.c_int), ("ctas", ctypes.c_int), ("scratch_bytes", ctypes.c_uint64),
-                ("busy_frac", ctypes.c_double), ("best_key", ctypes.c_uint16 * MAX_DIM), ("best_valid", ctypes.c_int)]
+                ("busy_frac", ctypes.c_double), ("best_key", ctypes.c_uint16 * MAX_DIM), ("best_valid", ctypes.c_int),
+                ("stopped", ctypes.c_int), ("gpus", ctypes.c_int)]
 
 
 def lib() -> ctypes.CDLL:
@@ -98,7 +99,8 @@ def _stats_dict(rc, sol, st, n):
                 hist=np.array(list(st.hist)[:n + 1], dtype=np.uint64), kernel_ms=float(st.kernel_ms),
                 total_ms=float(st.total_ms), found=bool(st.found), launches=int(st.launches), warps=int(st.warps),
                 ctas=int(st.ctas), scratch_bytes=int(st.scratch_bytes), busy_frac=float(st.busy_frac),
-                best_key=np.array(list(st.best_key)[:n], dtype=np.int64) if st.best_valid else None)
+                best_key=np.array(list(st.best_key)[:n], dtype=np.int64) if st.best_valid else None,
+                stopped=bool(st.stopped), gpus=int(st.gpus))
 
 
 def closest(lat, con, **opts):

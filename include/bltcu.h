@@ -40,6 +40,15 @@ typedef struct bltcu_opts {
                             BLTCU_TIMEOUT_MS, else none) */
     int eager;           /* explored children a warp collects on one level before it descends into the first (0 = default;
                             1 = each warp descends at once, the reference's depth-first order inside a subtree) */
+    int gpus;            /* bltcu_closest_ex() with world <= 1: search on this many devices (device, device+1, ...) from
+                            this one process, a host thread and a share of the subtrees each, results merged before the
+                            call returns (0 = environment variable BLT_GPUS, else 1) */
+    void *stop_flag;     /* world > 1: host address of one int shared by all ranks of the search (any host memory the
+                            ranks share: a variable when they are threads, a POSIX shared-memory page when they are
+                            processes).  The rank that finds a point sets it, every other rank stops within a
+                            millisecond: closest() returns at the first point (closest.cc:300-312).  GPUs never access
+                            the word; each rank's host thread relays it to and from its device while the kernel runs.
+                            The caller zeroes it before the search.  NULL = each rank stops only on its own find */
 } bltcu_opts;
 
 /* Statistics of one search.  niter/nprune are SolverStats of libblt/closest.h:14-17. */
@@ -61,6 +70,8 @@ typedef struct bltcu_stats {
      * the `sol` of the rank whose key is lexicographically last (closest.cc:300-303 keeps the last recorded leaf). */
     uint16_t best_key[BLTCU_MAX_DIM];
     int best_valid;        /* 1 = a leaf was recorded by this rank (best_key and sol are meaningful) */
+    int stopped;           /* 1 = this rank ended early because another rank set the stop flag */
+    int gpus;              /* devices that took part (bltcu_closest_ex with opts.gpus / BLT_GPUS) */
 } bltcu_stats;
 
 /* closest(): libblt/closest.h:50-54, libblt/closest.cc:166-327.
