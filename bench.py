@@ -10,8 +10,12 @@ committed under tests/golden/ with the script that made it).  A node = one layer
 
 `value`  : nodes / device time of the search kernel(s), inputs resident in HBM (CUDA events on the launching stream,
            max over ranks, summed over the K steps).
-`e2e`    : the same metric through the C ABI call bltcu_closest_ex() with pinned HOST buffers: host->device copy of
-           the basis and bounds, search, device->host copy of the result, wall clock around the call.
+`e2e`    : the same metric through the plugin call blt_check() (include/blt.h) on a context holding the UN-reduced
+           system of the fixture, host data in and out: stretch to the cube, exact LLL (host seam), host->device copy
+           of the reduced basis and bounds, search, device->host copy of the result, back-substitution, final exact
+           check; wall clock around the call (`lll_ms` / `search_ms` broken out from blt_b200_last_stats).
+           At N > 1 the plugin call is one process using N GPUs (BLT_GPUS = N, a host thread per device): rank 0
+           makes it while the other ranks wait at a barrier.
 N > 1    : every rank runs the deterministic static split and then searches its own share of the subtrees
            (bltcu_opts.rank/world); no collective on the data path, one all-reduce of the counters at the end.
            Total work is fixed => "strong" scaling.
@@ -47,7 +51,8 @@ def f_alg(k: int, m: int) -> float:
 
 def load_workload():
     z = np.load(FIXTURE)
-    return dict(lat=z["lat"].astype(np.int64), con=z["con"].astype(np.int64), w=int(z["w"]), seed=int(z["seed"]),
+    return dict(lat=z["lat"].astype(np.int64), con=z["con"].astype(np.int64), A=z["A"].astype(np.int64), C=z["C"].astype(np.int64),
+                w=int(z["w"]), seed=int(z["seed"]),
                 n=int(z["lat"].shape[0]), m=int(z["lat"].shape[1]), nodes_expected=int(z["nodes"]))
 
 
@@ -134,7 +139,38 @@ def batch_supplement(blt_b200):
         g = blt_b200.closest(la, co, timeout_ms=60000)
         sat.append({"instance": name, "found": bool(g["found"]), "gpu_ms": 1e3 * (time.perf_counter() - t1),
                     "gpu_nodes": int(g["nodes"]), "cpu_port_nodes": int(zj[f"nodes_{name}"])})
-    return {"lll_batch": lll, "sat_time_to_decision": sat,
+    # BASELINE.json config 4: dense UNSAT n = m = 80 (10.8 M nodes), exhaustive, counts against the oracle's stored ones
+    z80 = np.load(os.path.join(ROOT, "tests", "golden", "bench_dense80_w105.npz"))
+    blt_b200.closest(z80["lat"], z80["con"], timeout_ms=600000)
+    g80 = blt_b200.closest(z80["lat"], z80["con"], timeout_ms=600000)
+    dense80 = {"workload": "config 4: dense UNSAT BILP n=80 m=80 |a|<=100 width=105 seed=0, exhaustive (tests/golden/bench_dense80_w105.npz)",
+               "nodes": int(g80["nodes"]), "nodes_per_s": g80["nodes"] / (g80["kernel_ms"] * 1e-3), "kernel_ms": g80["kernel_ms"],
+               "count_ok": bool(g80["nodes"] == int(z80["nodes"]) and g80["pivots"] == int(z80["pivots"])), "busy_frac": g80["busy_frac"]}
+    # BASELINE.json config 2: 40 variables x 20 rows through blt_check_batch (reduction-bound: time to decision)
+    from blt_b200 import api
+    rng = np.random.default_rng(2)
+    ctxs = []
+    for _ in range(30):
+        A2 = rng.integers(-100, 101, size=(20, 40))
+        c2 = rng.integers(-10**6, 10**6 + 1, size=20)
+        cx = api.Context()
+        vs = [cx.var(str(j)) for j in range(40)]
+        for i in range(20):
+            e = cx.const(0)
+            for j in range(40):
+                e = e + int(A2[i, j]) * vs[j]
+            cx.assume(int(c2[i]), e, int(c2[i]) + 8)
+        ctxs.append(cx)
+    api.check_batch(ctxs[:2])
+    t1 = time.perf_counter()
+    res2 = api.check_batch(ctxs)
+    dt2 = time.perf_counter() - t1
+    config2 = {"workload": "config 2: 30 systems of 40 variables x 20 rows, |a|<=100, width 8, through blt_check_batch",
+               "ms_per_system": 1e3 * dt2 / len(ctxs), "decisions_sat": int(sum(1 for x in res2 if x == 10)),
+               "decisions_unsat": int(sum(1 for x in res2 if x == 11))}
+    for cx in ctxs:
+        cx.free()
+    return {"lll_batch": lll, "sat_time_to_decision": sat, "dense80": dense80, "config2": config2,
             "workload": "config 5: 4000 dense 20x20 instances (tests/golden/batch20.npz x10), a warp per instance plus helpers",
             "instances_per_s": len(lats) / dt,
             "nodes_per_s": (int(r["niter"].sum()) + int(r["nprune"].sum()) + len(lats)) / dt, "kernel_ms": r["kernel_ms"],
@@ -236,15 +272,37 @@ def main():
 
     expected_nodes = wl["nodes_expected"]
 
+    # The plugin call: a context with the un-reduced system, as run_blt builds it (libblt/run_blt.cc:151-166); built once,
+    # outside the timed region (it is the caller's input), checked K times.
+    ctx = None
+    if rank == 0:
+        from blt_b200 import api
+        A, C = wl["A"], wl["C"]
+        ctx = api.Context()
+        xs = [ctx.var(str(j)) for j in range(A.shape[1])]
+        for i in range(A.shape[0]):
+            e = ctx.const(0)
+            for j in range(A.shape[1]):
+                if A[i, j]:
+                    e = e + int(A[i, j]) * xs[j]
+            if ctx.assume(int(C[i, 0]), e, int(C[i, 1])) != 0:
+                raise SystemExit("bench.py: blt_assume failed")
+
     def step_e2e():
+        """One blt_check() of the whole system on rank 0 (all N GPUs from one process at N > 1)."""
         flush.zero_()
         torch.cuda.synchronize()
+        if rank != 0:
+            return dict(nodes=0, lll_ms=0.0, search_ms=0.0), 0.0
+        os.environ["BLT_GPUS"] = str(world)
+        os.environ["BLTCU_TIMEOUT_MS"] = str(opts["timeout_ms"])
         t0 = time.perf_counter()
-        r = blt_b200.closest(lat_h.numpy(), con_h.numpy(), **opts)
+        rc = ctx.check()
         dt = time.perf_counter() - t0
-        if r["rc"] != 0:
-            raise SystemExit(f"bench.py: search failed with status {r['rc']}")
-        return r, dt
+        if rc != 11:  # BLT_CHECK_UNSAT: the workload is an exhaustive (UNSAT) enumeration
+            raise SystemExit(f"bench.py: blt_check returned {rc}")
+        st = ctx.last_stats()
+        return dict(nodes=st["niter"] + st["nprune"] + 2, lll_ms=st["lll_ms"], search_ms=st["search_ms"]), dt
 
     for _ in range(max(args.warmup, 3)):
         step_dev()
@@ -265,13 +323,17 @@ def main():
         last = r
     barrier()
     wall_s = time.perf_counter() - t_wall0
-    # end to end through the host-buffer ABI
-    e2e_s, e2e_nodes = 0.0, 0
+    # end to end through the plugin call
+    e2e_s, e2e_nodes, e2e_lll_ms, e2e_search_ms = 0.0, 0, 0.0, 0.0
+    step_e2e()  # untimed: the other devices' workspaces are allocated on first use
+    barrier()
     for _ in range(args.steps):
         r, dt = step_e2e()
+        barrier()
         e2e_s += dt
         e2e_nodes += r["nodes"]
-    barrier()
+        e2e_lll_ms += r["lll_ms"]
+        e2e_search_ms += r["search_ms"]
     sampler.stop_flag = True
 
     red = torch.tensor([kernel_ms, e2e_s], dtype=torch.float64, device="cuda")
@@ -296,12 +358,16 @@ def main():
                 "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": workload_config(wl),
                 "niter": int(niter_all), "nprune": int(nprune_all), "nodes_per_step": nodes_all / args.steps,
-                "time_to_decision_ms": kernel_ms_max / args.steps, "wall_ms_per_step": 1e3 * wall_s / args.steps,
+                "time_to_decision_ms": 1e3 * e2e_s_max / args.steps, "wall_ms_per_step": 1e3 * wall_s / args.steps,
                 "pivots_per_node": last["pivots"] / max(1, last["nodes"]), "donated": last["donated"],
                 "warps": last["warps"], "busy_frac": last["busy_frac"],
                 "count_ok": bool(int(round(nodes_all / args.steps)) == expected_nodes),
-                "e2e": {"value": e2e_nodes_all / e2e_s_max, "unit": UNIT, "h2d_bytes_per_step": (n * m + 2 * m) * 8,
-                        "d2h_bytes_per_step": n * 8 + 1024},
+                "e2e": {"value": e2e_nodes_all / e2e_s_max, "unit": UNIT, "h2d_bytes_per_step": (n * m + 2 * m) * 8 * world,
+                        "d2h_bytes_per_step": (n * 8 + 1024) * world,
+                        "call": "blt_check() on the un-reduced system (stretch, exact LLL on the host, search, back-substitution)"
+                                + (f", one process driving {world} GPUs (BLT_GPUS)" if world > 1 else ""),
+                        "ms_per_call": 1e3 * e2e_s_max / args.steps, "lll_ms": e2e_lll_ms / args.steps,
+                        "search_ms": e2e_search_ms / args.steps, "count_ok": bool(e2e_nodes // args.steps == expected_nodes)},
                 "gpu_launches": int(launches_all),
                 "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
                              "frac": achieved / peak, "traffic": None,

@@ -84,6 +84,11 @@ struct QCtl {
     int timed_out;              // watchdog fired: 1 node loop, 2 idle loop, 3 pop spin, 4 push spin
     int fail_info;              // failcode | level << 8 of the first LP failure (diagnostics)
     int dive_state;             // first descent of the search: 0 not started, 1 under way (the other warps wait), 2 over
+    // feed: subtrees the rank's host thread hands in while the kernel runs (multi-rank searches: the ranks take the
+    // second half of the static split's subtrees from a shared counter, whoever runs dry first)
+    unsigned int feed_head;     // next entry of Params::feed to take (device)
+    unsigned int feed_tail;     // entries written so far (host, through the copy engine)
+    int feed_open;              // host: more entries may come
     unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
     unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated;
     unsigned long long dive_end_ns;  // %globaltimer when the first descent ended (diagnostics)
@@ -127,6 +132,7 @@ struct Params {
     ord_t *best_key;        // per warp: n
     int *best_valid;        // per warp
     int *out_list;          // static split output (record indices)
+    int *feed;              // record indices handed in by the host while the kernel runs (nullptr = none)
     int static_depth;       // records shallower than this emit every child; children at this depth are collected
     int dynamic;            // 1 = donate to idle warps
     int donate_min_level;
@@ -1378,9 +1384,20 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
                     if (hold) { __nanosleep(500); if (overdue(q, 2)) stop = 1; }
                     else slot = ring_pop(q, &q->head, &q->tail, P.ring, P.ring_mask);
                     if (slot >= 0 && (((const int *)(P.pool + (size_t)slot * RL.stride))[1] & REC_DIVE)) q->dive_state = 1;
+                    if (!hold && slot < 0 && P.feed &&
+                        (int)(*(volatile unsigned int *)&q->feed_tail - *(volatile unsigned int *)&q->feed_head) > 0) {  // a subtree from the host's feed
+                        atomicAdd(&q->pending, 1);      // counted before it is taken, so that nobody sees an empty search
+                        for (;;) {
+                            const unsigned int fh = *(volatile unsigned int *)&q->feed_head, ft = *(volatile unsigned int *)&q->feed_tail;
+                            if ((int)(ft - fh) <= 0) { atomicSub(&q->pending, 1); break; }
+                            if (atomicCAS(&q->feed_head, fh, fh + 1) == fh) { slot = ((volatile int *)P.feed)[fh]; break; }
+                        }
+                    }
                     if (hold) {}
                     else if (slot < 0) {
-                        if (*(volatile int *)&q->pending == 0) stop = 1;
+                        const bool fed_out = !P.feed || (*(volatile int *)&q->feed_open == 0 &&
+                                                         (int)(*(volatile unsigned int *)&q->feed_tail - *(volatile unsigned int *)&q->feed_head) <= 0);
+                        if (*(volatile int *)&q->pending == 0 && fed_out) stop = 1;
                         else {
                             if (!am_idle) { atomicAdd(&q->idle, 1); am_idle = true; }
                             __nanosleep(500);
@@ -2147,7 +2164,12 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     // The stop word of a multi-rank search is plain host memory shared by the ranks' host threads (or processes).  GPUs
     // never touch it: while its kernel runs, each rank's host thread looks at its own device's `found` through a second
     // stream, raises the word when it is set, and writes `abort` into its device when somebody else raised the word.
-    volatile int *host_stop = (world > 1 && o.stop_flag && !o.no_early_exit) ? (volatile int *)o.stop_flag : nullptr;
+    // Word 1 of the same block is a counter from which the ranks take the second half of the static split's subtrees one
+    // at a time, whoever has idle warps first; the host thread writes the record index into the device's feed (`dyn`).
+    volatile int *shared = (world > 1 && o.stop_flag) ? (volatile int *)o.stop_flag : nullptr;
+    volatile int *host_stop = (shared && !o.no_early_exit) ? shared : nullptr;
+    std::vector<int> dyn;   // record slots of the subtrees dealt on demand, in depth-first order
+    bool feeding = false;
 
     int launches = 0;
     const size_t setup_smem = warp_smem_bytes(n, m, 0, 1);
@@ -2198,6 +2220,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     CK(cudaMemsetAsync(P.sol, 0, (size_t)n * 8, st));
 
     float kernel_ms = 0.f;
+    unsigned int fed_total = 0;
     bool lp_failed = false;
     const bool verbose = getenv("BLTCU_VERBOSE") != nullptr;
     QCtl acc;  // totals
@@ -2211,21 +2234,39 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventRecord(w->e0, st));
         CK(launch_search(m, ctas, wpc * 32, smem_bytes, st, P));
         CK(cudaEventRecord(w->e1, st));
-        if (host_stop) {
-            bool told = false;
+        if (host_stop || feeding) {
+            bool told = false, closed = !feeding;
+            unsigned int fed = 0;
+            int *pin = w->pin;  // [0..4] pending idle abort status found (as laid out in QCtl); [8..] values to send
             while (cudaEventQuery(w->e1) == cudaErrorNotReady) {
-                CK(cudaMemcpyAsync(w->pin, &P.q->found, 4, cudaMemcpyDeviceToHost, w->stream2));
+                CK(cudaMemcpyAsync(pin, &P.q->pending, 20, cudaMemcpyDeviceToHost, w->stream2));
                 CK(cudaStreamSynchronize(w->stream2));
-                if (w->pin[0]) *host_stop = 1;
-                if (*host_stop && !told) {
-                    w->pin[1] = 1;
-                    CK(cudaMemcpyAsync(&P.q->abort, w->pin + 1, 4, cudaMemcpyHostToDevice, w->stream2));
+                if (host_stop && pin[4]) *host_stop = 1;
+                if (host_stop && *host_stop && !told) {
+                    pin[8] = 1;
+                    CK(cudaMemcpyAsync(&P.q->abort, pin + 8, 4, cudaMemcpyHostToDevice, w->stream2));
                     CK(cudaStreamSynchronize(w->stream2));
                     told = true;
                 }
-                std::this_thread::sleep_for(std::chrono::microseconds(100));
+                if (!closed && !told && pin[1] * 2 > nwarps) {  // more than half of the warps wait for work: one more subtree
+                    const int i = __atomic_fetch_add((int *)(shared + 1), 1, __ATOMIC_RELAXED);
+                    if (i < (int)dyn.size()) {
+                        pin[9] = dyn[(size_t)i]; pin[10] = (int)(fed + 1);
+                        CK(cudaMemcpyAsync(P.feed + fed, pin + 9, 4, cudaMemcpyHostToDevice, w->stream2));
+                        CK(cudaMemcpyAsync(&P.q->feed_tail, pin + 10, 4, cudaMemcpyHostToDevice, w->stream2));
+                        ++fed;
+                    } else {
+                        pin[11] = 0;
+                        CK(cudaMemcpyAsync(&P.q->feed_open, pin + 11, 4, cudaMemcpyHostToDevice, w->stream2));
+                        closed = true;
+                    }
+                    CK(cudaStreamSynchronize(w->stream2));
+                    continue;  // a hungry device is served again at once
+                }
+                std::this_thread::sleep_for(std::chrono::microseconds(50));
             }
             (void)cudaGetLastError();
+            fed_total += fed;
         }
         CK(cudaMemcpyAsync(&hq, P.q, sizeof hq, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -2303,10 +2344,15 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
         std::sort(idx.begin(), idx.end(), [&](int a, int b) { return keys[a] < keys[b]; });
         initial.clear();
-        for (size_t i = 0; i < idx.size(); ++i) if ((int)(i % world) == rank) initial.push_back(out[idx[i]]);
+        // first half of the subtrees: dealt round-robin now; second half (with a shared block): taken on demand
+        const size_t nstat = shared ? (idx.size() + 1) / 2 : idx.size();
+        for (size_t i = 0; i < nstat; ++i) if ((int)(i % world) == rank) initial.push_back(out[idx[i]]);
+        for (size_t i = nstat; i < idx.size(); ++i) dyn.push_back(out[idx[i]]);
+        feeding = !dyn.empty();
         const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0)) || (host_stop && *host_stop);
-        if (!stop && !initial.empty()) {
+        if (!stop && (!initial.empty() || feeding)) {
             if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
+            if (feeding) { hq.feed_open = 1; P.feed = P.out_list; CK(cudaMemcpyAsync(P.q, &hq, sizeof hq, cudaMemcpyHostToDevice, st)); }
             if (found) { hq.found = 1; CK(cudaMemcpyAsync(P.q, &hq, sizeof hq, cudaMemcpyHostToDevice, st)); }
             P.static_depth = 0; P.dynamic = 1;
             if (launch()) return BLTCU_STATUS_ERROR;
@@ -2355,7 +2401,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         memset(stats, 0, sizeof *stats);
         stats->niter = acc.niter; stats->nprune = acc.nprune; stats->nodes = acc.nodes; stats->pivots = acc.pivots;
         stats->quick_prunes = acc.quick; stats->refactors = acc.refactors; stats->cold_starts = acc.colds;
-        stats->donated = acc.donated;
+        stats->donated = acc.donated + fed_total;
         stats->busy_frac = (acc.idle_ns + acc.busy_ns) ? (double)acc.busy_ns / (double)(acc.idle_ns + acc.busy_ns) : 0.0;
         for (int i = 0; i <= n; ++i) stats->hist[i] = acc.hist[i];
         stats->kernel_ms = kernel_ms;
@@ -2418,8 +2464,8 @@ static int closest_one_device(const int64_t *lat, const int64_t *con, int n, int
 static int closest_multi_device(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts &base, int gpus, int64_t *sol,
                                 bltcu_stats *stats) {
     const auto t0 = std::chrono::steady_clock::now();
-    int flag_word = 0;
-    int *flag = &flag_word;
+    int shared_words[16] = {0};  // [0] stop word, [1] counter of the subtrees dealt on demand (bltcu_opts.stop_flag)
+    int *flag = shared_words;
     std::vector<bltcu_stats> st((size_t)gpus);
     std::vector<std::vector<int64_t>> sols((size_t)gpus, std::vector<int64_t>((size_t)n, 0));
     std::vector<int> rcs((size_t)gpus, BLTCU_STATUS_ERROR);

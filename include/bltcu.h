@@ -43,12 +43,15 @@ typedef struct bltcu_opts {
     int gpus;            /* bltcu_closest_ex() with world <= 1: search on this many devices (device, device+1, ...) from
                             this one process, a host thread and a share of the subtrees each, results merged before the
                             call returns (0 = environment variable BLT_GPUS, else 1) */
-    void *stop_flag;     /* world > 1: host address of one int shared by all ranks of the search (any host memory the
-                            ranks share: a variable when they are threads, a POSIX shared-memory page when they are
-                            processes).  The rank that finds a point sets it, every other rank stops within a
-                            millisecond: closest() returns at the first point (closest.cc:300-312).  GPUs never access
-                            the word; each rank's host thread relays it to and from its device while the kernel runs.
-                            The caller zeroes it before the search.  NULL = each rank stops only on its own find */
+    void *stop_flag;     /* world > 1: host address of 16 ints shared by all ranks of the search (any host memory the
+                            ranks share: an array when they are threads, a POSIX shared-memory page when they are
+                            processes), zeroed by the caller before the search.  Word 0 is the stop word: the rank that
+                            finds a point sets it, every other rank stops within a millisecond, as closest() returns at
+                            the first point (closest.cc:300-312).  Word 1 is a counter from which the ranks take the
+                            second half of the split's subtrees one by one, whoever has idle warps (load balance between
+                            GPUs; the first half is dealt i % world).  GPUs never access the block; each rank's host
+                            thread relays between it and its device while the kernel runs.  NULL = static deal only,
+                            each rank stops only on its own find */
 } bltcu_opts;
 
 /* Statistics of one search.  niter/nprune are SolverStats of libblt/closest.h:14-17. */
