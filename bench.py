@@ -244,8 +244,12 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the search has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    host_group = None
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # Barriers around the plugin call must not occupy a GPU: rank 0's call runs persistent kernels on EVERY device
+        # (one CTA per SM), and an NCCL barrier kernel spinning on another rank's device would keep an SM from them.
+        host_group = dist.new_group(backend="gloo")
     wl = load_workload()
     n, m = wl["n"], wl["m"]
     lat_h = torch.from_numpy(wl["lat"]).contiguous().pin_memory()
@@ -262,9 +266,17 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    shared = None
+    if world > 1:  # stop word + on-demand subtree counter shared by the ranks (host memory; no collective)
+        from blt_b200.dist import StopFlag
+        shared = StopFlag()
+        opts["stop_flag"] = shared.address
+
     def step_dev():
         flush.zero_()
         torch.cuda.synchronize()
+        if shared is not None:
+            shared.reset()
         r = blt_b200.closest_dev(lat_d.data_ptr(), con_d.data_ptr(), n, m, **opts)
         if r["rc"] != 0:
             raise SystemExit(f"bench.py: search failed with status {r['rc']}")
@@ -324,12 +336,18 @@ def main():
     barrier()
     wall_s = time.perf_counter() - t_wall0
     # end to end through the plugin call
+    def host_barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier(group=host_group)
+
     e2e_s, e2e_nodes, e2e_lll_ms, e2e_search_ms = 0.0, 0, 0.0, 0.0
+    host_barrier()
     step_e2e()  # untimed: the other devices' workspaces are allocated on first use
-    barrier()
+    host_barrier()
     for _ in range(args.steps):
         r, dt = step_e2e()
-        barrier()
+        host_barrier()
         e2e_s += dt
         e2e_nodes += r["nodes"]
         e2e_lll_ms += r["lll_ms"]
@@ -396,6 +414,7 @@ def main():
                                               "oracle/blt_oracle.c single thread"}
         print(json.dumps(line))
     if world > 1:
+        shared.close()
         dist.destroy_process_group()
     return 0
 

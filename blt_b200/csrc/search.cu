@@ -2208,6 +2208,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         unsigned int nf = 0;
         std::vector<char> used(pool_cap, 0);
         for (int r : initial) used[r] = 1;
+        for (int r : dyn) used[r] = 1;  // records waiting to be fed stay where they are
         for (int i = 0; i < pool_cap; ++i) if (!used[i]) fring[nf++] = i;
         hq.ftail = nf;
         hq.deadline_ns = deadline_ns;
@@ -2261,7 +2262,10 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                         closed = true;
                     }
                     CK(cudaStreamSynchronize(w->stream2));
-                    continue;  // a hungry device is served again at once
+                    // one subtree per 150 us at most: while a search ramps up every warp looks idle, and a rank must not
+                    // swallow the whole on-demand half in those first milliseconds
+                    std::this_thread::sleep_for(std::chrono::microseconds(150));
+                    continue;
                 }
                 std::this_thread::sleep_for(std::chrono::microseconds(50));
             }

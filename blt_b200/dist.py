@@ -65,7 +65,8 @@ def reduce_results(local: dict, n: int, group=None, device=None) -> dict:
 
 
 class StopFlag:
-    """The stop word of a multi-rank search when the ranks are processes on one node: one int in a POSIX shared-memory
+    """The shared block of a multi-rank search (bltcu_opts.stop_flag: stop word + on-demand subtree counter) when the
+    ranks are processes on one node: 16 ints in a POSIX shared-memory
     page (/dev/shm), mapped by every rank (bltcu_opts.stop_flag); each rank's host thread relays it to and from its GPU
     while the search kernel runs.  The rank that finds a point sets it, the others stop within a millisecond: closest() returns
     at the first point (closest.cc:300-312).  No collective is involved: torch.distributed only provides the barriers
@@ -89,8 +90,8 @@ class StopFlag:
             fd = os.open(self.path, os.O_RDWR)
         self._mm = mmap.mmap(fd, mmap.PAGESIZE)
         os.close(fd)
-        self._word = ctypes.c_int.from_buffer(self._mm)
-        self.address = ctypes.addressof(self._word)
+        self._words = (ctypes.c_int * 16).from_buffer(self._mm)   # [0] stop word, [1] on-demand subtree counter
+        self.address = ctypes.addressof(self._words)
 
     def reset(self):
         """Zeroes the word; collective (every rank calls it before the search starts)."""
@@ -99,13 +100,14 @@ class StopFlag:
         if dist.is_initialized():
             dist.barrier()
         if self.rank == 0:
-            self._word.value = 0
+            for i in range(16):
+                self._words[i] = 0
         if dist.is_initialized():
             dist.barrier()
 
     @property
     def value(self) -> int:
-        return int(self._word.value)
+        return int(self._words[0])
 
     def close(self):
         import os

@@ -127,3 +127,55 @@ def test_two_rank_batch_gather():
         assert niter == [100 + i for i in range(7)] and nprune == [2 * i for i in range(7)]
         assert found == [i % 2 == 0 for i in range(7)]
         assert ms == 4.0
+
+
+def _flag_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import ctypes
+
+    import torch.distributed as dist
+
+    from blt_b200.dist import StopFlag
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    flag = StopFlag(name=f"bltcu_test_{port}")
+    flag.reset()
+    words = (ctypes.c_int * 16).from_address(flag.address)
+    if rank == 1:
+        words[0] = 1                      # what the finder's host thread does
+    dist.barrier()
+    seen = flag.value
+    # the on-demand counter: every rank takes three tickets; together they must be 0..5, each once
+    mine = []
+    for _ in range(3):
+        # Python has no atomic fetch-add on shared memory; ranks take turns instead (the C library does it atomically)
+        for turn in range(world):
+            dist.barrier()
+            if turn == rank:
+                mine.append(int(words[1]))
+                words[1] += 1
+    dist.barrier()
+    total = int(words[1])
+    flag.reset()
+    cleared = flag.value
+    q.put((rank, seen, sorted(mine), total, cleared))
+    flag.close()
+    dist.destroy_process_group()
+
+
+def test_shared_block_is_visible_to_both_ranks():
+    """blt_b200.dist.StopFlag: the 16-int block of bltcu_opts.stop_flag in POSIX shared memory (one process per GPU)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29100 + os.getpid() % 150
+    procs = [ctx.Process(target=_flag_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(seen == 1 and total == 6 and cleared == 0 for _, seen, _, total, cleared in res)
+    assert sorted(res[0][2] + res[1][2]) == [0, 1, 2, 3, 4, 5]

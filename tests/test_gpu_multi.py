@@ -50,11 +50,16 @@ def test_stop_word_ends_the_other_ranks(gpu):
     second = gpu.closest(lat, con, rank=other, world=2, split_depth=3, stop_flag=addr)
     assert second["rc"] == 0 and not second["found"] and second["stopped"]
     assert second["nodes"] <= alone[other]["nodes"] // 2 + 64
-    # exhaustive mode ignores the word (node counts must not depend on who finished first)
+    # exhaustive mode ignores the stop word, and the on-demand counter (word 1) hands every subtree of the second half
+    # to exactly one rank: the two ranks' counts add up to the whole tree whoever takes what
+    whole = gpu.closest(lat, con, no_early_exit=1)
+    for i in range(16):
+        word[i] = 0
     word[0] = 1
-    full = gpu.closest(lat, con, rank=other, world=2, split_depth=3, stop_flag=addr, no_early_exit=1)
-    again = gpu.closest(lat, con, rank=other, world=2, split_depth=3, no_early_exit=1)
-    assert full["nodes"] == again["nodes"] and not full["stopped"]
+    parts = [gpu.closest(lat, con, rank=r, world=2, split_depth=3, stop_flag=addr, no_early_exit=1) for r in (other, finder)]
+    assert all(p["rc"] == 0 and not p["stopped"] for p in parts)
+    assert sum(p["nodes"] for p in parts) == whole["nodes"] and sum(p["niter"] for p in parts) == whole["niter"]
+    assert word[1] > 0
 
 
 def test_one_process_two_gpus_exhaustive(gpu, golden):
