@@ -85,7 +85,7 @@ struct QCtl {
     int fail_info;              // failcode | level << 8 of the first LP failure (diagnostics)
     int dive_state;             // first descent of the search: 0 not started, 1 under way (the other warps wait), 2 over
     // feed: subtrees the rank's host thread hands in while the kernel runs (multi-rank searches: the ranks take the
-    // second half of the static split's subtrees from a shared counter, whoever runs dry first)
+    // last eighth of the static split's subtrees from a shared counter, whoever runs dry first)
     unsigned int feed_head;     // next entry of Params::feed to take (device)
     unsigned int feed_tail;     // entries written so far (host, through the copy engine)
     int feed_open;              // host: more entries may come
@@ -1992,7 +1992,7 @@ int get_ws(int device, DevWs **out) {
     CK(cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, device)); w->smem_optin = (size_t)v;
     CK(cudaStreamCreateWithFlags(&w->stream, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&w->stream2, cudaStreamNonBlocking));
-    CK(cudaHostAlloc((void **)&w->pin, 64, cudaHostAllocDefault));
+    CK(cudaHostAlloc((void **)&w->pin, 4096, cudaHostAllocDefault));
     CK(cudaEventCreate(&w->e0)); CK(cudaEventCreate(&w->e1));
     g_ws.push_back(w);
     *out = w;
@@ -2164,7 +2164,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     // The stop word of a multi-rank search is plain host memory shared by the ranks' host threads (or processes).  GPUs
     // never touch it: while its kernel runs, each rank's host thread looks at its own device's `found` through a second
     // stream, raises the word when it is set, and writes `abort` into its device when somebody else raised the word.
-    // Word 1 of the same block is a counter from which the ranks take the second half of the static split's subtrees one
+    // Word 1 of the same block is a counter from which the ranks take the last eighth of the static split's subtrees one
     // at a time, whoever has idle warps first; the host thread writes the record index into the device's feed (`dyn`).
     volatile int *shared = (world > 1 && o.stop_flag) ? (volatile int *)o.stop_flag : nullptr;
     volatile int *host_stop = (shared && !o.no_early_exit) ? shared : nullptr;
@@ -2249,20 +2249,24 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                     CK(cudaStreamSynchronize(w->stream2));
                     told = true;
                 }
-                if (!closed && !told && pin[1] * 2 > nwarps) {  // more than half of the warps wait for work: one more subtree
-                    const int i = __atomic_fetch_add((int *)(shared + 1), 1, __ATOMIC_RELAXED);
-                    if (i < (int)dyn.size()) {
-                        pin[9] = dyn[(size_t)i]; pin[10] = (int)(fed + 1);
-                        CK(cudaMemcpyAsync(P.feed + fed, pin + 9, 4, cudaMemcpyHostToDevice, w->stream2));
+                if (!closed && !told && pin[1] * 8 > nwarps) {  // an eighth of the warps wait for work: one more chunk
+                    // a chunk is 1/16 of a rank's fair share of the on-demand part (at most what the staging page holds)
+                    const int chunk = std::min(1000, std::max(1, (int)(dyn.size() / (16 * (size_t)world))));
+                    const int i0 = __atomic_fetch_add((int *)(shared + 1), chunk, __ATOMIC_RELAXED);
+                    if (i0 < (int)dyn.size()) {
+                        const int cnt = std::min(chunk, (int)dyn.size() - i0);
+                        for (int e = 0; e < cnt; ++e) pin[16 + e] = dyn[(size_t)(i0 + e)];
+                        pin[10] = (int)fed + cnt;
+                        CK(cudaMemcpyAsync(P.feed + fed, pin + 16, (size_t)cnt * 4, cudaMemcpyHostToDevice, w->stream2));
                         CK(cudaMemcpyAsync(&P.q->feed_tail, pin + 10, 4, cudaMemcpyHostToDevice, w->stream2));
-                        ++fed;
+                        fed += (unsigned int)cnt;
                     } else {
                         pin[11] = 0;
                         CK(cudaMemcpyAsync(&P.q->feed_open, pin + 11, 4, cudaMemcpyHostToDevice, w->stream2));
                         closed = true;
                     }
                     CK(cudaStreamSynchronize(w->stream2));
-                    // one subtree per 150 us at most: while a search ramps up every warp looks idle, and a rank must not
+                    // one chunk per 150 us at most: while a search ramps up every warp looks idle, and a rank must not
                     // swallow the whole on-demand half in those first milliseconds
                     std::this_thread::sleep_for(std::chrono::microseconds(150));
                     continue;
@@ -2348,8 +2352,9 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
         std::sort(idx.begin(), idx.end(), [&](int a, int b) { return keys[a] < keys[b]; });
         initial.clear();
-        // first half of the subtrees: dealt round-robin now; second half (with a shared block): taken on demand
-        const size_t nstat = shared ? (idx.size() + 1) / 2 : idx.size();
+        // Seven eighths of the subtrees are dealt round-robin now; with a shared block the last eighth is taken on demand,
+        // which evens out the ranks' finishing times (measured: an on-demand HALF starves the GPUs between refills).
+        const size_t nstat = shared ? idx.size() - idx.size() / 8 : idx.size();
         for (size_t i = 0; i < nstat; ++i) if ((int)(i % world) == rank) initial.push_back(out[idx[i]]);
         for (size_t i = nstat; i < idx.size(); ++i) dyn.push_back(out[idx[i]]);
         feeding = !dyn.empty();

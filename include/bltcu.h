@@ -48,8 +48,8 @@ typedef struct bltcu_opts {
                             processes), zeroed by the caller before the search.  Word 0 is the stop word: the rank that
                             finds a point sets it, every other rank stops within a millisecond, as closest() returns at
                             the first point (closest.cc:300-312).  Word 1 is a counter from which the ranks take the
-                            second half of the split's subtrees one by one, whoever has idle warps (load balance between
-                            GPUs; the first half is dealt i % world).  GPUs never access the block; each rank's host
+                            last eighth of the split's subtrees in small chunks, whoever has idle warps (load balance
+                            between GPUs; the rest is dealt i % world).  GPUs never access the block; each rank's host
                             thread relays between it and its device while the kernel runs.  NULL = static deal only,
                             each rank stops only on its own find */
 } bltcu_opts;
