@@ -48,3 +48,23 @@ for seed in range(4):
     out[f"con{seed}"] = np.array(Ci, dtype=np.int64)
     out[f"xs{seed}"] = xs
 np.savez_compressed(f"{G}/subset_sum60.npz", **out)
+
+# The same lattice with 26-bit weights (density 2.3: many subsets hit the target, so a search that is worth the name
+# finds one): seeds whose instance the oracle decides SAT without an LP failure; counts of the oracle stored.
+import oracle  # noqa: E402
+
+out = {}
+for seed in range(12):
+    A, C, xs = subset_sum(60, 26, seed)
+    L0 = [[Fraction(int(A[i][j])) for i in range(A.shape[0])] for j in range(A.shape[1])]
+    C0 = [[Fraction(int(b[0])), Fraction(int(b[1]))] for b in C]
+    L, Ci = context.convert_to_integral(L0, C0)
+    assert context.stretch_to_cube(L, Ci) == 0
+    rank, Lr, U = blt_b200.lll(np.array(L, dtype=np.int64))
+    lat, con = np.array(Lr[len(Lr) - rank:], dtype=np.int64), np.array(Ci, dtype=np.int64)
+    r = oracle.closest(lat, con, max_nodes=2000000)
+    if r["rc"] == 0 and oracle.check_soln(lat, con, r["sol"]) and r["nodes"] > 1000:
+        out[f"lat{seed}"], out[f"con{seed}"], out[f"nodes{seed}"] = lat, con, r["nodes"]
+        print("b26 seed", seed, "SAT after", r["nodes"], "nodes")
+out["seeds"] = np.array(sorted(int(k[3:]) for k in out if k.startswith("lat")))
+np.savez_compressed(f"{G}/subset_sum60_b26.npz", **out)
