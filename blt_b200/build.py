@@ -6,7 +6,8 @@ import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = [os.path.join(HERE, "csrc", "search.cu"), os.path.join(HERE, "csrc", "peaks.cu"),
-       os.path.join(HERE, "csrc", "lll_batch.cu"), os.path.join(HERE, "csrc", "host", "lll.cpp")]
+       os.path.join(HERE, "csrc", "lll_batch.cu"), os.path.join(HERE, "csrc", "host", "lll.cpp"),
+       os.path.join(HERE, "csrc", "host", "sound.cpp")]
 HOST_SRC = [os.path.join(HERE, "csrc", "host", f) for f in ("context.cpp", "blt_api.cpp")]
 HOST_HDR = [os.path.join(HERE, "csrc", "host", "context.h"), os.path.join(HERE, "..", "include", "blt.h"),
             os.path.join(HERE, "..", "include", "codes.h")]

@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cstring>
 #include <iostream>
 #include <sstream>
 
@@ -214,10 +215,8 @@ int Context::reduced(Prepared &p, int rank) {
     p.newL.assign((size_t)rank * p.n, 0);
     for (size_t i = 0; i < (size_t)rank; ++i)
         for (size_t j = 0; j < p.n; ++j) p.newL[i * p.n + j] = p.L[(i + p.m - rank) * p.n + j];
-    if (enable_yices_) {  // context.cc:210-228: this build carries no Yices; same failure as a missing libyices.so
-        ERROR("Context::check: ERROR Yices support was requested, but libyices.so failed to load!");
-        return BLT_STATUS_ERROR;
-    }
+    // context.cc:210-228 loads libyices.so here when sound mode was requested.  This build has no Yices: sound mode is
+    // the search kernel's own (bltcu_opts.sound, a prune needs a bound clear of the radius), selected in check().
     p.presoln.assign((size_t)rank, 0);
     return BLT_STATUS_OK;
 }
@@ -252,8 +251,11 @@ int Context::check() {  // context.cc:139-280
     if (rc != BLT_STATUS_OK) return rc;
     // search seam: closest(newL, C, yok, presoln_b, stats), context.cc:236
     bltcu_stats st;
+    bltcu_opts opts;
+    memset(&opts, 0, sizeof opts);
+    opts.sound = enable_yices_ ? 1 : 0;  // blt_init(enable_yices), run_blt -y
     t0 = clk::now();
-    rc = bltcu_closest_ex(p.newL.data(), p.C.data(), rank, (int)p.n, nullptr, p.presoln.data(), &st);
+    rc = bltcu_closest_ex(p.newL.data(), p.C.data(), rank, (int)p.n, &opts, p.presoln.data(), &st);
     last.search_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
     if (rc != BLT_STATUS_OK) return rc;
     return finish(p, st.niter, st.nprune);
@@ -268,6 +270,7 @@ int check_batch(Context **ctx, int count, int *results) {
     std::vector<char> live((size_t)count, 0);
     for (int i = 0; i < count; ++i) {
         if (!ctx[i]) { results[i] = BLT_STATUS_INPUT_ERROR; continue; }
+        if (ctx[i]->sound()) { results[i] = ctx[i]->check(); continue; }  // the batch kernels have no sound mode: one at a time
         results[i] = ctx[i]->prepare(P[i]);
         live[i] = results[i] == BLT_STATUS_OK;
     }

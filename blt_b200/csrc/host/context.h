@@ -80,6 +80,7 @@ public:
     CheckStats last;
 
     explicit Context(int flag = 0) : enable_yices_(flag != 0) {}
+    bool sound() const { return enable_yices_; }  // blt_init(enable_yices): sound pruning requested
     int nvars() const;
     int nassumpts() const { return (int)assumptions.size(); }
     Expr mkVar(const std::string &);

@@ -48,6 +48,10 @@
 
 #define FULLMASK 0xffffffffu
 #define DIST_EPS 1.0e-4  // libblt/glpk_wrapper.h:13
+// Sound mode (bltcu_opts.sound; the reference asks Yices about every LP prune,
+// closest.cc:258-267): a layer is pruned only when the dual bound clears the radius by this relative margin on top of
+// the 1e-4 band -- orders of magnitude above the floating-point error of the bound -- and kept otherwise.
+#define SOUND_MARGIN 1.0e-6
 #define EPS_OPT 1.0e-9
 #define PIV_TOL 1.0e-11
 #define HARRIS_DELTA 1.0e-10
@@ -61,7 +65,7 @@ typedef unsigned short ord_t;  // sibling ordinal on one level of a path key (sa
 #define LDQ_C 26   // row stride of the shared-memory copy of the first QS_MAX + 1 columns of Q: ld_vec(QS_MAX + 1)
 
 enum { NODE_EXPLORE = 0, NODE_PRUNE = 1, NODE_FAIL = -1 };
-enum { C_NITER = 0, C_NPRUNE, C_NODES, C_DONATED, C_PIVOTS, C_QUICK, C_REFAC, C_COLDS, C_IDLE_NS, C_BUSY_NS, C_COUNT = 12 };
+enum { C_NITER = 0, C_NPRUNE, C_NODES, C_DONATED, C_PIVOTS, C_QUICK, C_REFAC, C_COLDS, C_IDLE_NS, C_BUSY_NS, C_INBAND, C_COUNT = 12 };
 #define CTR(s, k) do { if ((s).lane == 0) (s).ctr[k]++; } while (0)
 enum { REC_TOP = 1, REC_CONT = 2, REC_DIVE = 4 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
 // REC_DIVE: this record is on the very first descent of the search (the reference's first dive towards the Babai
@@ -90,7 +94,7 @@ struct QCtl {
     unsigned int feed_tail;     // entries written so far (host, through the copy engine)
     int feed_open;              // host: more entries may come
     unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
-    unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated;
+    unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated, inband;
     unsigned long long dive_end_ns;  // %globaltimer when the first descent ended (diagnostics)
     unsigned long long idle_ns, busy_ns;  // summed over warps: time spent waiting for work / expanding records
     unsigned long long hist[MAXD + 1];
@@ -111,6 +115,7 @@ struct Params {
     const double *Rm;       // n x n upper triangular, Rm[j*n+i] = q_j . b_i
     const double *QTp;      // m
     double radius;
+    double radius_lp;       // the radius the node LPs prune against: radius, or radius * (1 + SOUND_MARGIN) in sound mode
     const int64_t *lat;     // n x m
     const int64_t *con;     // m x 2
     QCtl *q;
@@ -1081,7 +1086,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
 #pragma unroll 1
             for (;;) {
                 int art = 0;
-                double rad = P.radius;
+                double rad = P.radius_lp;
                 if (s.qd < qd0) {
                     lp_extend(s);
                     if (cold) { lp_values<!BIG>(s); art = s.val[s.qd - 1] > 0.0 ? 1 : -1; if (s.qd < qd0) rad = INFINITY; }
@@ -1104,6 +1109,7 @@ __device__ __forceinline__ int expand_impl(const Params &P, WS &s, const unsigne
                 status = NODE_PRUNE;
             }
             if (status == NODE_EXPLORE) {  // real centre of the next level: x_{kk-1} of the optimum
+                if (P.radius_lp != P.radius && !approxLE(d, P.radius)) CTR(s, C_INBAND);  // kept by the sound margin alone
                 gn = fma(-(double)ucur, Rk1k, g2);
                 xlast = (gn - s.v[qd0]) / Rk1;
             }
@@ -1462,7 +1468,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         atomicAdd(&q->niter, s.ctr[C_NITER]); atomicAdd(&q->nprune, s.ctr[C_NPRUNE]); atomicAdd(&q->nodes, s.ctr[C_NODES]);
         atomicAdd(&q->donated, s.ctr[C_DONATED]);
         atomicAdd(&q->pivots, s.ctr[C_PIVOTS]); atomicAdd(&q->quick, s.ctr[C_QUICK]); atomicAdd(&q->refactors, s.ctr[C_REFAC]);
-        atomicAdd(&q->colds, s.ctr[C_COLDS]);
+        atomicAdd(&q->colds, s.ctr[C_COLDS]); atomicAdd(&q->inband, s.ctr[C_INBAND]);
         atomicAdd(&q->idle_ns, s.ctr[C_IDLE_NS] + (gtimer() - t_mark)); atomicAdd(&q->busy_ns, s.ctr[C_BUSY_NS]);
     }
     __syncwarp();
@@ -1838,7 +1844,7 @@ __global__ void __launch_bounds__(384, 1) bltcu_batch_kernel(const BatchParams B
             inst = __shfl_sync(FULLMASK, inst, 0);
             radius = __shfl_sync(FULLMASK, radius, 0);
             P.lat = BP.lat + (size_t)inst * n * m; P.con = BP.con + (size_t)inst * 2 * m; P.sol = BP.sol + (size_t)inst * n;
-            P.radius = radius;
+            P.radius = radius; P.radius_lp = radius;
             P.q = oq;
             // a handed-over subtree belongs to a shared problem: its order no longer matters (see the second pass on the
             // host), so it is expanded eagerly, which produces the records other idle warps are waiting for
@@ -2189,6 +2195,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     CK(cudaStreamSynchronize(st));
     if ((int)(now_rc[1] & 0xffffffffu) != 0) return BLTCU_STATUS_LP_FAIL;  // dependent basis rows
     P.radius = (double)(con0[1] - con0[0]) / 2.0;
+    P.radius_lp = o.sound ? P.radius * (1.0 + SOUND_MARGIN) : P.radius;
     {
         long long tmo = o.timeout_ms;
         if (tmo <= 0) { const char *e = getenv("BLTCU_TIMEOUT_MS"); if (e) tmo = atoll(e); }
@@ -2228,7 +2235,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     memset(&acc, 0, sizeof acc);
     auto add_counts = [&](const QCtl &x) {
         acc.niter += x.niter; acc.nprune += x.nprune; acc.nodes += x.nodes; acc.pivots += x.pivots; acc.quick += x.quick;
-        acc.refactors += x.refactors; acc.colds += x.colds; acc.donated += x.donated; acc.idle_ns += x.idle_ns; acc.busy_ns += x.busy_ns;
+        acc.refactors += x.refactors; acc.colds += x.colds; acc.donated += x.donated; acc.inband += x.inband; acc.idle_ns += x.idle_ns; acc.busy_ns += x.busy_ns;
         for (int i = 0; i <= n; ++i) acc.hist[i] += x.hist[i];
     };
     auto launch = [&]() -> int {
@@ -2418,6 +2425,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         stats->launches = launches;
         stats->warps = nwarps; stats->ctas = ctas;
         stats->scratch_bytes = L.total;
+        stats->inband = acc.inband;
         stats->stopped = (!found && host_stop && *host_stop) ? 1 : 0;
         stats->gpus = 1;
         stats->best_valid = have_key ? 1 : 0;
@@ -2504,7 +2512,7 @@ static int closest_multi_device(const int64_t *lat, const int64_t *con, int n, i
         for (int r = 0; r < gpus; ++r) {
             stats->niter += st[r].niter; stats->nprune += st[r].nprune; stats->nodes += st[r].nodes; stats->pivots += st[r].pivots;
             stats->quick_prunes += st[r].quick_prunes; stats->refactors += st[r].refactors; stats->cold_starts += st[r].cold_starts;
-            stats->donated += st[r].donated; stats->launches += st[r].launches; stats->warps += st[r].warps; stats->ctas += st[r].ctas;
+            stats->donated += st[r].donated; stats->inband += st[r].inband; stats->launches += st[r].launches; stats->warps += st[r].warps; stats->ctas += st[r].ctas;
             stats->scratch_bytes += st[r].scratch_bytes;
             for (int i = 0; i <= n; ++i) stats->hist[i] += st[r].hist[i];
             stats->kernel_ms = std::max(stats->kernel_ms, st[r].kernel_ms);
@@ -2934,6 +2942,7 @@ extern "C" int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int
     P.donate_min_level = std::min(6, std::max(2, n / 3));
     P.no_early_exit = 0;
     P.radius = (double)(con[1] - con[0]) / 2.0;  // closest.cc:193-194: row 0 only
+    P.radius_lp = P.radius;
 
     cudaStream_t st = 0;  // legacy default stream: creating a stream would be an allocation
     CK(cudaMemcpyAsync(d_lat, lat, (size_t)n * m * 8, cudaMemcpyHostToDevice, st));

@@ -18,7 +18,7 @@ class Opts(ctypes.Structure):
     _fields_ = [("device", ctypes.c_int), ("rank", ctypes.c_int), ("world", ctypes.c_int),
                 ("split_depth", ctypes.c_int), ("donate_min_level", ctypes.c_int), ("no_early_exit", ctypes.c_int),
                 ("warps_per_cta", ctypes.c_int), ("ctas", ctypes.c_int), ("timeout_ms", ctypes.c_int),
-                ("eager", ctypes.c_int), ("gpus", ctypes.c_int), ("stop_flag", ctypes.c_void_p)]
+                ("eager", ctypes.c_int), ("sound", ctypes.c_int), ("gpus", ctypes.c_int), ("stop_flag", ctypes.c_void_p)]
 
 
 class Stats(ctypes.Structure):
@@ -29,7 +29,7 @@ class Stats(ctypes.Structure):
                 ("total_ms", ctypes.c_double), ("found", ctypes.c_int), ("launches", ctypes.c_int),
                 ("warps", ctypes.c_int), ("ctas", ctypes.c_int), ("scratch_bytes", ctypes.c_uint64),
                 ("busy_frac", ctypes.c_double), ("best_key", ctypes.c_uint16 * MAX_DIM), ("best_valid", ctypes.c_int),
-                ("stopped", ctypes.c_int), ("gpus", ctypes.c_int)]
+                ("stopped", ctypes.c_int), ("gpus", ctypes.c_int), ("inband", ctypes.c_uint64)]
 
 
 def lib() -> ctypes.CDLL:
@@ -61,6 +61,8 @@ def lib() -> ctypes.CDLL:
         L.bltcu_lll_fixed_host.restype = ctypes.c_int
         L.bltcu_check_soln.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
         L.bltcu_check_soln.restype = ctypes.c_int
+        L.bltcu_yprune.argtypes = [i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
+        L.bltcu_yprune.restype = ctypes.c_int
         L.bltcu_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
         L.bltcu_infdist.restype = ctypes.c_int
         L.bltcu_closest_noalloc.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.c_int, i64p, u64p, u64p,
@@ -100,7 +102,7 @@ def _stats_dict(rc, sol, st, n):
                 total_ms=float(st.total_ms), found=bool(st.found), launches=int(st.launches), warps=int(st.warps),
                 ctas=int(st.ctas), scratch_bytes=int(st.scratch_bytes), busy_frac=float(st.busy_frac),
                 best_key=np.array(list(st.best_key)[:n], dtype=np.int64) if st.best_valid else None,
-                stopped=bool(st.stopped), gpus=int(st.gpus))
+                stopped=bool(st.stopped), gpus=int(st.gpus), inband=int(st.inband))
 
 
 def closest(lat, con, **opts):
@@ -167,6 +169,19 @@ def check_soln(lat, con, u) -> bool:
     if rc != BLT_STATUS_OK:
         raise RuntimeError(f"bltcu_check_soln failed with status {rc}")
     return bool(ok.value)
+
+
+def yprune(lat, u, k: int, con):
+    """yprune() of libblt/yices_wrapper.h:26-34 without Yices: the exact decision whether the layer with u[k:] fixed meets
+    the cube (host, Fourier-Motzkin in 128-bit integers, k <= 6).  Returns (rc, decision): rc LP_OK 20 / LP_ERROR 21,
+    decision BLT_CHECK_SAT 10 (keep) / BLT_CHECK_UNSAT 11 (prune) / BLT_CHECK_UNKNOWN 12."""
+    lat = _i64(lat)
+    u = _i64(u)
+    con = _i64(con)
+    n, m = lat.shape
+    d = ctypes.c_int(0)
+    rc = lib().bltcu_yprune(_p(lat, ctypes.c_int64), n, m, _p(u, ctypes.c_int64), k, _p(con, ctypes.c_int64), ctypes.byref(d))
+    return rc, int(d.value)
 
 
 def infdist(B, u, k: int, p):

@@ -27,8 +27,9 @@ typedef struct SolvState_internal_ *CSolvState; /* a bookmark in the assumption 
 extern "C" {
 #endif
 
-/* libblt/blt.cc:25-28.  enable_yices != 0 asks for sound mode; this build has no Yices, so blt_check() then fails
- * with BLT_STATUS_ERROR exactly like the reference does when libyices.so cannot be loaded (context.cc:211-226). */
+/* libblt/blt.cc:25-28.  enable_yices != 0 asks for sound mode (run_blt -y).  The reference then consults Yices on every
+ * LP prune (closest.cc:258-267); this build needs no libyices.so: the GPU search prunes a layer only when the LP's dual
+ * bound is clear of the radius by a margin far above its rounding error, and keeps it otherwise (bltcu_opts.sound). */
 CContext blt_init(int enable_yices);
 /* libblt/blt.cc:30-35: a fresh (or the existing) variable of that name as an expression. */
 CExpr blt_var(CContext, const char *);

@@ -40,6 +40,9 @@ typedef struct bltcu_opts {
                             BLTCU_TIMEOUT_MS, else none) */
     int eager;           /* explored children a warp collects on one level before it descends into the first (0 = default;
                             1 = each warp descends at once, the reference's depth-first order inside a subtree) */
+    int sound;           /* 1 = sound pruning (the reference's -y mode, closest.cc:258-267, without Yices): a layer is pruned
+                            only when the LP's dual bound clears the radius by a margin far above its floating-point
+                            error; layers inside that margin are kept (counted in bltcu_stats.inband) */
     int gpus;            /* bltcu_closest_ex() with world <= 1: search on this many devices (device, device+1, ...) from
                             this one process, a host thread and a share of the subtrees each, results merged before the
                             call returns (0 = environment variable BLT_GPUS, else 1) */
@@ -75,6 +78,7 @@ typedef struct bltcu_stats {
     int best_valid;        /* 1 = a leaf was recorded by this rank (best_key and sol are meaningful) */
     int stopped;           /* 1 = this rank ended early because another rank set the stop flag */
     int gpus;              /* devices that took part (bltcu_closest_ex with opts.gpus / BLT_GPUS) */
+    uint64_t inband;       /* sound mode: layers kept only because of the safety margin */
 } bltcu_stats;
 
 /* closest(): libblt/closest.h:50-54, libblt/closest.cc:166-327.
@@ -116,6 +120,14 @@ int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank);
  * what a loop over bltcu_lll() gives; a problem whose numbers outgrow 512 bits is reduced by bltcu_lll() on the host
  * (stats->found, if stats is not NULL, reports how many).  Returns BLT_STATUS_OK / INPUT_ERROR / ERROR. */
 int bltcu_lll_batch(int64_t *B, int64_t *U, int count, int r, int c, int *rank, int device, bltcu_stats *stats);
+
+/* yprune(): libblt/yices_wrapper.h:26-34, libblt/yices_wrapper.cc:47-157 -- the exact decision the reference's sound
+ * mode asks of Yices: does the layer with coefficients u[k..n) fixed meet the cube?  Decided on the host by
+ * Fourier-Motzkin elimination in exact 128-bit integers (no Yices).  *decision = BLT_CHECK_SAT (keep) / BLT_CHECK_UNSAT
+ * (prune); returns LP_OK.  Layers with more than BLTCU_YPRUNE_MAX_K free coefficients, or whose elimination outgrows
+ * its limits, give BLT_CHECK_UNKNOWN and LP_ERROR like a solver failure in the reference. */
+#define BLTCU_YPRUNE_MAX_K 6
+int bltcu_yprune(const int64_t *lat, int n, int m, const int64_t *u, int k, const int64_t *con, int *decision);
 
 /* check_soln(): libblt/closest.cc:330-340, evaluated on the device (int64, wraps like the reference). */
 int bltcu_check_soln(const int64_t *lat, const int64_t *con, int n, int m, const int64_t *u, int *ok);

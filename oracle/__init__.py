@@ -49,6 +49,10 @@ def lib() -> ctypes.CDLL:
         L.oracle_check_soln.restype = ctypes.c_int
         L.oracle_infdist.argtypes = [f64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, f64p, f64p, f64p]
         L.oracle_infdist.restype = ctypes.c_int
+        L.oracle_set_sound.argtypes = [ctypes.c_double]
+        L.oracle_set_sound.restype = None
+        L.oracle_inband.argtypes = []
+        L.oracle_inband.restype = ctypes.c_uint64
         _LIB = L
     return _LIB
 
@@ -61,7 +65,7 @@ def _p(a, t):
     return a.ctypes.data_as(ctypes.POINTER(t))
 
 
-def closest(lat, con, max_nodes: int = 0):
+def closest(lat, con, max_nodes: int = 0, sound: bool = False):
     """closest() of libblt/closest.cc:166-327.  Returns dict(rc, sol, niter, nprune, hist, pivots, ...)."""
     lat = _i64(lat)
     con = _i64(con)
@@ -75,12 +79,13 @@ def closest(lat, con, max_nodes: int = 0):
     nprune = ctypes.c_uint64(0)
     hist = np.zeros(n + 1, dtype=np.uint64)
     stats = np.zeros(4, dtype=np.uint64)
+    lib().oracle_set_sound(1.0e-6 if sound else 0.0)   # SOUND_MARGIN of blt_b200/csrc/search.cu
     rc = lib().oracle_closest(_p(lat, ctypes.c_int64), _p(con, ctypes.c_int64), n, m, _p(sol, ctypes.c_int64),
                               ctypes.byref(niter), ctypes.byref(nprune), _p(hist, ctypes.c_uint64),
                               _p(stats, ctypes.c_uint64), ctypes.c_uint64(max_nodes))
     return dict(rc=rc, sol=sol, niter=int(niter.value), nprune=int(nprune.value), hist=hist,
                 pivots=int(stats[0]), refactors=int(stats[1]), quick=int(stats[2]), colds=int(stats[3]),
-                nodes=int(hist.sum()))
+                nodes=int(hist.sum()), inband=int(lib().oracle_inband()))
 
 
 def check_soln(lat, con, u) -> bool:

@@ -586,6 +586,13 @@ static void chain_load(LP *lp, const Chain *ch, int qd) {
     for (int p = 1; p < qd; ++p) if (lp->zrow[p] >= 0) lp->pos[lp->zrow[p]] = p;
 }
 
+/* Sound mode (bltcu_opts.sound): the node LPs prune against radius * (1 + margin); 0 = the reference's plain rule.
+ * The reference's own sound mode asks Yices about every LP prune (closest.cc:258-267); Yices is not available here. */
+static double g_sound_margin = 0.0;
+static uint64_t g_inband = 0;
+void oracle_set_sound(double margin) { g_sound_margin = margin; }
+uint64_t oracle_inband(void) { return g_inband; }
+
 int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter_out,
                    uint64_t *nprune_out, uint64_t *hist, uint64_t *stats, uint64_t max_nodes) {
     if (n <= 0 || m <= 0 || m < n) return BLT_STATUS_INPUT_ERROR; /* closest.cc:173-177 */
@@ -594,6 +601,8 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
     double *p = (double *)malloc((size_t)m * sizeof(double));
     for (int j = 0; j < m; ++j) p[j] = (double)(con[2 * j + 1] + con[2 * j]) / 2.0; /* closest.cc:180-185 */
     const double radius = (double)(con[1] - con[0]) / 2.0;                          /* closest.cc:193-194: row 0 only */
+    const double radius_lp = g_sound_margin > 0.0 ? radius * (1.0 + g_sound_margin) : radius;
+    g_inband = 0;
 
     Geo g;
     uint64_t counter = 0, nprune = 0, nodes = 0;
@@ -685,11 +694,12 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
             } else chain_load(lp, &ch[k][side], qd);
             memcpy(lp->chat, chatL[k], (qd - 1) * sizeof(double));
             lp->chat[qd - 1] = clast;
-            status = lp_solve_art(lp, radius, cmax, &d, art);
-            if (status == NODE_FAIL) status = lp_cold_solve(lp, qd, radius, cmax, &d); /* warm start went bad: from scratch */
+            status = lp_solve_art(lp, radius_lp, cmax, &d, art);
+            if (status == NODE_FAIL) status = lp_cold_solve(lp, qd, radius_lp, cmax, &d); /* warm start went bad: from scratch */
             if (status == NODE_FAIL) { rc = BLT_STATUS_LP_FAIL; goto done; }
             chain_store(&ch[k][side], lp);
             if (status == NODE_EXPLORE) { /* real centre of the next level: x_{kk-1} of the optimum */
+                if (radius_lp != radius && !approximatelyLE(d, radius, DIST_EPS)) g_inband++;
                 /* next coordinate of the rotated right-hand side: the part fixed by the levels above (32-lane order),
                  * then this level's own coefficient */
                 double part[32];

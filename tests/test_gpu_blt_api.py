@@ -105,12 +105,24 @@ def test_incremental_check_and_backtrack(api):  # test_context.cc:123-143 + blt_
     ctx.free()
 
 
-def test_yices_request_fails_like_missing_library(api):  # context.cc:211-226
-    ctx = api.Context(1)
-    x = ctx.var("x")
-    ctx.assume(0, x, 3)
-    assert ctx.check() == 1  # BLT_STATUS_ERROR
-    ctx.free()
+def test_sound_mode_request_selects_the_gpu_sound_search(api):  # blt_init(1), run_blt -y; context.cc:210-228, closest.cc:258-267
+    """The reference needs libyices.so for this and fails without it; here sound mode is the search kernel's own
+    (a prune needs a bound clear of the radius).  Decisions and models must be those of the plain mode."""
+    for name, rows, names, want in CASES[:6]:
+        ctx = api.Context(1)
+        v = [ctx.var(nm) for nm in names]
+        for lo, coef, hi, const in rows:
+            e = ctx.const(const)
+            for c, x in zip(coef, v):
+                if c != 0:
+                    e = e + c * x
+            assert ctx.assume(lo, e, hi) == 0
+        assert ctx.check() == want, name
+        if want == SAT:
+            x = [ctx.model(nm)[1] for nm in names]
+            for lo, coef, hi, const in rows:
+                assert lo <= sum(c * xi for c, xi in zip(coef, x)) + const <= hi
+        ctx.free()
 
 
 def test_tof(api):  # libblt/test_expr.cc: round(2/7 * (4x + y + 2/7)) -> x:1, y:0, const 0

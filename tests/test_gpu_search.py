@@ -197,3 +197,23 @@ def test_first_dive_reaches_the_babai_point(gpu, golden, name):
     assert (got["sol"] == z[f"sol_{name}"]).all()
     full = gpu.closest(lat, con)
     assert full["rc"] == 0 and full["found"] and oracle.check_soln(lat, con, full["sol"])
+
+
+def test_sound_mode_keeps_layers_inside_the_safety_margin(gpu):
+    """bltcu_opts.sound (the reference's -y mode, closest.cc:258-267, without Yices).  Two layers of this instance lie at
+    distance 29,999,999.5 and 30,000,000.5 from the centre with radius 29,996,985.5: beyond the 1e-4 band by less
+    than one part in 10^6.  The plain search prunes them (5 solves), the sound search keeps them (11 solves, 2 layers
+    counted as in-band); both equal the oracle run the same way.  On an ordinary instance the modes coincide."""
+    lat = np.array([[1000000000, 0], [0, 30000000]], dtype=np.int64)
+    con = np.array([[500000000 - 29996985, 500000000 + 29996986], [-29996985, 29996986]], dtype=np.int64)
+    for sound in (0, 1):
+        ref = oracle.closest(lat, con, sound=bool(sound))
+        got = gpu.closest(lat, con, sound=sound)
+        assert got["rc"] == ref["rc"] == 0 and not got["found"]
+        assert (got["niter"], got["nprune"], got["nodes"], got["inband"]) == (ref["niter"], ref["nprune"], ref["nodes"], ref["inband"])
+        assert (got["nodes"], got["inband"]) == ((11, 2) if sound else (5, 0))
+    A, C = dense_bilp(20, 110, 5)
+    lat, con, _ = reduced_search_input(A, C)
+    ref = oracle.closest(lat, con, sound=True)
+    got = gpu.closest(lat, con, sound=1)
+    assert (got["niter"], got["nprune"], got["pivots"], got["inband"]) == (ref["niter"], ref["nprune"], ref["pivots"], 0)

@@ -121,3 +121,53 @@ def test_run_blt_cli_errors(tmp_path):
     assert r.returncode == 1 and "cannot parse input file" in r.stderr
     r = subprocess.run([RUN_BLT], capture_output=True, text=True)
     assert r.returncode == 1 and "Usage:" in r.stdout
+
+
+# ---- exact layer-meets-cube decision (the reference's Yices known answers, libblt/test_yices.cc:37-123) -------------
+def _cube(p, b):
+    return [[pi - b, pi + b] for pi in p]
+
+
+def test_yprune_2d_known_answers():
+    import blt_b200
+    B = [[8, 4], [4, 8]]
+    assert blt_b200.yprune(B, [0, 1], 1, _cube([4, 4], 2)) == (20, 11)      # farther than 2: prune
+    assert blt_b200.yprune(B, [0, 1], 1, _cube([4, 4], 3)) == (20, 10)      # not farther than 3, just barely: keep
+    assert blt_b200.yprune(B, [0, 1], 1, _cube([4, 4], 1000)) == (20, 10)
+    for u1 in range(-10, 11):
+        assert blt_b200.yprune(B, [0, u1], 1, _cube([4, 4], 4)) == (20, 10 if u1 in (0, 1) else 11)
+
+
+def test_yprune_3d_known_answers():
+    import blt_b200
+    B = [[1, 0, 3], [0, 2, 1], [4, 4, -4]]
+    for u2 in range(-10, 11):
+        assert blt_b200.yprune(B, [0, 0, u2], 2, _cube([0, 0, 0], 4)) == (20, 10 if -1 <= u2 <= 1 else 11)
+
+
+def test_yprune_agrees_with_the_layer_distance_and_knows_its_limits():
+    """Property in the spirit of libblt/test_compare_glpk_yices.cc:47-104: exact UNSAT => the oracle's layer distance is
+    definitely larger than the radius, exact SAT => it is approximately <= the radius (1e-4, relative)."""
+    import numpy as np
+    import oracle
+    import blt_b200
+    rng = np.random.default_rng(7)
+    for _ in range(300):
+        n = int(rng.integers(2, 5))
+        B = rng.integers(-9, 10, size=(n, n))
+        if abs(np.linalg.det(B)) < 0.5:
+            continue
+        k = int(rng.integers(1, n))
+        u = rng.integers(-4, 5, size=n)
+        p = rng.integers(-20, 21, size=n)
+        b = int(rng.integers(1, 12))
+        rc, dec = blt_b200.yprune(B, u, k, _cube(list(p), b))
+        assert rc == 20 and dec in (10, 11)
+        orc, d, _ = oracle.infdist(B.astype(float), u, k, p.astype(float))
+        assert orc == 0
+        if dec == 11:
+            assert d > b * (1 - 1e-9)
+        else:
+            assert d <= b * (1 + 1e-4)
+    big = np.eye(8, dtype=np.int64)
+    assert blt_b200.yprune(big, [0] * 8, 7, _cube([0] * 8, 1)) == (21, 12)    # beyond BLTCU_YPRUNE_MAX_K: unknown
