@@ -43,6 +43,9 @@ def lib() -> ctypes.CDLL:
                                           ctypes.POINTER(ctypes.c_double)]
         L.blt_b200_last_stats.restype = ci
         L.blt_check_batch.argtypes, L.blt_check_batch.restype = [ctypes.POINTER(vp), ci, ctypes.POINTER(ci)], ci
+        L.blt_b200_solve_raw_files.argtypes = [ctypes.c_char_p, ctypes.c_char_p, ci, ctypes.POINTER(i64), ci, ctypes.POINTER(ci),
+                                               ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
+        L.blt_b200_solve_raw_files.restype = ci
         _LIB = L
     return _LIB
 
@@ -129,3 +132,15 @@ def check_batch(contexts):
     if rc != 0:
         raise RuntimeError(f"blt_check_batch failed with status {rc}")
     return list(res)
+
+
+def solve_raw_files(lat_path: str, con_path: str, sound: bool = False):
+    """solve_raw() of libblt/test_regression.cc:36-61 on two Boost-format matrix files (blt_b200_solve_raw_files).
+    Returns dict(rc, x, niter, nprune): rc BLT_CHECK_SAT 10 / BLT_CHECK_UNSAT 11 or a status code; x = coefficients of the
+    point with respect to the rows of the lattice file."""
+    cap = 4096
+    x = (ctypes.c_int64 * cap)()
+    rows, ni, npr = ctypes.c_int(0), ctypes.c_uint64(0), ctypes.c_uint64(0)
+    rc = lib().blt_b200_solve_raw_files(lat_path.encode(), con_path.encode(), 1 if sound else 0, x, cap, ctypes.byref(rows),
+                                        ctypes.byref(ni), ctypes.byref(npr))
+    return dict(rc=rc, x=[int(v) for v in x[:rows.value]], niter=int(ni.value), nprune=int(npr.value))

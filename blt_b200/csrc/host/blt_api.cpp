@@ -1,5 +1,6 @@
 // blt_api.cpp -- the twelve functions of blt.h (reference: libblt/blt.cc:22-120), same ownership rules:
 // every CExpr is owned by the library and freed by blt_free(); callers never free.
+#include <fstream>
 #include <map>
 #include <mutex>
 #include <string>
@@ -85,6 +86,25 @@ void blt_free(CContext ctx) {
     for (Expr *e : es) delete e;
     for (SolvState *s : ss) delete s;
     delete reinterpret_cast<Context *>(ctx);
+}
+
+// Extension (include/blt.h): solve_raw() of libblt/test_regression.cc:36-61 on two Boost-format matrix files.
+int blt_b200_solve_raw_files(const char *lat_path, const char *con_path, int sound, int64 *x, int x_cap, int *rows, uint64_t *niter,
+                             uint64_t *nprune) {
+    if (!lat_path || !con_path) return BLT_STATUS_INPUT_ERROR;
+    std::ifstream fl(lat_path), fc(con_path);
+    std::vector<int64> M, C, sol;
+    size_t r = 0, c = 0, cr = 0, cc = 0;
+    if (read_lattice(fl, M, r, c) != 0 || read_lattice(fc, C, cr, cc) != 0) return BLT_STATUS_INPUT_ERROR;
+    if (cc != 2 || cr != c) return BLT_STATUS_INPUT_ERROR;  // closest.cc:173-177
+    CheckStats st;
+    const int rc = solve_raw(M, r, c, C, sound, &sol, &st);
+    if (rows) *rows = (int)r;
+    if (niter) *niter = st.niter;
+    if (nprune) *nprune = st.nprune;
+    if (x && (rc == BLT_CHECK_SAT || rc == BLT_CHECK_UNSAT))
+        for (size_t i = 0; i < r && (int)i < x_cap; ++i) x[i] = sol[i];
+    return rc;
 }
 
 // Not in blt.h (the reference keeps SolverStats private): counters of the context's last blt_check().

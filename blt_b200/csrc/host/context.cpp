@@ -2,7 +2,9 @@
 // Plain C++17, no Boost.  The two hot seams go to the GPU library: bltcu_lll() and bltcu_closest_ex().
 #include "context.h"
 
+#include <ctype.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <chrono>
@@ -150,7 +152,37 @@ int convert_to_integral(const std::vector<rat64> &L0, const std::vector<rat64> &
     return BLT_STATUS_OK;
 }
 
+// BLT_CHECKED_STRETCH=1: the same scaling with every product checked in 128 bits; an lcm or a scaled entry beyond int64
+// is BLT_STATUS_INPUT_ERROR with a message instead of a silent wrap (the reference's heuristics at context.cc:470-474
+// miss some overflows: test_95.bilp needs a 73-bit lcm).  Off by default: wrap-faithful like the reference.
+static int stretch_to_cube_checked(std::vector<int64> &L, std::vector<int64> &C, size_t nrows, size_t ncols) {
+    typedef __int128 i128;
+    const i128 lim = (i128)INT64_MAX;
+    i128 l = 1;
+    for (size_t i = 0; i < ncols; ++i) {
+        const i128 r = (i128)C[2 * i + 1] - (i128)C[2 * i];
+        if (r <= 0) { ERROR("upper and lower bound coincide or conflict"); return BLT_STATUS_INPUT_ERROR; }
+        i128 a = l, b = r;
+        while (b) { const i128 t = a % b; a = b; b = t; }
+        l = l / a * r;
+        if (l > lim) { ERROR("stretch_to_cube: the common width (lcm of the row widths) does not fit 64 bits"); return BLT_STATUS_INPUT_ERROR; }
+    }
+    for (size_t i = 0; i < ncols; ++i) {
+        const i128 mult = l / ((i128)C[2 * i + 1] - (i128)C[2 * i]);
+        const i128 lo = (i128)C[2 * i] * mult, hi = (i128)C[2 * i + 1] * mult;
+        if (lo > lim || lo < -lim || hi > lim || hi < -lim) { ERROR("stretch_to_cube: a scaled bound does not fit 64 bits"); return BLT_STATUS_INPUT_ERROR; }
+        C[2 * i] = (int64)lo; C[2 * i + 1] = (int64)hi;
+        for (size_t j = 0; j < nrows; ++j) {
+            const i128 v = (i128)L[j * ncols + i] * mult;
+            if (v > lim || v < -lim) { ERROR("stretch_to_cube: a scaled coefficient does not fit 64 bits"); return BLT_STATUS_INPUT_ERROR; }
+            L[j * ncols + i] = (int64)v;
+        }
+    }
+    return BLT_STATUS_OK;
+}
+
 int stretch_to_cube(std::vector<int64> &L, std::vector<int64> &C, size_t nrows, size_t ncols) {  // context.cc:455-501
+    if (const char *e = getenv("BLT_CHECKED_STRETCH")) if (e[0] == '1') return stretch_to_cube_checked(L, C, nrows, ncols);
     int64 l = 1;
     for (size_t i = 0; i < ncols; ++i) {
         const int64 r = (int64)((uint64_t)C[2 * i + 1] - (uint64_t)C[2 * i]);
@@ -315,6 +347,68 @@ int check_batch(Context **ctx, int count, int *results) {
         }
     }
     return BLT_STATUS_OK;
+}
+
+// ---- Boost ublas matrix text, "[r,c]((a,b,..),(..),..)" (read_lattice, libblt/parser.cc:43-55): the legacy .lat/.con
+// files of test/data -------------------------------------------------------------------------------------------------
+int read_lattice(std::istream &in, std::vector<int64> &M, size_t &nr, size_t &nc) {
+    if (!in) { ERROR("could not open input stream for parsing"); return 1; }
+    auto skip = [&]() { while (in && isspace(in.peek())) in.get(); };
+    auto expect = [&](char c) { skip(); if (in.peek() != c) return false; in.get(); return true; };
+    long long r = 0, c = 0;
+    if (!expect('[') || !(in >> r) || !expect(',') || !(in >> c) || !expect(']') || r <= 0 || c <= 0 || !expect('(')) {
+        ERROR("malformed matrix header, expected [rows,cols](("); return 1;
+    }
+    nr = (size_t)r; nc = (size_t)c;
+    M.assign(nr * nc, 0);
+    for (size_t i = 0; i < nr; ++i) {
+        if (i && !expect(',')) { ERROR("malformed matrix: missing row separator"); return 1; }
+        if (!expect('(')) { ERROR("malformed matrix: missing row"); return 1; }
+        for (size_t j = 0; j < nc; ++j) {
+            if (j && !expect(',')) { ERROR("malformed matrix: short row"); return 1; }
+            long long v = 0;
+            if (!(in >> v)) { ERROR("malformed matrix: expecting an integer"); return 1; }
+            M[i * nc + j] = (int64)v;
+        }
+        if (!expect(')')) { ERROR("malformed matrix: long row"); return 1; }
+    }
+    if (!expect(')')) { ERROR("malformed matrix: missing end"); return 1; }
+    return 0;
+}
+
+// solve_raw() of libblt/test_regression.cc:36-61: LLL on the lattice as given (no stretch), closest(), exact check.
+// lat: r x c generating rows, con: c x 2.  x (r entries, may be NULL) receives the coefficients of the point with
+// respect to the ORIGINAL rows (sol * U).  Returns BLT_CHECK_SAT / BLT_CHECK_UNSAT or a status code.
+int solve_raw(const std::vector<int64> &lat, size_t r, size_t c, const std::vector<int64> &con, int sound, std::vector<int64> *x,
+              CheckStats *stats) {
+    using clk = std::chrono::steady_clock;
+    if (r == 0 || c == 0 || lat.size() != r * c || con.size() != 2 * c) return BLT_STATUS_INPUT_ERROR;
+    std::vector<int64> M = lat, U(r * r, 0);
+    int rank = 0;
+    auto t0 = clk::now();
+    int rc = bltcu_lll(M.data(), U.data(), (int)r, (int)c, &rank);
+    const double lll_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
+    if (rc != BLT_STATUS_OK) return rc;
+    if (rank == 0) return BLT_STATUS_INPUT_ERROR;
+    std::vector<int64> newL(M.begin() + (r - (size_t)rank) * c, M.end()), sol((size_t)rank, 0);
+    bltcu_stats st;
+    bltcu_opts opts;
+    memset(&opts, 0, sizeof opts);
+    opts.sound = sound ? 1 : 0;
+    t0 = clk::now();
+    rc = bltcu_closest_ex(newL.data(), con.data(), rank, (int)c, &opts, sol.data(), &st);
+    const double search_ms = std::chrono::duration<double, std::milli>(clk::now() - t0).count();
+    if (stats) { stats->niter = st.niter; stats->nprune = st.nprune; stats->rank = rank; stats->lll_ms = lll_ms; stats->search_ms = search_ms; }
+    if (rc != BLT_STATUS_OK) return rc;
+    if (x) {
+        x->assign(r, 0);
+        for (size_t j = 0; j < r; ++j) {
+            uint64_t acc = 0;
+            for (size_t i = r - (size_t)rank; i < r; ++i) acc += (uint64_t)sol[i - (r - (size_t)rank)] * (uint64_t)U[i * r + j];
+            (*x)[j] = (int64)acc;
+        }
+    }
+    return check_soln_host(newL, con, (size_t)rank, c, sol) ? BLT_CHECK_SAT : BLT_CHECK_UNSAT;
 }
 
 // ---- parser (libblt/parser.cc:72-166) -------------------------------------------------------------------------------

@@ -5,6 +5,7 @@
 
 #include <stdint.h>
 
+#include <istream>
 #include <map>
 #include <set>
 #include <string>
@@ -103,6 +104,9 @@ public:
 };
 typedef Context::Prepared Prepared;
 int check_batch(Context **ctx, int count, int *results);
+int read_lattice(std::istream &in, std::vector<int64> &M, size_t &nr, size_t &nc);   // libblt/parser.cc:43-55
+int solve_raw(const std::vector<int64> &lat, size_t r, size_t c, const std::vector<int64> &con, int sound, std::vector<int64> *x,
+              CheckStats *stats);                                                        // libblt/test_regression.cc:36-61
 
 // libblt/context.cc:405-501, on row-major vectors: L is nrows x ncols (rows = variables), C is ncols x 2
 int convert_to_integral(const std::vector<rat64> &L0, const std::vector<rat64> &C0, size_t nrows, size_t ncols,

@@ -29,6 +29,29 @@ static void print_usage(char *argv[]) {
 }
 
 int main(int argc, char *argv[]) {
+    // Extension: run_blt [-m] [-y] --latcon <file.lat> <file.con> solves a legacy lattice/constraint pair the way the
+    // reference's regression driver does (solve_raw, libblt/test_regression.cc:36-61); same PROBLEM line, same exit status.
+    for (int i = 1; i < argc; ++i) {
+        if (std::string(argv[i]) != "--latcon") continue;
+        if (i + 2 >= argc) { std::cerr << "Error: --latcon needs <file.lat> <file.con>" << std::endl; return 1; }
+        bool model = false, sound = false;
+        for (int j = 1; j < i; ++j) { if (std::string(argv[j]) == "-m") model = true; if (std::string(argv[j]) == "-y") sound = true; }
+        std::vector<int64> x(4096);
+        int rows = 0;
+        uint64_t ni = 0, np = 0;
+        const clock_t start = clock();
+        const int rc = blt_b200_solve_raw_files(argv[i + 1], argv[i + 2], sound ? 1 : 0, x.data(), (int)x.size(), &rows, &ni, &np);
+        const double elapsed = (1.0 * (clock() - start)) / CLOCKS_PER_SEC;
+        std::cout << "PROBLEM " << argv[i + 1] << " RUNTIME " << elapsed << " "
+                  << "niter " << "XXX" << " npru " << "XXX" << " " << "rc " << "XXX" << " check "
+                  << (rc == BLT_CHECK_SAT ? " SAT " : (rc == BLT_CHECK_UNSAT ? " UNSAT " : "INPUT_ERROR")) << std::endl;
+        if (const char *e = getenv("BLT_STATS")) if (e[0] == '1') std::cerr << "BLT_STATS niter " << ni << " nprune " << np << " rc " << rc << std::endl;
+        if (model && rc == BLT_CHECK_SAT) {
+            std::cout << "PROBLEM " << argv[i + 1] << " MODEL (";
+            for (int k = 0; k < rows; ++k) std::cout << x[k] << (k < rows - 1 ? ", " : ")\n");
+        }
+        return rc;
+    }
     bool do_model = false, do_version = false, do_yices = false;
     int opt;
     while ((opt = getopt(argc, argv, "mhvy")) != -1) {

@@ -68,6 +68,15 @@ int blt_check_batch(CContext *ctxs, int count, int *results);
  * times of the two seams.  Any pointer may be NULL. */
 int blt_b200_last_stats(CContext ctx, uint64_t *niter, uint64_t *nprune, int *rank, double *lll_ms, double *search_ms);
 
+/* Extension, no counterpart in blt.h: the reference's own regression driver solve_raw() (libblt/test_regression.cc:36-61)
+ * as a library call, for the legacy lattice/constraint pairs of test/data (test_95, test_50, test_50_8, test_4x4), whose
+ * .bilp forms cannot pass stretch_to_cube (73-bit lcm).  Reads two matrices in Boost ublas text format (read_lattice,
+ * libblt/parser.cc:43-55): lat_path r x c generating rows, con_path c x 2 bounds; exact LLL, closest(), exact check; no
+ * stretch.  x (x_cap entries, may be NULL) receives the coefficients of the point with respect to the rows of the file.
+ * Returns BLT_CHECK_SAT / BLT_CHECK_UNSAT or a BLT_STATUS_* code.  run_blt --latcon <lat> <con> calls it. */
+int blt_b200_solve_raw_files(const char *lat_path, const char *con_path, int sound, int64 *x, int x_cap, int *rows, uint64_t *niter,
+                             uint64_t *nprune);
+
 #ifdef __cplusplus
 }
 #endif

@@ -242,3 +242,35 @@ def test_reference_c_client_unchanged():
     r = subprocess.run([exe], capture_output=True, text=True, timeout=300)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "Tests pass!" in r.stdout
+
+
+@pytest.mark.parametrize("name", ["test_4x4", "test_95", "test_50", "test_50_8"])
+def test_run_blt_latcon_on_the_reference_fixtures(api, golden, name):
+    """The legacy lattice/constraint pairs of test/data through the PRODUCT (reader of the Boost matrix text,
+    libblt/parser.cc:43-55; solve_raw, libblt/test_regression.cc:36-61, :84-106): SAT, and the returned coefficients
+    give a point of the box when multiplied with the rows of the file."""
+    lat_p, con_p = f"{golden}/{name}.lat", f"{golden}/{name}.con"
+    r = api.solve_raw_files(lat_p, con_p)
+    assert r["rc"] == SAT
+    lat = np.array(bltio.read_boost(lat_p), dtype=object)
+    con = bltio.read_boost(con_p)
+    z = np.array(r["x"], dtype=object) @ lat
+    assert all(int(con[i][0]) <= int(z[i]) <= int(con[i][1]) for i in range(len(con)))
+    out = subprocess.run([RUN_BLT, "-m", "--latcon", lat_p, con_p], capture_output=True, text=True, timeout=300)
+    assert out.returncode == SAT and " SAT " in out.stdout and "MODEL (" in out.stdout
+    assert re.search(r"niter XXX npru XXX rc XXX", out.stdout)       # the reference's line, XXX and all (run_blt.cc:173-175)
+
+
+def test_checked_stretch_names_the_overflow(golden, tmp_path):
+    """test_50 as a .bilp (the transposed lattice with its bounds, what libblt/latcon2bilp.cc writes) needs a 73-bit lcm
+    in stretch_to_cube.  With BLT_CHECKED_STRETCH=1 the product says so and returns
+    BLT_STATUS_INPUT_ERROR (exit 3) instead of wrapping silently."""
+    lat = bltio.read_boost(f"{golden}/test_50.lat")
+    con = bltio.read_boost(f"{golden}/test_50.con")
+    bilp = tmp_path / "test_50.bilp"
+    with open(bilp, "w") as f:
+        for i in range(len(con)):
+            f.write(f"{int(con[i][0])} <= " + " ".join(str(int(lat[j][i])) for j in range(len(lat))) + f" <= {int(con[i][1])}\n")
+    env = dict(os.environ, BLT_CHECKED_STRETCH="1")
+    out = subprocess.run([RUN_BLT, str(bilp)], capture_output=True, text=True, timeout=300, env=env)
+    assert out.returncode == 3 and "does not fit 64 bits" in out.stderr

@@ -171,3 +171,17 @@ def test_yprune_agrees_with_the_layer_distance_and_knows_its_limits():
             assert d <= b * (1 + 1e-4)
     big = np.eye(8, dtype=np.int64)
     assert blt_b200.yprune(big, [0] * 8, 7, _cube([0] * 8, 1)) == (21, 12)    # beyond BLTCU_YPRUNE_MAX_K: unknown
+
+
+def test_boost_matrix_reader_rejects_malformed_files(tmp_path):
+    """read_lattice (libblt/parser.cc:43-55) of the product: bad input is BLT_STATUS_INPUT_ERROR before any GPU work."""
+    from blt_b200 import api
+    good_con = tmp_path / "c.con"
+    good_con.write_text("[2,2]((0,1),(0,1))")
+    for text in ("", "[2,2]((1,2),(3))", "[2,2]((1,2),(3,4)", "[0,2]()", "[2,2]((1,x),(3,4))"):
+        bad = tmp_path / "bad.lat"
+        bad.write_text(text)
+        assert api.solve_raw_files(str(bad), str(good_con))["rc"] == 3
+    lat = tmp_path / "l.lat"
+    lat.write_text("[2,3]((1,0,0),(0,1,0))")
+    assert api.solve_raw_files(str(lat), str(good_con))["rc"] == 3   # con must be c x 2 with c = 3 (closest.cc:173-177)
