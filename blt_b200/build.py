@@ -32,7 +32,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     from concurrent.futures import ThreadPoolExecutor
 
     os.makedirs(os.path.join(HERE, "lib", "obj"), exist_ok=True)
-    hdrs = [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h")]
+    hdrs = [os.path.join(HERE, "..", "include", "bltcu.h"), os.path.join(HERE, "csrc", "lll_fixed.h"), os.path.join(HERE, "csrc", "lll_fp.h")]
     newest_hdr = max(os.path.getmtime(h) for h in hdrs)
     stale = [src for src in SRC if force or not os.path.exists(_obj(src))
              or os.path.getmtime(_obj(src)) < max(os.path.getmtime(src), newest_hdr)]

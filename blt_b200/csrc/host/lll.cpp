@@ -18,6 +18,7 @@
 
 #include "../../../include/bltcu.h"
 #include "../lll_fixed.h"
+#include "../lll_fp.h"
 
 namespace {
 
@@ -324,6 +325,19 @@ extern "C" int bltcu_lll_arbitrary(int64_t *B, int64_t *U, int r, int c, int *ra
 // which one finished.
 extern "C" int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank) {
     if (!B || r <= 0 || c <= 0 || !rank) return BLTCU_STATUS_INPUT_ERROR;
+    // Fast pass (lll_fp.h): the same sequence of row operations with every decision taken in fp64 against a margin and
+    // every row operation in exact int64; it either completes with the integral algorithm's output or defers, leaving
+    // B untouched (independent rows only).  60 x 60 with entries up to 100: 5 ms against 90 ms for the passes below.
+    if (r <= c && !getenv("BLTCU_LLL_EXACT_ONLY")) {
+        std::vector<int64_t> b(B, B + (size_t)r * c), u((size_t)r * r, 0);
+        std::vector<double> work(lllfp::scratch_doubles(r));
+        if (lllfp::reduce_one(b.data(), u.data(), r, c, work.data(), lllfp::HostLanes()) == r) {
+            memcpy(B, b.data(), b.size() * 8);
+            if (U) memcpy(U, u.data(), u.size() * 8);
+            *rank = r;
+            return BLTCU_STATUS_OK;
+        }
+    }
     if ((long)r * c <= 128 * 128) {
         std::vector<int64_t> b((size_t)r * c), u((size_t)r * r);
         for (int pass = 0; pass < 2; ++pass) {

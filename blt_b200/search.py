@@ -59,6 +59,8 @@ def lib() -> ctypes.CDLL:
         L.bltcu_lll_arbitrary.restype = ctypes.c_int
         L.bltcu_lll_fixed_host.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int), ctypes.c_int]
         L.bltcu_lll_fixed_host.restype = ctypes.c_int
+        L.bltcu_lll_fp_host.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+        L.bltcu_lll_fp_host.restype = ctypes.c_int
         L.bltcu_check_soln.argtypes = [i64p, i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
         L.bltcu_check_soln.restype = ctypes.c_int
         L.bltcu_yprune.argtypes = [i64p, ctypes.c_int, ctypes.c_int, i64p, ctypes.c_int, i64p, ctypes.POINTER(ctypes.c_int)]
@@ -275,3 +277,17 @@ def lll_arbitrary(B):
     if rc != BLT_STATUS_OK:
         raise RuntimeError(f"bltcu_lll_arbitrary failed with status {rc}")
     return int(rk.value), B, U
+
+
+def lll_fp_host(B):
+    """Test seam: the floating-point pass of bltcu_lll_batch (decisions in fp64 with margins, row operations in exact
+    int64) executed on the host.  Returns (deferred, rank, B, U); deferred = True means the problem was left to the
+    multiprecision routine and B is returned unchanged."""
+    B = _i64(B).copy()
+    r, c = B.shape
+    U = np.zeros((r, r), dtype=np.int64)
+    rk = ctypes.c_int(0)
+    rc = lib().bltcu_lll_fp_host(_p(B, ctypes.c_int64), _p(U, ctypes.c_int64), r, c, ctypes.byref(rk))
+    if rc not in (0, 1):
+        raise RuntimeError(f"bltcu_lll_fp_host failed with status {rc}")
+    return bool(rc), int(rk.value), B, U

@@ -185,3 +185,38 @@ def test_boost_matrix_reader_rejects_malformed_files(tmp_path):
     lat = tmp_path / "l.lat"
     lat.write_text("[2,3]((1,0,0),(0,1,0))")
     assert api.solve_raw_files(str(lat), str(good_con))["rc"] == 3   # con must be c x 2 with c = 3 (closest.cc:173-177)
+
+
+def test_fp_decision_pass_of_the_lll_equals_the_exact_algorithm():
+    """lll_fp.h (host instantiation): decisions in fp64 against a margin, row operations in exact int64.  Wherever the
+    pass completes, basis, transform and rank are the oracle's exact integral LLL bit for bit; dependent generating sets
+    are always deferred; bltcu_lll (which tries this pass first) equals the oracle either way."""
+    import numpy as np
+    import blt_b200
+    from oracle.lll import lll as oracle_lll
+
+    def wrap(M):
+        return np.array([[((int(x) + 2**63) % 2**64) - 2**63 for x in row] for row in M], dtype=np.int64)
+
+    rng = np.random.default_rng(5)
+    done = deferred = 0
+    for r, c, amax, cnt in ((20, 20, 100, 60), (12, 12, 50, 40), (30, 30, 100, 8), (60, 60, 100, 1), (10, 14, 1000, 20), (5, 5, 3, 40)):
+        for _ in range(cnt):
+            B = rng.integers(-amax, amax + 1, size=(r, c))
+            ork, oB, oU = oracle_lll([[int(x) for x in row] for row in B])
+            d, rk, Bf, Uf = blt_b200.lll_fp_host(B)
+            if d:
+                deferred += 1
+                assert (Bf == B).all()
+            else:
+                done += 1
+                assert rk == ork == r and (Bf == wrap(oB)).all() and (Uf == wrap(oU)).all()
+            rk2, B2, U2 = blt_b200.lll(B)
+            assert rk2 == ork and (B2 == wrap(oB)).all() and (U2 == wrap(oU)).all()
+    assert done > 100 and deferred < done // 4
+    for _ in range(3):   # 40 vectors of rank 20: the dependent-row branch belongs to the multiprecision routine
+        assert blt_b200.lll_fp_host(rng.integers(-100, 101, size=(40, 20)))[0]
+    B = np.array([[1, 2], [2, 4]])                       # dependent rows of a square matrix
+    assert blt_b200.lll_fp_host(B)[0]
+    B = np.array([[3, 1], [1, 1]]) * 2**40               # inner products beyond 2^53
+    assert blt_b200.lll_fp_host(B)[0]
