@@ -127,8 +127,10 @@ def batch_supplement(blt_b200):
     t1 = time.perf_counter()
     _, _, _, linfo = blt_b200.lll_batch(Bs)
     dt_l = time.perf_counter() - t1
-    lll = {"workload": "4000 exact LLL reductions of 20x20 integer bases, entries in [-100, 100], one warp each",
-           "problems_per_s": len(Bs) / dt_l, "kernel_ms": linfo["kernel_ms"], "e2e_ms": 1e3 * dt_l, "on_host": linfo["on_host"]}
+    lll = {"workload": "4000 exact LLL reductions of 20x20 integer bases, entries in [-100, 100], one warp each: fp64 decisions + "
+                       "exact int64 row operations, deferred problems through the 512-bit kernel",
+           "problems_per_s": len(Bs) / dt_l, "kernel_ms": linfo["kernel_ms"], "e2e_ms": 1e3 * dt_l, "deferred": linfo["deferred"],
+           "on_host": linfo["on_host"], "hbm_gb_per_s": len(Bs) * 8 * (2 * 20 * 20 + 2 * 20 * 20) / (linfo["kernel_ms"] * 1e-3) / 1e9}
     # time-to-decision on the reference's own SAT regression fixtures (64 x 64, LLL-reduced; SURVEY.md 8d metric ii)
     sat = []
     zj = np.load(os.path.join(ROOT, "tests", "golden", "jpeg_reduced.npz"))
@@ -395,17 +397,17 @@ def main():
                 "clocks": sampler.summary()}
         if world == 1:
             line["batch"] = batch_supplement(blt_b200)
-            prof = os.path.join(ROOT, "profiles", "r1_final_summary.json")
+            prof = os.path.join(ROOT, "profiles", "r2_final_summary.json")
             if os.path.exists(prof):  # dram bytes of the search kernel from the committed ncu --set full capture
                 pj = json.load(open(prof))
                 if pj.get("fixture") == os.path.basename(FIXTURE):
                     line["roofline"]["traffic"] = pj.get("dram_bytes_per_launch")
-                    line["roofline"]["traffic_source"] = "profiles/r1_final_summary.json (ncu --set full, one launch)"
+                    line["roofline"]["traffic_source"] = "profiles/r2_final_summary.json (ncu --set full, one launch)"
                 elif pj.get("dram_bytes_per_node"):
                     # the capture was taken on a smaller instance of the same workload (a replay of this one outlasts
                     # the search's watchdog): scaled by the node count, and said so
                     line["roofline"]["traffic"] = pj["dram_bytes_per_node"] * nodes_all / args.steps
-                    line["roofline"]["traffic_source"] = (f"profiles/r1_final_summary.json: {pj['dram_bytes_per_node']:.0f} B/node measured "
+                    line["roofline"]["traffic_source"] = (f"profiles/r2_final_summary.json: {pj['dram_bytes_per_node']:.0f} B/node measured "
                                                           f"by ncu --set full on {pj.get('fixture')}, times the nodes of this launch")
         if not args.no_cpu and world == 1:
             v, cn, dt = cpu_sample(wl, args.cpu_nodes)

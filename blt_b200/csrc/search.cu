@@ -853,11 +853,17 @@ __device__ __forceinline__ void chain_load(WS &s, const double *dH, const int *d
     const int LD = s.LD;
     s.qd = q;
     if (q <= 32) {
-        if (s.lane < q) {
+        if (s.lane < q) {  // eight loads in flight per lane (the source is global memory)
             const double *src = dH + s.lane;
             double *dst = s.W + s.lane;
 #pragma unroll 1
-            for (int i = 0; i < q; ++i) dst[(size_t)i * LD] = src[(size_t)i * q];
+            for (int i = 0; i < q; i += 8) {
+                double v[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = i + e < q ? src[(size_t)(i + e) * q] : 0.0;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) if (i + e < q) dst[(size_t)(i + e) * LD] = v[e];
+            }
         }
     } else {
 #pragma unroll 1
@@ -949,11 +955,22 @@ __device__ __forceinline__ void use_side(WS &s, int side) {
     if (BIG) { s.W = side ? s.Wg_b : s.Wg_a; s.LD = s.LDG; } else { s.W = side ? s.Ws_b : s.Ws_a; s.LD = s.LDS; }
     s.zrow = side ? s.zrow_b : s.zrow_a; s.pos = side ? s.pos_b : s.pos_a; s.sg = side ? s.sg_b : s.sg_a;
 }
+// Four loads in flight per lane before the first store: a rolled load-store loop pays one L2 round trip per iteration.
 __device__ __forceinline__ void copy_words(void *dst, const void *src, size_t bytes, int lane) {  // bytes % 8 == 0
     unsigned long long *d = (unsigned long long *)dst;
     const unsigned long long *s = (const unsigned long long *)src;
+    const size_t nw = bytes / 8;
 #pragma unroll 1
-    for (size_t i = lane; i < bytes / 8; i += 32) d[i] = s[i];
+    for (size_t i = lane; i < nw; i += 128) {
+        const unsigned long long v0 = s[i];
+        const unsigned long long v1 = i + 32 < nw ? s[i + 32] : 0ull;
+        const unsigned long long v2 = i + 64 < nw ? s[i + 64] : 0ull;
+        const unsigned long long v3 = i + 96 < nw ? s[i + 96] : 0ull;
+        d[i] = v0;
+        if (i + 32 < nw) d[i + 32] = v1;
+        if (i + 64 < nw) d[i + 64] = v2;
+        if (i + 96 < nw) d[i + 96] = v3;
+    }
 }
 // writes the record of an explored child (children level k-1) whose vertex is the current working state
 __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL, WS &s, unsigned char *C, int k, double xlast,

@@ -241,8 +241,8 @@ def lll(B):
 
 def lll_batch(Bs, device: int = 0):
     """Batched LLL on the GPU (bltcu_lll_batch): Bs is count x r x c.  Returns (ranks, reduced Bs, Us, info) with the same
-    bases and transforms a loop over lll() gives; info has kernel_ms, total_ms and on_host (problems whose numbers
-    outgrew the kernel's 512-bit integers and were reduced by the host implementation)."""
+    bases and transforms a loop over lll() gives; info has kernel_ms, total_ms, deferred (problems the fp64-decision pass
+    left to the 512-bit kernel) and on_host (problems whose numbers outgrew 512 bits: reduced by the host routine)."""
     Bs = _i64(Bs).copy()
     if Bs.ndim != 3:
         raise ValueError("lll_batch wants Bs (count, r, c)")
@@ -254,7 +254,8 @@ def lll_batch(Bs, device: int = 0):
                                ctypes.byref(st))
     if rc != BLT_STATUS_OK:
         raise RuntimeError(f"bltcu_lll_batch failed with status {rc}")
-    return ranks, Bs, Us, dict(kernel_ms=float(st.kernel_ms), total_ms=float(st.total_ms), on_host=int(st.found))
+    return ranks, Bs, Us, dict(kernel_ms=float(st.kernel_ms), total_ms=float(st.total_ms), on_host=int(st.found),
+                              deferred=int(st.donated), launches=int(st.launches))
 
 
 def lll_fixed_host(B, limbs: int = 16):
