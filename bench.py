@@ -356,6 +356,26 @@ def main():
         e2e_search_ms += r["search_ms"]
     sampler.stop_flag = True
 
+    # BASELINE.json config 5 at N > 1: 10,000 instances of 20 x 20, whole problems sharded over the ranks (supplementary)
+    batch10k = None
+    if world > 1:
+        from blt_b200.dist import closest_batch_sharded
+        zb = np.load(os.path.join(ROOT, "tests", "golden", "batch20.npz"))
+        lats = np.ascontiguousarray(np.tile(zb["lat"], (25, 1, 1)))
+        cons = np.ascontiguousarray(np.tile(zb["con"], (25, 1, 1)))
+        closest_batch_sharded(lats[:400 * world], cons[:400 * world], device=local_rank)
+        barrier()
+        tb = time.perf_counter()
+        rb = closest_batch_sharded(lats, cons, device=local_rank)
+        barrier()
+        dtb = torch.tensor([time.perf_counter() - tb], dtype=torch.float64, device="cuda")
+        dist.all_reduce(dtb, op=dist.ReduceOp.MAX)
+        okb = bool((rb["niter"] == np.tile(zb["niter"], 25)).all() and (rb["nprune"] == np.tile(zb["nprune"], 25)).all()
+                   and (rb["status"] == np.tile(zb["rc"], 25)).all())
+        batch10k = {"workload": f"config 5: 10,000 dense 20x20 instances (tests/golden/batch20.npz x25), {len(lats) // world} per GPU",
+                    "instances_per_s": len(lats) / float(dtb.item()), "e2e_ms": 1e3 * float(dtb.item()),
+                    "nodes_per_s": (int(rb["niter"].sum()) + int(rb["nprune"].sum()) + len(lats)) / float(dtb.item()), "count_ok": okb}
+
     red = torch.tensor([kernel_ms, e2e_s], dtype=torch.float64, device="cuda")
     tot = torch.tensor([float(nodes), float(e2e_nodes), float(last["niter"]), float(last["nprune"]), float(launches)],
                        dtype=torch.float64, device="cuda")
@@ -395,6 +415,8 @@ def main():
                                      "throughput measured on this GPU by bltcu_fp64_peak (MEASURED_PEAKS.json has no "
                                      "FP64 figure)"},
                 "clocks": sampler.summary()}
+        if batch10k is not None:
+            line["batch10k"] = batch10k
         if world == 1:
             line["batch"] = batch_supplement(blt_b200)
             prof = os.path.join(ROOT, "profiles", "r2_final_summary.json")
