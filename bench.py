@@ -392,6 +392,7 @@ def main():
         value = nodes_all / (kernel_ms_max * 1e-3)
         flops = float(sum(hist_all[k] * f_alg(k, m) for k in range(n + 1)))
         peak = blt_b200.fp64_peak(local_rank, 5)
+        int_peak = blt_b200.int32_peak(local_rank, 3)
         achieved = flops / (kernel_ms_max * 1e-3) / 1e12 / max(world, 1)
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
                 "warmup": max(args.warmup, 3), "ms_per_step": kernel_ms_max / args.steps, "higher_is_better": True,
@@ -410,7 +411,7 @@ def main():
                         "search_ms": e2e_search_ms / args.steps, "count_ok": bool(e2e_nodes // args.steps == expected_nodes)},
                 "gpu_launches": int(launches_all),
                 "roofline": {"bound": "fp64", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                             "frac": achieved / peak, "traffic": None,
+                             "frac": achieved / peak, "traffic": None, "int32_peak_tiops": int_peak,
                              "note": "achieved = sum_k N_k*F_alg(k,m) per GPU / search-kernel time; peak = FP64 FMA "
                                      "throughput measured on this GPU by bltcu_fp64_peak (MEASURED_PEAKS.json has no "
                                      "FP64 figure)"},

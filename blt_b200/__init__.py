@@ -8,7 +8,7 @@ All of them call the CUDA kernels through the C ABI declared in include/bltcu.h.
 libbltcu.so is missing or no CUDA device is usable the calls raise / return BLT_STATUS_ERROR.
 """
 from .search import (BLT_CHECK_SAT, BLT_CHECK_UNSAT, BLT_STATUS_ERROR, BLT_STATUS_INPUT_ERROR, BLT_STATUS_LP_FAIL,
-                     BLT_STATUS_OK, check_soln, closest, closest_batch, closest_dev, closest_noalloc, fp64_peak, infdist, lib, lll, lll_arbitrary, lll_batch, lll_fixed_host, lll_fp_host, version, yprune)
+                     BLT_STATUS_OK, check_soln, closest, closest_batch, closest_dev, closest_noalloc, fp64_peak, infdist, int32_peak, lib, lll, lll_arbitrary, lll_batch, lll_fixed_host, lll_fp_host, version, yprune)
 
-__all__ = ["closest", "closest_batch", "closest_dev", "closest_noalloc", "infdist", "check_soln", "lib", "lll", "lll_arbitrary", "lll_batch", "lll_fixed_host", "lll_fp_host", "version", "yprune", "fp64_peak", "BLT_STATUS_OK", "BLT_STATUS_ERROR",
+__all__ = ["closest", "closest_batch", "closest_dev", "closest_noalloc", "infdist", "check_soln", "lib", "lll", "lll_arbitrary", "lll_batch", "lll_fixed_host", "lll_fp_host", "version", "yprune", "fp64_peak", "int32_peak", "BLT_STATUS_OK", "BLT_STATUS_ERROR",
            "BLT_STATUS_LP_FAIL", "BLT_STATUS_INPUT_ERROR", "BLT_CHECK_SAT", "BLT_CHECK_UNSAT"]

@@ -76,6 +76,8 @@ def lib() -> ctypes.CDLL:
         L.bltcu_closest_batch.restype = ctypes.c_int
         L.bltcu_fp64_peak.argtypes = [ctypes.c_int, ctypes.c_int, f64p]
         L.bltcu_fp64_peak.restype = ctypes.c_int
+        L.bltcu_int32_peak.argtypes = [ctypes.c_int, ctypes.c_int, f64p]
+        L.bltcu_int32_peak.restype = ctypes.c_int
         L.bltcu_release.argtypes = []
         L.bltcu_release.restype = None
         L.bltcu_version.argtypes = []
@@ -205,6 +207,15 @@ def fp64_peak(device: int = 0, reps: int = 5) -> float:
     rc = lib().bltcu_fp64_peak(device, reps, ctypes.byref(v))
     if rc != BLT_STATUS_OK:
         raise RuntimeError(f"bltcu_fp64_peak failed with status {rc}")
+    return float(v.value)
+
+
+def int32_peak(device: int = 0, reps: int = 5) -> float:
+    """Measured INT32 multiply-add peak of the device in Tera-operations/s (2 per IMAD)."""
+    v = ctypes.c_double(0.0)
+    rc = lib().bltcu_int32_peak(device, reps, ctypes.byref(v))
+    if rc != BLT_STATUS_OK:
+        raise RuntimeError(f"bltcu_int32_peak failed with status {rc}")
     return float(v.value)
 
 

@@ -155,6 +155,8 @@ int bltcu_closest_noalloc(const int64_t *lat, const int64_t *con, int n, int m, 
 /* Measurement helper (no counterpart in the reference): FP64 FMA throughput of `device` in TFLOP/s, best of
  * `reps` launches.  bench.py uses it as the roofline denominator of the search kernel. */
 int bltcu_fp64_peak(int device, int reps, double *tflops);
+/* The same for the INT32 multiply-add pipe (Tera-operations per second, 2 per IMAD): the second roofline north_star names. */
+int bltcu_int32_peak(int device, int reps, double *tiops);
 
 /* Releases the cached device workspace of every device this process used. */
 void bltcu_release(void);
