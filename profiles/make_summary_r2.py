@@ -2,7 +2,8 @@
 
     ncu -i gpurun_out/r2y_search.ncu-rep --page raw --csv > /tmp/r2_search.csv
     ncu -i gpurun_out/r2y_batch.ncu-rep  --page raw --csv > /tmp/r2_batch.csv
-    python profiles/make_summary_r2.py gpurun_out/r2y_launches.csv /tmp/r2_search.csv /tmp/r2_batch.csv bench_dense60_w130.npz 20529854
+    ncu -i gpurun_out/r3a_lllfp.ncu-rep  --page raw --csv > /tmp/r2_lll.csv     (capture of `python tests/lll_probe.py`)
+    python profiles/make_summary_r2.py gpurun_out/r2y_launches.csv /tmp/r2_search.csv /tmp/r2_batch.csv bench_dense60_w130.npz 20529854 /tmp/r2_lll.csv
 
 The launch list is copied to profiles/r2_final_launches.csv.
 """
@@ -15,6 +16,7 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 launches, raw_search, raw_batch, fixture, nodes = sys.argv[1], sys.argv[2], sys.argv[3], sys.argv[4], int(sys.argv[5])
+raw_lll = sys.argv[6] if len(sys.argv) > 6 else None
 
 
 def load(path):
@@ -66,6 +68,8 @@ B = load(raw_batch)
 name_col = "Kernel Name"
 bk = [d for d in B if "batch_kernel" in d[name_col][0]]
 lk = [d for d in B if "lll_fp_kernel" in d[name_col][0]]
+if raw_lll:  # captured on its own: python tests/lll_probe.py (gpurun_out/r3a_lllfp.ncu-rep)
+    lk = load(raw_lll)
 
 shutil.copyfile(launches, os.path.join(HERE, "r2_final_launches.csv"))
 lrows = [r for r in csv.reader(open(launches)) if len(r) > 10 and r[0].isdigit()]
@@ -127,9 +131,11 @@ for title, ks, per, pn in (("bltcu_batch_kernel<32> (config 5: 4000 problems of 
         md += f"\n## `{title}`\n\n| metric | value |\n|---|---|\n{r}"
 md += """
 Reading: the batch search is the same engine on smaller bases (fewer active lanes per instruction).  The LLL pass moves
-51 MB of algorithmic bytes (8(2rc + 2r^2) per problem) in a few milliseconds: a few percent of the measured HBM peak
-(6,534 GB/s, MEASURED_PEAKS.json); it is a latency chain of a few hundred dependent visits per problem, one warp each,
-so issue utilisation, not bandwidth, is the meaningful figure.
+51 MB of algorithmic bytes (8(2rc + 2r^2) per problem) in 2.7 ms (launch list; 3.4 ms under the full capture) = 19 GB/s,
+0.3 % of the measured HBM peak (6,534 GB/s, MEASURED_PEAKS.json): it is a chain of a few hundred dependent row visits
+per problem, one warp each, so issue utilisation (55 % of the issue slots, ALU pipe 25 %, FP64 pipe 12 %) is the
+meaningful figure, not bandwidth.  The 512-bit kernel that takes the deferred problems (19 of these 4000) needs 37 ms
+for them, which is all but 3 of the 40 ms `bltcu_lll_batch` reports.
 """
 open(os.path.join(HERE, "r2_final_summary.md"), "w").write(md)
 print("wrote r2_final_summary.md")
