@@ -20,7 +20,10 @@
 #include "lll_fixed.h"
 #include "lll_fp.h"
 
+#include <algorithm>
+#include <atomic>
 #include <mutex>
+#include <thread>
 
 #define LLL_W 16  // limbs of 32 bits
 
@@ -201,7 +204,27 @@ extern "C" int bltcu_lll_batch(int64_t *B, int64_t *U, int count, int r, int c, 
     int rc = BLTCU_STATUS_OK;
     bltcu_stats st2;
     memset(&st2, 0, sizeof st2);
-    if (!rest.empty()) {
+    int on_host_threads = 0;
+    const unsigned hc = std::max(1u, std::thread::hardware_concurrency());
+    if (!rest.empty() && status.size() > rest.size() && rest.size() <= 4 * (size_t)hc) {
+        // A handful of stragglers of the fast pass (typically half a percent: a decision on a tie): one 512-bit warp per
+        // problem would take ~100 ms for them however few they are; the host routine takes ~3 ms each, on all cores.
+        std::atomic<size_t> next(0);
+        std::atomic<int> bad(BLTCU_STATUS_OK);
+        std::vector<std::thread> th;
+        const unsigned nt = (unsigned)std::min<size_t>(hc, rest.size());
+        for (unsigned t = 0; t < nt; ++t)
+            th.emplace_back([&]() {
+                for (size_t j = next++; j < rest.size(); j = next++) {
+                    const int i = rest[j];
+                    const int s = bltcu_lll(B + (size_t)i * r * c, U ? U + (size_t)i * r * r : nullptr, r, c, &rank[i]);
+                    if (s != BLTCU_STATUS_OK) bad = s;
+                }
+            });
+        for (auto &t : th) t.join();
+        rc = bad.load();
+        on_host_threads = (int)rest.size();
+    } else if (!rest.empty()) {
         const size_t k = rest.size();
         std::vector<int64_t> b2(k * r * c), u2(k * r * r);
         std::vector<int> rk2(k, 0);
@@ -216,7 +239,7 @@ extern "C" int bltcu_lll_batch(int64_t *B, int64_t *U, int count, int r, int c, 
     if (stats) {
         stats->kernel_ms = fp_ms + st2.kernel_ms;
         stats->launches = (fp_scratch ? 1 : 0) + st2.launches;
-        stats->found = st2.found;                 // problems reduced by the host routine
+        stats->found = st2.found + on_host_threads;   // problems reduced by the host routine
         stats->donated = rest.size();             // problems the floating-point pass deferred to the 512-bit kernel
         stats->warps = count;
         stats->scratch_bytes = fp_scratch + st2.scratch_bytes;

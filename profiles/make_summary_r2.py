@@ -134,8 +134,9 @@ Reading: the batch search is the same engine on smaller bases (fewer active lane
 51 MB of algorithmic bytes (8(2rc + 2r^2) per problem) in 2.7 ms (launch list; 3.4 ms under the full capture) = 19 GB/s,
 0.3 % of the measured HBM peak (6,534 GB/s, MEASURED_PEAKS.json): it is a chain of a few hundred dependent row visits
 per problem, one warp each, so issue utilisation (55 % of the issue slots, ALU pipe 25 %, FP64 pipe 12 %) is the
-meaningful figure, not bandwidth.  The 512-bit kernel that takes the deferred problems (19 of these 4000) needs 37 ms
-for them, which is all but 3 of the 40 ms `bltcu_lll_batch` reports.
+meaningful figure, not bandwidth.  The 512-bit kernel needed 37 ms for the 19 problems this pass defers (that is the
+`bltcu_lll_batch_kernel` line of the launch list above); since then a handful of stragglers goes to the host routine on
+all cores instead: 18 ms end to end for the 4000 problems, copies included.
 """
 open(os.path.join(HERE, "r2_final_summary.md"), "w").write(md)
 print("wrote r2_final_summary.md")
