@@ -376,6 +376,26 @@ def main():
                     "instances_per_s": len(lats) / float(dtb.item()), "e2e_ms": 1e3 * float(dtb.item()),
                     "nodes_per_s": (int(rb["niter"].sum()) + int(rb["nprune"].sum()) + len(lats)) / float(dtb.item()), "count_ok": okb}
 
+    # BASELINE.json config 3 at N > 1: time to the first point of a dimension-60 subset-sum instance, every rank stopped
+    # by the shared stop word (supplementary)
+    sat_exit = None
+    if world > 1:
+        from blt_b200.dist import closest_sharded
+        zs = np.load(os.path.join(ROOT, "tests", "golden", "subset_sum60_b26.npz"))
+        runs = []
+        for sd in [int(x) for x in zs["seeds"]]:
+            la, co = zs[f"lat{sd}"], zs[f"con{sd}"]
+            closest_sharded(la, co, stop=shared, device=local_rank, timeout_ms=120000)
+            barrier()
+            t1 = time.perf_counter()
+            rs = closest_sharded(la, co, stop=shared, device=local_rank, timeout_ms=120000)
+            dts = torch.tensor([time.perf_counter() - t1], dtype=torch.float64, device="cuda")
+            dist.all_reduce(dts, op=dist.ReduceOp.MAX)
+            runs.append({"seed": sd, "found": bool(rs["found"]), "ms_until_every_rank_returned": 1e3 * float(dts.item()),
+                         "nodes_all_ranks": int(rs["nodes"])})
+        sat_exit = {"workload": "config 3: Lagarias-Odlyzko subset-sum lattice, 60 weights of 26 bits (tests/golden/subset_sum60_b26.npz), "
+                                "first point ends the search on every rank (shared stop word)", "runs": runs}
+
     red = torch.tensor([kernel_ms, e2e_s], dtype=torch.float64, device="cuda")
     tot = torch.tensor([float(nodes), float(e2e_nodes), float(last["niter"]), float(last["nprune"]), float(launches)],
                        dtype=torch.float64, device="cuda")
@@ -418,6 +438,8 @@ def main():
                 "clocks": sampler.summary()}
         if batch10k is not None:
             line["batch10k"] = batch10k
+        if sat_exit is not None:
+            line["sat_early_exit"] = sat_exit
         if world == 1:
             line["batch"] = batch_supplement(blt_b200)
             prof = os.path.join(ROOT, "profiles", "r2_final_summary.json")
