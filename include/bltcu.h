@@ -111,14 +111,19 @@ int bltcu_closest_batch(const int64_t *lat, const int64_t *con, int count, int n
 
 /* LLL(): libblt/ntl_wrapper.h:20, libblt/ntl_wrapper.cc:37-52 (exact integral LLL, delta = 3/4, NTL::LLL(det2,B,U)).
  * B: r x c row-major, reduced in place: zero rows first, the `rank` reduced basis rows last.  U: r x r output with
- * U * B_in = B_out (may be NULL).  Returns BLT_STATUS_OK or BLT_STATUS_INPUT_ERROR. */
+ * U * B_in = B_out (may be NULL).  Returns BLT_STATUS_OK or BLT_STATUS_INPUT_ERROR.  Host routine (a single reduction
+ * is one chain of dependent steps): first the integral algorithm's row operations with its decisions taken in fp64
+ * against a margin and the operations themselves in exact int64 (60 x 60: a few ms); a decision inside the margin,
+ * dependent rows or numbers beyond 2^53 hand over to multiprecision passes that perform the same operations. */
 int bltcu_lll(int64_t *B, int64_t *U, int r, int c, int *rank);
 
 /* Batched LLL() for many small problems of one shape (configs 2 and 5 are reduction-bound).
- * B: count x r x c, reduced in place; U: count x r x r out (may be NULL); rank: count.  One GPU warp reduces one problem
- * with 512-bit exact integers, the same operations in the same order as bltcu_lll(), so basis and U are identical to
- * what a loop over bltcu_lll() gives; a problem whose numbers outgrow 512 bits is reduced by bltcu_lll() on the host
- * (stats->found, if stats is not NULL, reports how many).  Returns BLT_STATUS_OK / INPUT_ERROR / ERROR. */
+ * B: count x r x c, reduced in place; U: count x r x r out (may be NULL); rank: count.  One GPU warp reduces one problem,
+ * the same operations in the same order as bltcu_lll(), so basis and U are identical to what a loop over bltcu_lll()
+ * gives: first the fp64-decision pass (see bltcu_lll), then, for what it deferred (stats->donated), the host routine
+ * on all cores when it is a handful or a second kernel with 512-bit exact integers when it is a crowd (dependent
+ * generating sets always are); numbers beyond 512 bits end in the host routine (stats->found = problems reduced on the
+ * host).  Returns BLT_STATUS_OK / INPUT_ERROR / ERROR. */
 int bltcu_lll_batch(int64_t *B, int64_t *U, int count, int r, int c, int *rank, int device, bltcu_stats *stats);
 
 /* yprune(): libblt/yices_wrapper.h:26-34, libblt/yices_wrapper.cc:47-157 -- the exact decision the reference's sound
