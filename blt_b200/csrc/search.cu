@@ -2262,10 +2262,27 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         if (host_stop || feeding) {
             bool told = false, closed = !feeding;
             unsigned int fed = 0;
+            const auto t_launch = std::chrono::steady_clock::now();
+            double closed_ms = -1.0, first_hungry_ms = -1.0;
+            struct Sample { double t; int idle, pending, qlen, fed; };
+            std::vector<Sample> samples;
+            const bool trace = getenv("BLTCU_TRACE") != nullptr;  // developer aid: the relay's looks at the device, binned
+            int hungry_polls = 0, feed_polls = 1, feed_idle_div = 8;
+            if (const char *e = getenv("BLTCU_FEED_POLLS")) feed_polls = std::max(1, atoi(e));
+            if (const char *e = getenv("BLTCU_FEED_IDLE_DIV")) feed_idle_div = std::max(1, atoi(e));
+            bool ramped = getenv("BLTCU_FEED_RAMP_GUARD") == nullptr, seen_idle = false;  // the guard is off unless asked for
+            int feed_per_idle = 0, feed_hold_us = 150;
+            if (const char *e = getenv("BLTCU_FEED_PER_IDLE")) feed_per_idle = std::max(0, atoi(e));
+            if (const char *e = getenv("BLTCU_FEED_HOLD_US")) feed_hold_us = std::max(0, atoi(e));
             int *pin = w->pin;  // [0..4] pending idle abort status found (as laid out in QCtl); [8..] values to send
             while (cudaEventQuery(w->e1) == cudaErrorNotReady) {
                 CK(cudaMemcpyAsync(pin, &P.q->pending, 20, cudaMemcpyDeviceToHost, w->stream2));
+                if (trace) CK(cudaMemcpyAsync(pin + 12, &P.q->head, 8, cudaMemcpyDeviceToHost, w->stream2));
                 CK(cudaStreamSynchronize(w->stream2));
+                if (trace) {
+                    const double t = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
+                    samples.push_back({t, pin[1], pin[0], (int)((unsigned int)pin[13] - (unsigned int)pin[12]), (int)fed});
+                }
                 if (host_stop && pin[4]) *host_stop = 1;
                 if (host_stop && *host_stop && !told) {
                     pin[8] = 1;
@@ -2273,9 +2290,25 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                     CK(cudaStreamSynchronize(w->stream2));
                     told = true;
                 }
-                if (!closed && !told && pin[1] * 8 > nwarps) {  // an eighth of the warps wait for work: one more chunk
+                // hungry: an eighth of the warps wait for work (on BLTCU_FEED_POLLS looks in a row, default 1).  Measured
+                // (profiles/r2_feed_policy.md): stricter tests, larger chunks and larger on-demand parts all lose, because
+                // a subtree that starts late cannot finish before its own critical path has run (tens of ms here).
+                // BLTCU_FEED_RAMP_GUARD: while a search ramps up every warp looks idle; with the guard nothing is handed out
+                // before the warps have been busy once (or 5 ms have passed).  Measured equal at 8 GPUs, and it would delay
+                // small searches, so it is off by default.
+                if (pin[1] > 0) seen_idle = true;  // the kernel has started
+                if (!ramped && ((seen_idle && pin[1] * 8 < nwarps) ||
+                                std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count() > 5.0)) ramped = true;
+                hungry_polls = (ramped && pin[1] * feed_idle_div > nwarps) ? hungry_polls + 1 : 0;
+                if (!closed && !told && hungry_polls >= feed_polls) {  // one more chunk
+                    if (verbose && first_hungry_ms < 0.0 && fed > 0) first_hungry_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
                     // a chunk is 1/16 of a rank's fair share of the on-demand part (at most what the staging page holds)
-                    const int chunk = std::min(1000, std::max(1, (int)(dyn.size() / (16 * (size_t)world))));
+                    int chunk = std::min(1000, std::max(1, (int)(dyn.size() / (16 * (size_t)world))));
+                    if (feed_per_idle > 0) {  // one subtree per so many waiting warps, less as the on-demand part runs out
+                        const int left = std::max(0, (int)dyn.size() - __atomic_load_n((int *)(shared + 1), __ATOMIC_RELAXED));
+                        chunk = std::max(chunk, std::min(pin[1] / feed_per_idle, std::max(1, left / (2 * world))));
+                        chunk = std::min(1000, chunk);
+                    }
                     const int i0 = __atomic_fetch_add((int *)(shared + 1), chunk, __ATOMIC_RELAXED);
                     if (i0 < (int)dyn.size()) {
                         const int cnt = std::min(chunk, (int)dyn.size() - i0);
@@ -2288,17 +2321,30 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                         pin[11] = 0;
                         CK(cudaMemcpyAsync(&P.q->feed_open, pin + 11, 4, cudaMemcpyHostToDevice, w->stream2));
                         closed = true;
+                        closed_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
                     }
                     CK(cudaStreamSynchronize(w->stream2));
                     // one chunk per 150 us at most: while a search ramps up every warp looks idle, and a rank must not
                     // swallow the whole on-demand half in those first milliseconds
-                    std::this_thread::sleep_for(std::chrono::microseconds(150));
+                    std::this_thread::sleep_for(std::chrono::microseconds(feed_hold_us));
                     continue;
                 }
                 std::this_thread::sleep_for(std::chrono::microseconds(50));
             }
             (void)cudaGetLastError();
             fed_total += fed;
+            if (trace && !samples.empty()) {
+                const double bin = std::max(1.0, samples.back().t / 40.0);
+                size_t i = 0;
+                for (double t0 = 0.0; i < samples.size(); t0 += bin) {
+                    long cnt = 0; double idle = 0, pend = 0, ql = 0; int fedv = 0;
+                    for (; i < samples.size() && samples[i].t < t0 + bin; ++i) { cnt++; idle += samples[i].idle; pend += samples[i].pending; ql += samples[i].qlen; fedv = samples[i].fed; }
+                    if (cnt) fprintf(stderr, "bltcu: trace rank %d t %7.1f ms idle %6.0f of %d warps, pending %7.0f, ring %6.0f, fed %d\n", rank, t0, idle / cnt, nwarps, pend / cnt, ql / cnt, fedv);
+                }
+            }
+            if (verbose && feeding)
+                fprintf(stderr, "bltcu: rank %d took %u of %zu on-demand subtrees, second request after %.2f ms, none left after %.2f ms\n", rank, fed,
+                        dyn.size(), first_hungry_ms, closed_ms);
         }
         CK(cudaMemcpyAsync(&hq, P.q, sizeof hq, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -2307,7 +2353,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         CK(cudaEventElapsedTime(&ms, w->e0, w->e1));
         kernel_ms += ms;
         launches++;
-        if (verbose) fprintf(stderr, "bltcu: search launch %d (static depth %d): %.3f ms, %llu nodes, %u subtrees published, first descent over after %.3f ms\n", launches, P.static_depth, ms, (unsigned long long)hq.nodes, hq.out_count, hq.dive_end_ns ? (double)(hq.dive_end_ns - now_rc[0]) * 1e-6 : -1.0);
+        if (verbose) fprintf(stderr, "bltcu: rank %d search launch %d (static depth %d): %.3f ms, %llu nodes, busy %.3f, %u subtrees published, first descent over after %.3f ms\n", rank, launches, P.static_depth, ms, (unsigned long long)hq.nodes, (double)hq.busy_ns / (double)std::max<unsigned long long>(1, hq.busy_ns + hq.idle_ns), hq.out_count, hq.dive_end_ns ? (double)(hq.dive_end_ns - now_rc[0]) * 1e-6 : -1.0);
         if (hq.fail_info) lp_failed = true;
         if (hq.fail_info && verbose) {
             fprintf(stderr, "bltcu: LP failure code %d at level k=%d (basis size %d), u =", hq.fail_info & 255, (hq.fail_info >> 8) & 255, hq.fail_info >> 16);
@@ -2376,11 +2422,20 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         for (size_t i = 0; i < idx.size(); ++i) idx[i] = (int)i;
         std::sort(idx.begin(), idx.end(), [&](int a, int b) { return keys[a] < keys[b]; });
         initial.clear();
-        // Seven eighths of the subtrees are dealt round-robin now; with a shared block the last eighth is taken on demand,
-        // which evens out the ranks' finishing times (measured: an on-demand HALF starves the GPUs between refills).
-        const size_t nstat = shared ? idx.size() - idx.size() / 8 : idx.size();
-        for (size_t i = 0; i < nstat; ++i) if ((int)(i % world) == rank) initial.push_back(out[idx[i]]);
-        for (size_t i = nstat; i < idx.size(); ++i) dyn.push_back(out[idx[i]]);
+        // Seven eighths of the subtrees are dealt round-robin now; with a shared block the last eighth is taken on demand
+        // (measured: an on-demand HALF starves the GPUs between refills).
+        // Developer knobs: BLTCU_FEED_DIV=d takes 1/d of the subtrees on demand (default 8), the LAST 1/d of the
+        // depth-first order unless BLTCU_FEED_STRIDED is set (then every d-th subtree: measured slower).
+        int feed_div = 8;
+        if (const char *e = getenv("BLTCU_FEED_DIV")) feed_div = std::min(64, std::max(2, atoi(e)));
+        const bool feed_tail = getenv("BLTCU_FEED_STRIDED") == nullptr;
+        const size_t nstat = shared ? idx.size() - idx.size() / (size_t)feed_div : idx.size();
+        size_t dealt = 0;
+        for (size_t i = 0; i < idx.size(); ++i) {
+            const bool on_demand = shared && (feed_tail ? i >= nstat : (i % (size_t)feed_div) == (size_t)feed_div - 1);
+            if (on_demand) dyn.push_back(out[idx[i]]);
+            else if ((int)(dealt++ % (size_t)world) == rank) initial.push_back(out[idx[i]]);
+        }
         feeding = !dyn.empty();
         const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0)) || (host_stop && *host_stop);
         if (!stop && (!initial.empty() || feeding)) {
