@@ -2271,12 +2271,17 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
             if (const char *e = getenv("BLTCU_FEED_POLLS")) feed_polls = std::max(1, atoi(e));
             if (const char *e = getenv("BLTCU_FEED_IDLE_DIV")) feed_idle_div = std::max(1, atoi(e));
             bool ramped = getenv("BLTCU_FEED_RAMP_GUARD") == nullptr, seen_idle = false;  // the guard is off unless asked for
-            int feed_per_idle = 0, feed_hold_us = 150;
+            bool fed_state = getenv("BLTCU_FEED_EAGER") != nullptr;  // (eager: top up from the start, for measurements)
+            int feed_per_idle = 0, feed_hold_us = 150, feed_backlog = 0;
+            if (const char *e = getenv("BLTCU_FEED_BACKLOG")) { feed_backlog = std::max(0, atoi(e)); if (feed_backlog > 0) { ramped = false; feed_hold_us = 0; } }
             if (const char *e = getenv("BLTCU_FEED_PER_IDLE")) feed_per_idle = std::max(0, atoi(e));
             if (const char *e = getenv("BLTCU_FEED_HOLD_US")) feed_hold_us = std::max(0, atoi(e));
-            int *pin = w->pin;  // [0..4] pending idle abort status found (as laid out in QCtl); [8..] values to send
+            // pin[0..11]: pending idle abort status found out_count timed_out fail_info dive_state feed_head feed_tail
+            // feed_open, as laid out in QCtl; [12..13] head, tail of the ring (trace); [20..22] values to send; [32..] a chunk
+            int *pin = w->pin;
+            static_assert(offsetof(QCtl, feed_head) - offsetof(QCtl, pending) == 36 && offsetof(QCtl, feed_open) - offsetof(QCtl, pending) == 44, "relay snapshot layout");
             while (cudaEventQuery(w->e1) == cudaErrorNotReady) {
-                CK(cudaMemcpyAsync(pin, &P.q->pending, 20, cudaMemcpyDeviceToHost, w->stream2));
+                CK(cudaMemcpyAsync(pin, &P.q->pending, 48, cudaMemcpyDeviceToHost, w->stream2));
                 if (trace) CK(cudaMemcpyAsync(pin + 12, &P.q->head, 8, cudaMemcpyDeviceToHost, w->stream2));
                 CK(cudaStreamSynchronize(w->stream2));
                 if (trace) {
@@ -2285,8 +2290,8 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                 }
                 if (host_stop && pin[4]) *host_stop = 1;
                 if (host_stop && *host_stop && !told) {
-                    pin[8] = 1;
-                    CK(cudaMemcpyAsync(&P.q->abort, pin + 8, 4, cudaMemcpyHostToDevice, w->stream2));
+                    pin[20] = 1;
+                    CK(cudaMemcpyAsync(&P.q->abort, pin + 20, 4, cudaMemcpyHostToDevice, w->stream2));
                     CK(cudaStreamSynchronize(w->stream2));
                     told = true;
                 }
@@ -2300,26 +2305,35 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                 if (!ramped && ((seen_idle && pin[1] * 8 < nwarps) ||
                                 std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count() > 5.0)) ramped = true;
                 hungry_polls = (ramped && pin[1] * feed_idle_div > nwarps) ? hungry_polls + 1 : 0;
-                if (!closed && !told && hungry_polls >= feed_polls) {  // one more chunk
+                // backlog policy (BLTCU_FEED_BACKLOG=k): keep k subtrees waiting in the feed, whether or not anybody is idle:
+                // a warp that runs dry with the ring empty takes one at once instead of waiting for the next look
+                const int backlog = (int)(fed - (unsigned int)pin[9]);
+                // ... from the moment this rank's own share first leaves an eighth of its warps without work
+                if (ramped && pin[1] * feed_idle_div > nwarps) fed_state = true;
+                const bool top_up = feed_backlog > 0 && fed_state && backlog < feed_backlog;
+                if (!closed && !told && (feed_backlog > 0 ? top_up : hungry_polls >= feed_polls)) {  // one more chunk
                     if (verbose && first_hungry_ms < 0.0 && fed > 0) first_hungry_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
                     // a chunk is 1/16 of a rank's fair share of the on-demand part (at most what the staging page holds)
-                    int chunk = std::min(1000, std::max(1, (int)(dyn.size() / (16 * (size_t)world))));
-                    if (feed_per_idle > 0) {  // one subtree per so many waiting warps, less as the on-demand part runs out
+                    int chunk = std::min(960, std::max(1, (int)(dyn.size() / (16 * (size_t)world))));
+                    if (feed_backlog > 0) {  // fill up, but never more than half of a rank's fair share of what is left
+                        const int left = std::max(0, (int)dyn.size() - __atomic_load_n((int *)(shared + 1), __ATOMIC_RELAXED));
+                        chunk = std::min(960, std::max(1, std::min(feed_backlog - backlog, left / (2 * world))));
+                    } else if (feed_per_idle > 0) {  // one subtree per so many waiting warps, less as the on-demand part runs out
                         const int left = std::max(0, (int)dyn.size() - __atomic_load_n((int *)(shared + 1), __ATOMIC_RELAXED));
                         chunk = std::max(chunk, std::min(pin[1] / feed_per_idle, std::max(1, left / (2 * world))));
-                        chunk = std::min(1000, chunk);
+                        chunk = std::min(960, chunk);
                     }
                     const int i0 = __atomic_fetch_add((int *)(shared + 1), chunk, __ATOMIC_RELAXED);
                     if (i0 < (int)dyn.size()) {
                         const int cnt = std::min(chunk, (int)dyn.size() - i0);
-                        for (int e = 0; e < cnt; ++e) pin[16 + e] = dyn[(size_t)(i0 + e)];
-                        pin[10] = (int)fed + cnt;
-                        CK(cudaMemcpyAsync(P.feed + fed, pin + 16, (size_t)cnt * 4, cudaMemcpyHostToDevice, w->stream2));
-                        CK(cudaMemcpyAsync(&P.q->feed_tail, pin + 10, 4, cudaMemcpyHostToDevice, w->stream2));
+                        for (int e = 0; e < cnt; ++e) pin[32 + e] = dyn[(size_t)(i0 + e)];
+                        pin[21] = (int)fed + cnt;
+                        CK(cudaMemcpyAsync(P.feed + fed, pin + 32, (size_t)cnt * 4, cudaMemcpyHostToDevice, w->stream2));
+                        CK(cudaMemcpyAsync(&P.q->feed_tail, pin + 21, 4, cudaMemcpyHostToDevice, w->stream2));
                         fed += (unsigned int)cnt;
                     } else {
-                        pin[11] = 0;
-                        CK(cudaMemcpyAsync(&P.q->feed_open, pin + 11, 4, cudaMemcpyHostToDevice, w->stream2));
+                        pin[22] = 0;
+                        CK(cudaMemcpyAsync(&P.q->feed_open, pin + 22, 4, cudaMemcpyHostToDevice, w->stream2));
                         closed = true;
                         closed_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
                     }
@@ -2429,12 +2443,20 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         int feed_div = 8;
         if (const char *e = getenv("BLTCU_FEED_DIV")) feed_div = std::min(64, std::max(2, atoi(e)));
         const bool feed_tail = getenv("BLTCU_FEED_STRIDED") == nullptr;
-        const size_t nstat = shared ? idx.size() - idx.size() / (size_t)feed_div : idx.size();
+        size_t nstat = shared ? idx.size() - idx.size() / (size_t)feed_div : idx.size();
+        if (const char *e = getenv("BLTCU_FEED_PCT")) if (shared) nstat = idx.size() - idx.size() * (size_t)std::min(95, std::max(1, atoi(e))) / 100;
         size_t dealt = 0;
         for (size_t i = 0; i < idx.size(); ++i) {
             const bool on_demand = shared && (feed_tail ? i >= nstat : (i % (size_t)feed_div) == (size_t)feed_div - 1);
             if (on_demand) dyn.push_back(out[idx[i]]);
-            else if ((int)(dealt++ % (size_t)world) == rank) initial.push_back(out[idx[i]]);
+            else if ((int)(dealt++ % (size_t)world) == rank) {
+                initial.push_back(out[idx[i]]);
+                if (getenv("BLTCU_DUMP_KEYS")) {  // developer aid: the path (sibling ordinals from the top level down) of this rank's subtrees
+                    fprintf(stderr, "bltcu: subtree %zu of %zu key", i, idx.size());
+                    for (int e = 0; e < n && e < 10; ++e) fprintf(stderr, " %d", (int)keys[idx[i]][e]);  // top level first
+                    fprintf(stderr, "\n");
+                }
+            }
         }
         feeding = !dyn.empty();
         const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0)) || (host_stop && *host_stop);

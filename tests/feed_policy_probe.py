@@ -19,13 +19,16 @@ z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f
 lat, con = z["lat"], z["con"]
 blt_b200.closest(lat, con, rank=0, world=8, timeout_ms=120000)
 os.environ["BLTCU_VERBOSE"] = "1"
-for polls, per_idle, hold, fdiv in [(1, 0, 150, 8), (1, 32, 150, 8), (1, 0, 150, 3), (1, 32, 150, 3), (1, 16, 150, 3), (1, 8, 150, 3),
-                                    (1, 32, 50, 3), (1, 32, 150, 2), (1, 16, 150, 2)]:
-    os.environ["BLTCU_FEED_POLLS"] = str(polls)
-    os.environ["BLTCU_FEED_PER_IDLE"] = str(per_idle)
-    os.environ["BLTCU_FEED_HOLD_US"] = str(hold)
-    os.environ["BLTCU_FEED_DIV"] = str(fdiv)
+K = ("BLTCU_FEED_BACKLOG", "BLTCU_FEED_PCT", "BLTCU_FEED_DIV", "BLTCU_FEED_PER_IDLE", "BLTCU_FEED_HOLD_US", "BLTCU_FEED_POLLS")
+for env in [{}, {"BLTCU_FEED_BACKLOG": "64"}, {"BLTCU_FEED_BACKLOG": "256"},
+            {"BLTCU_FEED_PCT": "50"}, {"BLTCU_FEED_PCT": "50", "BLTCU_FEED_BACKLOG": "32"}, {"BLTCU_FEED_PCT": "50", "BLTCU_FEED_BACKLOG": "64"},
+            {"BLTCU_FEED_PCT": "50", "BLTCU_FEED_BACKLOG": "128"}, {"BLTCU_FEED_PCT": "50", "BLTCU_FEED_BACKLOG": "256"},
+            {"BLTCU_FEED_PCT": "50", "BLTCU_FEED_BACKLOG": "512"},
+            {"BLTCU_FEED_PCT": "70", "BLTCU_FEED_BACKLOG": "128"}, {"BLTCU_FEED_PCT": "70", "BLTCU_FEED_BACKLOG": "512"}]:
+    for k in K:
+        os.environ.pop(k, None)
+    os.environ.update(env)
     word = (ctypes.c_int * 16)()
-    print(f"--- polls {polls} one subtree per {per_idle} idle warps, hold-off {hold} us, on-demand tail 1/{fdiv}", file=sys.stderr, flush=True)
+    print(f"--- {env}", file=sys.stderr, flush=True)
     r = blt_b200.closest(lat, con, rank=0, world=8, stop_flag=ctypes.addressof(word), no_early_exit=1, timeout_ms=120000)
     print(f"    kernel {r['kernel_ms']:.1f} ms nodes {r['nodes']} busy {r['busy_frac']:.3f} -> {r['nodes'] / r['kernel_ms'] / 1e3:.1f} Mnodes/s", file=sys.stderr, flush=True)

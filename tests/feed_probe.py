@@ -18,14 +18,17 @@ gpus = int(sys.argv[2]) if len(sys.argv) > 2 else 2
 z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", fx))
 lat, con = z["lat"], z["con"]
 blt_b200.closest(lat, con, gpus=gpus, timeout_ms=120000)  # warm-up, allocations on every device
-K = ("BLTCU_FEED_STRIDED", "BLTCU_FEED_DIV", "BLTCU_FEED_PER_IDLE", "BLTCU_FEED_HOLD_US", "BLTCU_FEED_RAMP_GUARD")
-for name, env in [("shipped", {}), ("ramp guard", {"BLTCU_FEED_RAMP_GUARD": "1"}),
-                  ("tail/8 per 8", {"BLTCU_FEED_PER_IDLE": "8"}),
-                  ("tail/4 per 8", {"BLTCU_FEED_DIV": "4", "BLTCU_FEED_PER_IDLE": "8"}),
-                  ("tail/3 per 8", {"BLTCU_FEED_DIV": "3", "BLTCU_FEED_PER_IDLE": "8"}),
-                  ("tail/3 per 16", {"BLTCU_FEED_DIV": "3", "BLTCU_FEED_PER_IDLE": "16"}),
-                  ("tail/2 per 8", {"BLTCU_FEED_DIV": "2", "BLTCU_FEED_PER_IDLE": "8"}),
-                  ("tail/2 per 4", {"BLTCU_FEED_DIV": "2", "BLTCU_FEED_PER_IDLE": "4"})]:
+K = ("BLTCU_FEED_STRIDED", "BLTCU_FEED_DIV", "BLTCU_FEED_PER_IDLE", "BLTCU_FEED_HOLD_US", "BLTCU_FEED_RAMP_GUARD",
+     "BLTCU_FEED_BACKLOG", "BLTCU_FEED_PCT", "BLTCU_FEED_EAGER")
+for name, env in [("shipped", {}),
+                  ("backlog 128, 12 %", {"BLTCU_FEED_BACKLOG": "128"}),
+                  ("backlog 128, 35 %", {"BLTCU_FEED_BACKLOG": "128", "BLTCU_FEED_PCT": "35"}),
+                  ("backlog 128, 50 %", {"BLTCU_FEED_BACKLOG": "128", "BLTCU_FEED_PCT": "50"}),
+                  ("backlog 512, 50 %", {"BLTCU_FEED_BACKLOG": "512", "BLTCU_FEED_PCT": "50"}),
+                  ("backlog 32, 50 %", {"BLTCU_FEED_BACKLOG": "32", "BLTCU_FEED_PCT": "50"}),
+                  ("backlog 128, 70 %", {"BLTCU_FEED_BACKLOG": "128", "BLTCU_FEED_PCT": "70"}),
+                  ("backlog 128, 85 %", {"BLTCU_FEED_BACKLOG": "128", "BLTCU_FEED_PCT": "85"}),
+                  ("eager 128, 50 %", {"BLTCU_FEED_BACKLOG": "128", "BLTCU_FEED_PCT": "50", "BLTCU_FEED_EAGER": "1"})]:
     for k in K:
         os.environ.pop(k, None)
     os.environ.update(env)
@@ -36,5 +39,5 @@ for name, env in [("shipped", {}), ("ramp guard", {"BLTCU_FEED_RAMP_GUARD": "1"}
         ms = (time.perf_counter() - t0) * 1e3
         best = ms if best is None else min(best, ms)
     ok = r["nodes"] == int(z["nodes"]) and r["pivots"] == int(z["pivots"]) and (r["sol"] == z["sol"]).all()
-    print(f"{name:10s} gpus {r['gpus']} wall {best:.1f} ms kernel {r['kernel_ms']:.1f} ms -> {r['nodes'] / best / 1e3:.1f} Mnodes/s "
+    print(f"{name:18s} gpus {r['gpus']} wall {best:.1f} ms kernel {r['kernel_ms']:.1f} ms -> {r['nodes'] / best / 1e3:.1f} Mnodes/s "
           f"busy {r['busy_frac']:.3f} counts_ok {ok}", flush=True)
