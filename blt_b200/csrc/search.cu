@@ -70,6 +70,8 @@ enum { C_NITER = 0, C_NPRUNE, C_NODES, C_DONATED, C_PIVOTS, C_QUICK, C_REFAC, C_
 enum { REC_TOP = 1, REC_CONT = 2, REC_DIVE = 4 };  // REC_CONT: a suspended sibling loop (resume it), not a fresh explored node
 // REC_DIVE: this record is on the very first descent of the search (the reference's first dive towards the Babai
 // point): its loop is parked after the first explored child so that the first leaf is reached in n node latencies
+#define SHARE_EXPORT_SLOTS 64  // pool slots a rank keeps for records on their way out
+#define EXP_TICKETS 4096  // records one rank can hand to other GPUs in one search
 #define EAGER_MAX 8  // explored children a sibling loop produces before it is suspended in favour of its first child
 // REC_TOP: the record's children are the top level (first prune ends the search, closest.cc:280-286)
 
@@ -93,6 +95,10 @@ struct QCtl {
     unsigned int feed_head;     // next entry of Params::feed to take (device)
     unsigned int feed_tail;     // entries written so far (host, through the copy engine)
     int feed_open;              // host: more entries may come
+    // export: records handed to OTHER GPUs of a multi-rank search.  The host grants tickets (slot of ticket t in
+    // Params::exp_slots[t]); a warp that takes ticket t copies the oldest record of its stack there and marks exp_list[t].
+    int export_want;            // host: tickets granted so far
+    int export_claim;           // device: tickets taken
     unsigned long long deadline_ns;  // %globaltimer value after which every loop gives up (0 = none)
     unsigned long long niter, nprune, nodes, pivots, quick, refactors, colds, donated, inband;
     unsigned long long dive_end_ns;  // %globaltimer when the first descent ended (diagnostics)
@@ -144,6 +150,8 @@ struct Params {
     int lowwater;
     int no_early_exit;
     int dive_hold;          // 1 = the other warps wait while the first descent is under way
+    int *exp_slots;         // multi-rank searches with a work-sharing block: pool slot of each export ticket (host-written)
+    int *exp_list;          // ... 1 once the record of that ticket is in its slot (device-written, host-polled)
     int eager_max;          // explored children a sibling loop produces before it is parked (1 = the reference's depth-first order)
     int warps_per_cta;
     size_t warp_smem_doubles;
@@ -1455,6 +1463,33 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
             burst = P.dive_hold;
         }
         { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_BUSY_NS] += t - t_mark; t_mark = t; }
+        // another GPU of the search asked for work: the oldest record of the stack goes into the slot its ticket names
+        if (P.exp_list && A.acount > A.abot) {
+            int ticket = -1, eslot = -1;
+            if (lane == 0) {
+                const int want = *(volatile int *)&q->export_want;
+                int c = *(volatile int *)&q->export_claim;
+                while (c < want) {
+                    const int old = atomicCAS(&q->export_claim, c, c + 1);
+                    if (old == c) { ticket = c; eslot = ((volatile int *)P.exp_slots)[c]; break; }
+                    c = old;
+                }
+            }
+            ticket = __shfl_sync(FULLMASK, ticket, 0);
+            eslot = __shfl_sync(FULLMASK, eslot, 0);
+            if (ticket >= 0) {
+                const unsigned char *src = A.base + A.offs[A.abot];
+                const size_t bytes = (size_t)(A.offs[A.abot + 1] - A.offs[A.abot]);
+                copy_words(P.pool + (size_t)eslot * RL.stride, src, bytes, lane);
+                __syncwarp();
+                __threadfence_system();
+                if (lane == 0) ((volatile int *)P.exp_list)[ticket] = 1;
+                A.abot++;
+                CTR(s, C_DONATED);
+                if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; }
+                __syncwarp();
+            }
+        }
         // hand the oldest pending record to an idle warp
 #pragma unroll 1
         for (int rounds = burst ? A.acount - A.abot : 1; rounds > 0 && P.dynamic && A.acount > A.abot; --rounds) {
@@ -1998,6 +2033,8 @@ struct DevWs {  // cached per device, grow-only
     size_t in_cap = 0;
     cudaStream_t stream = nullptr, stream2 = nullptr;  // stream2: small copies beside a running search kernel
     int *pin = nullptr;                                // page-locked staging for them
+    unsigned char *rec_pin = nullptr;                  // page-locked staging for two records (work sharing between GPUs)
+    size_t rec_cap = 0;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     std::mutex mu;  // one call at a time per device; different devices run concurrently (opts.gpus)
 };
@@ -2034,6 +2071,7 @@ size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 struct Layout {
     int KQS, LDS, LDG, LDQ, wpc, ctas, nwarps, pool_cap, arena_slots;
     size_t warp_bytes, smem_bytes, wbuf_stride, arena_bytes, arena_stride;
+    size_t o_exp;  // export tickets: EXP_TICKETS slots, then EXP_TICKETS ready marks
     size_t o_q, o_in, o_B, o_p, o_Q, o_Qrev, o_Rm, o_QTp, o_tmp, o_rc, o_ring, o_fring, o_out, o_sol, o_bu, o_bk, o_bv, o_pool,
         o_wbuf, o_next, o_arena, total;
     RecLayout RL;
@@ -2082,6 +2120,7 @@ int make_layout(Layout &L, int n, int m, size_t smem_budget, int sms, int want_w
     L.o_ring = carve((size_t)L.pool_cap * 4);
     L.o_fring = carve((size_t)L.pool_cap * 4);
     L.o_out = carve((size_t)L.pool_cap * 4);
+    L.o_exp = carve((size_t)2 * EXP_TICKETS * 4);
     L.o_sol = carve((size_t)n * 8 + 8);
     L.o_bu = carve((size_t)L.nwarps * n * 8);
     L.o_bk = carve((size_t)L.nwarps * n * sizeof(ord_t));
@@ -2153,6 +2192,63 @@ static cudaError_t launch_batch(int m, int ctas, int threads, size_t smem, cudaS
     return cudaGetLastError();
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Work sharing between the GPUs of one search (bltcu_opts.stop_flag pointing at a block larger than the 16 legacy
+// ints, its size in bytes in word 2).  All traffic is host-relayed: a GPU that runs dry asks (need[r]); the host
+// thread of a GPU whose warps are all busy grants export tickets to its device, whose warps put the oldest record of
+// their stacks into the named pool slots; the host copies the record out, through the destination's mailbox in the
+// block, and the destination's host thread copies it into a reserved pool slot of its own device and appends it to
+// the feed the idle warps pop.  Records are self-contained (every rank has built the same geometry), so they can
+// be expanded on any GPU.  Termination: every rank idle (device empty, feed empty, no claimed ticket unprocessed,
+// mailbox empty) and exported == imported, read twice around the scan of the idle flags.
+// Block layout in ints: [0] stop word, [1] on-demand counter, [2] bytes of the block, [4] exported, [5] imported,
+// [6] done, [16+r] idle, [32+r] need, [48+r] mailbox head, [64+r] mailbox tail, [80+r] left; mailboxes from byte 4096:
+// per rank `slots` entries of 64 bytes of header (int seq) + one record.
+struct Share {
+    volatile int *w = nullptr;
+    int world = 0, rank = 0, slots = 0;
+    size_t stride = 0, entry = 0;
+    unsigned char *mail = nullptr;
+    bool on() const { return slots > 0; }
+    static constexpr int MAXW = 16;
+    void attach(volatile int *block, int world_, int rank_, size_t rec_stride) {
+        w = block; world = world_; rank = rank_; stride = rec_stride; slots = 0;
+        // opt-in (BLTCU_SHARE=1): correct at 2 and 8 GPUs, but on the bench tree it moves ~1,000-node records at the
+        // ~25 records/ms a host thread can relay and does not shorten the search (profiles/r2_feed_policy.md, section 6)
+        if (!block || world_ < 2 || world_ > MAXW || !getenv("BLTCU_SHARE") || atoi(getenv("BLTCU_SHARE")) == 0) return;
+        const long long bytes = (long long)(unsigned int)__atomic_load_n((int *)(block + 2), __ATOMIC_ACQUIRE);
+        entry = 64 + ((rec_stride + 63) / 64) * 64;
+        const long long avail = (bytes - 4096) / (long long)world_ / (long long)entry;
+        if (bytes < 4096 || avail < 2) return;
+        slots = (int)std::min<long long>(8, avail);
+        mail = (unsigned char *)block + 4096;
+    }
+    int *exported() const { return (int *)(w + 4); }
+    int *imported() const { return (int *)(w + 5); }
+    int *done() const { return (int *)(w + 6); }
+    int *idle(int r) const { return (int *)(w + 16 + r); }
+    int *need(int r) const { return (int *)(w + 32 + r); }
+    int *mhead(int r) const { return (int *)(w + 48 + r); }
+    int *mtail(int r) const { return (int *)(w + 64 + r); }
+    int *left(int r) const { return (int *)(w + 80 + r); }
+    unsigned char *slot(int r, unsigned int ticket) const { return mail + ((size_t)r * slots + ticket % (unsigned int)slots) * entry; }
+    void leave() {  // this rank takes no further part: it counts as idle, asks for nothing
+        if (!on()) return;
+        __atomic_store_n(need(rank), 0, __ATOMIC_SEQ_CST);
+        __atomic_store_n(idle(rank), 1, __ATOMIC_SEQ_CST);
+        __atomic_store_n(left(rank), 1, __ATOMIC_SEQ_CST);
+    }
+    bool all_idle() const {
+        for (int r = 0; r < world; ++r) if (!__atomic_load_n(idle(r), __ATOMIC_SEQ_CST)) return false;
+        return true;
+    }
+};
+struct ShareGuard {  // whatever way search_impl returns, the other ranks must not wait for this one
+    Share *s;
+    ~ShareGuard() { if (s) s->leave(); }
+};
+
 static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int n, int m, const bltcu_opts *opts,
                        int64_t *sol, bltcu_stats *stats) {
     const auto t_start = std::chrono::steady_clock::now();
@@ -2193,6 +2289,17 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
     volatile int *host_stop = (shared && !o.no_early_exit) ? shared : nullptr;
     std::vector<int> dyn;   // record slots of the subtrees dealt on demand, in depth-first order
     bool feeding = false;
+    Share share;            // work sharing between the GPUs (a block larger than the legacy 16 ints)
+    share.attach(shared, world, rank, RL.stride);
+    ShareGuard share_guard{&share};
+    if (share.on() && w->rec_cap < 2 * RL.stride) {
+        if (w->rec_pin) cudaFreeHost(w->rec_pin);
+        w->rec_pin = nullptr; w->rec_cap = 0;
+        CK(cudaHostAlloc((void **)&w->rec_pin, 2 * RL.stride, cudaHostAllocDefault));
+        w->rec_cap = 2 * RL.stride;
+    }
+    std::vector<int> resv;  // pool slots kept out of the free ring: imports first, then SHARE_EXPORT_SLOTS for exports
+    int want_resv = 0;
 
     int launches = 0;
     const size_t setup_smem = warp_smem_bytes(n, m, 0, 1);
@@ -2233,6 +2340,8 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         std::vector<char> used(pool_cap, 0);
         for (int r : initial) used[r] = 1;
         for (int r : dyn) used[r] = 1;  // records waiting to be fed stay where they are
+        resv.clear();
+        for (int i = pool_cap - 1; i >= 0 && (int)resv.size() < want_resv; --i) if (!used[i]) { used[i] = 1; resv.push_back(i); }
         for (int i = 0; i < pool_cap; ++i) if (!used[i]) fring[nf++] = i;
         hq.ftail = nf;
         hq.deadline_ns = deadline_ns;
@@ -2280,13 +2389,141 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
             // feed_open, as laid out in QCtl; [12..13] head, tail of the ring (trace); [20..22] values to send; [32..] a chunk
             int *pin = w->pin;
             static_assert(offsetof(QCtl, feed_head) - offsetof(QCtl, pending) == 36 && offsetof(QCtl, feed_open) - offsetof(QCtl, pending) == 44, "relay snapshot layout");
+            static_assert(offsetof(QCtl, export_claim) - offsetof(QCtl, pending) == 52, "relay snapshot layout");
+            // ---- work sharing between the GPUs (see struct Share) ----
+            const bool sharing = share.on() && P.exp_list != nullptr;
+            std::vector<int> imp_slots, exp_free, ticket_dst, ticket_slot;
+            size_t imp_next = 0;
+            int granted = 0, processed = 0, n_exported = 0, n_imported = 0, n_requests = 0;
+            unsigned int my_mhead = 0;
+            auto t_last_req = t_launch;
+            if (sharing) {
+                const int ne = std::min<int>(SHARE_EXPORT_SLOTS, (int)resv.size() / 2);
+                exp_free.assign(resv.end() - ne, resv.end());
+                imp_slots.assign(resv.begin(), resv.end() - ne);
+                ticket_dst.assign(EXP_TICKETS, -1); ticket_slot.assign(EXP_TICKETS, -1);
+                my_mhead = (unsigned int)__atomic_load_n(share.mhead(rank), __ATOMIC_ACQUIRE);
+                ramped = false;
+            }
+            const int epoch = sharing ? __atomic_load_n((int *)(share.w + 7), __ATOMIC_ACQUIRE) : 0;
+            auto seq_of = [&](unsigned int ticket) { return (int)((unsigned int)epoch * 0x10000u + ticket + 1u); };
+            // a record from this rank's mailbox into a reserved slot of the device's pool, then into the feed
+            auto import_step = [&]() -> int {
+                for (;;) {
+                    if ((int)((unsigned int)__atomic_load_n(share.mtail(rank), __ATOMIC_ACQUIRE) - my_mhead) <= 0) break;
+                    unsigned char *e = share.slot(rank, my_mhead);
+                    if (__atomic_load_n((int *)e, __ATOMIC_ACQUIRE) != seq_of(my_mhead)) break;  // claimed, not written yet
+                    if (imp_next >= imp_slots.size()) break;  // no slot left: the record waits (nothing more is asked for)
+                    __atomic_store_n(share.idle(rank), 0, __ATOMIC_SEQ_CST);
+                    unsigned char *stage = w->rec_pin + RL.stride;
+                    memcpy(stage, e + 64, RL.stride);
+                    my_mhead++;
+                    __atomic_store_n(share.mhead(rank), (int)my_mhead, __ATOMIC_RELEASE);
+                    const int slot = imp_slots[imp_next++];
+                    pin[24] = slot; pin[21] = (int)fed + 1;
+                    CK(cudaMemcpyAsync(P.pool + (size_t)slot * RL.stride, stage, RL.stride, cudaMemcpyHostToDevice, w->stream2));
+                    CK(cudaMemcpyAsync(P.feed + fed, pin + 24, 4, cudaMemcpyHostToDevice, w->stream2));
+                    CK(cudaMemcpyAsync(&P.q->feed_tail, pin + 21, 4, cudaMemcpyHostToDevice, w->stream2));
+                    CK(cudaStreamSynchronize(w->stream2));
+                    fed++; n_imported++;
+                    __atomic_fetch_add(share.imported(), 1, __ATOMIC_SEQ_CST);
+                }
+                return 0;
+            };
+            // the record of export ticket t out of the device and into the mailbox of the rank that asked for it
+            auto deliver = [&](int t) -> int {
+                const int slot = ticket_slot[t], dst = ticket_dst[t];
+                CK(cudaMemcpyAsync(w->rec_pin, P.pool + (size_t)slot * RL.stride, RL.stride, cudaMemcpyDeviceToHost, w->stream2));
+                CK(cudaStreamSynchronize(w->stream2));
+                exp_free.push_back(slot);
+                if ((host_stop && *host_stop) || __atomic_load_n(share.left(dst), __ATOMIC_SEQ_CST)) return 0;  // the search is over
+                __atomic_fetch_add(share.exported(), 1, __ATOMIC_SEQ_CST);
+                const unsigned int ticket = (unsigned int)__atomic_fetch_add(share.mtail(dst), 1, __ATOMIC_SEQ_CST);
+                // room in the ring of `slots` entries; while waiting this rank keeps serving its own mailbox (no cycles)
+                while ((int)(ticket - (unsigned int)__atomic_load_n(share.mhead(dst), __ATOMIC_ACQUIRE)) >= share.slots) {
+                    if ((host_stop && *host_stop) || __atomic_load_n(share.left(dst), __ATOMIC_SEQ_CST)) return 0;
+                    if (import_step()) return 1;
+                    std::this_thread::sleep_for(std::chrono::microseconds(20));
+                }
+                unsigned char *e = share.slot(dst, ticket);
+                memcpy(e + 64, w->rec_pin, RL.stride);
+                __atomic_store_n((int *)e, seq_of(ticket), __ATOMIC_RELEASE);
+                n_exported++;
+                return 0;
+            };
+            auto share_poll = [&]() -> int {
+                const int pending = pin[0], idle = pin[1], claim = pin[13];
+                // exports the device has completed (the list is read after the snapshot, on the same stream)
+                while (processed < claim) {
+                    const int cnt = std::min(claim - processed, 960);
+                    CK(cudaMemcpyAsync(pin + 32, P.exp_list + processed, (size_t)cnt * 4, cudaMemcpyDeviceToHost, w->stream2));
+                    CK(cudaStreamSynchronize(w->stream2));
+                    int k = 0;
+                    while (k < cnt && pin[32 + k]) { if (deliver(processed)) return 1; processed++; k++; }
+                    if (k < cnt) break;  // a warp has its ticket but is still copying
+                }
+                if (import_step()) return 1;
+                if (told) return 0;
+                const auto now = std::chrono::steady_clock::now();
+                if (pin[1] > 0) seen_idle = true;
+                if (!ramped && ((seen_idle && idle * 8 < nwarps) || std::chrono::duration<double, std::milli>(now - t_launch).count() > 5.0)) ramped = true;
+                const bool mailbox_empty = (unsigned int)__atomic_load_n(share.mtail(rank), __ATOMIC_ACQUIRE) == my_mhead;
+                const bool is_done = __atomic_load_n(share.done(), __ATOMIC_SEQ_CST) != 0;
+                // ask: an eighth of the warps wait and nothing is on its way
+                const bool hungry = ramped && idle * 8 > nwarps && !is_done;
+                const int asked = __atomic_load_n(share.need(rank), __ATOMIC_SEQ_CST);
+                if (hungry && asked == 0 && mailbox_empty && imp_slots.size() - imp_next >= 32 &&
+                    std::chrono::duration<double, std::micro>(now - t_last_req).count() > 200.0) {
+                    __atomic_store_n(share.need(rank), std::min(16, std::max(2, idle / 64)), __ATOMIC_SEQ_CST);
+                    t_last_req = now; n_requests++;
+                } else if (!hungry && asked > 0) __atomic_store_n(share.need(rank), 0, __ATOMIC_SEQ_CST);
+                // give: every warp busy, records queued beyond them, few tickets still unclaimed
+                if (idle * 16 < nwarps && pending >= nwarps && granted - claim < 4 && !is_done) {
+                    for (int k = 1; k < world; ++k) {
+                        const int d = (rank + k) % world;
+                        int nd = __atomic_load_n(share.need(d), __ATOMIC_SEQ_CST);
+                        if (nd <= 0 || __atomic_load_n(share.left(d), __ATOMIC_SEQ_CST)) continue;
+                        const int c = std::min(std::min(nd, 2), std::min((int)exp_free.size(), EXP_TICKETS - granted));
+                        if (c <= 0) break;
+                        if (!__atomic_compare_exchange_n(share.need(d), &nd, nd - c, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) continue;
+                        for (int i = 0; i < c; ++i) {
+                            const int slot = exp_free.back(); exp_free.pop_back();
+                            ticket_dst[granted + i] = d; ticket_slot[granted + i] = slot; pin[24 + i] = slot;
+                        }
+                        pin[23] = granted + c;
+                        CK(cudaMemcpyAsync(P.exp_slots + granted, pin + 24, (size_t)c * 4, cudaMemcpyHostToDevice, w->stream2));
+                        CK(cudaMemcpyAsync(&P.q->export_want, pin + 23, 4, cudaMemcpyHostToDevice, w->stream2));
+                        CK(cudaStreamSynchronize(w->stream2));
+                        granted += c;
+                        break;
+                    }
+                }
+                // idle flag and the end of the search
+                const bool my_idle = pending == 0 && fed == (unsigned int)pin[9] && processed == claim && mailbox_empty;
+                __atomic_store_n(share.idle(rank), my_idle ? 1 : 0, __ATOMIC_SEQ_CST);
+                if (my_idle && !is_done) {
+                    const int e1 = __atomic_load_n(share.exported(), __ATOMIC_SEQ_CST);
+                    const int i1 = __atomic_load_n(share.imported(), __ATOMIC_SEQ_CST);
+                    if (e1 == i1 && share.all_idle() && __atomic_load_n(share.exported(), __ATOMIC_SEQ_CST) == e1)
+                        __atomic_store_n(share.done(), 1, __ATOMIC_SEQ_CST);
+                }
+                if (__atomic_load_n(share.done(), __ATOMIC_SEQ_CST) && !closed) {
+                    pin[22] = 0;
+                    CK(cudaMemcpyAsync(&P.q->feed_open, pin + 22, 4, cudaMemcpyHostToDevice, w->stream2));
+                    CK(cudaStreamSynchronize(w->stream2));
+                    closed = true;
+                    closed_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
+                }
+                return 0;
+            };
+            CK(cudaStreamWaitEvent(w->stream2, w->e0, 0));  // the snapshots below must see this launch's control block
             while (cudaEventQuery(w->e1) == cudaErrorNotReady) {
-                CK(cudaMemcpyAsync(pin, &P.q->pending, 48, cudaMemcpyDeviceToHost, w->stream2));
-                if (trace) CK(cudaMemcpyAsync(pin + 12, &P.q->head, 8, cudaMemcpyDeviceToHost, w->stream2));
+                CK(cudaMemcpyAsync(pin, &P.q->pending, 56, cudaMemcpyDeviceToHost, w->stream2));
+                if (trace) CK(cudaMemcpyAsync(pin + 14, &P.q->head, 8, cudaMemcpyDeviceToHost, w->stream2));
                 CK(cudaStreamSynchronize(w->stream2));
                 if (trace) {
                     const double t = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_launch).count();
-                    samples.push_back({t, pin[1], pin[0], (int)((unsigned int)pin[13] - (unsigned int)pin[12]), (int)fed});
+                    samples.push_back({t, pin[1], pin[0], (int)((unsigned int)pin[15] - (unsigned int)pin[14]), (int)fed});
                 }
                 if (host_stop && pin[4]) *host_stop = 1;
                 if (host_stop && *host_stop && !told) {
@@ -2294,6 +2531,11 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                     CK(cudaMemcpyAsync(&P.q->abort, pin + 20, 4, cudaMemcpyHostToDevice, w->stream2));
                     CK(cudaStreamSynchronize(w->stream2));
                     told = true;
+                }
+                if (sharing) {
+                    if (share_poll()) return BLTCU_STATUS_ERROR;
+                    std::this_thread::sleep_for(std::chrono::microseconds(40));
+                    continue;
                 }
                 // hungry: an eighth of the warps wait for work (on BLTCU_FEED_POLLS looks in a row, default 1).  Measured
                 // (profiles/r2_feed_policy.md): stricter tests, larger chunks and larger on-demand parts all lose, because
@@ -2347,6 +2589,11 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
             }
             (void)cudaGetLastError();
             fed_total += fed;
+            if (sharing) {
+                share.leave();
+                if (verbose) fprintf(stderr, "bltcu: rank %d asked %d times, took in %d records, handed out %d (%d tickets granted), feed closed after %.2f ms\n",
+                                     rank, n_requests, n_imported, n_exported, granted, closed_ms);
+            }
             if (trace && !samples.empty()) {
                 const double bin = std::max(1.0, samples.back().t / 40.0);
                 size_t i = 0;
@@ -2356,7 +2603,7 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                     if (cnt) fprintf(stderr, "bltcu: trace rank %d t %7.1f ms idle %6.0f of %d warps, pending %7.0f, ring %6.0f, fed %d\n", rank, t0, idle / cnt, nwarps, pend / cnt, ql / cnt, fedv);
                 }
             }
-            if (verbose && feeding)
+            if (verbose && feeding && !sharing)
                 fprintf(stderr, "bltcu: rank %d took %u of %zu on-demand subtrees, second request after %.2f ms, none left after %.2f ms\n", rank, fed,
                         dyn.size(), first_hungry_ms, closed_ms);
         }
@@ -2447,7 +2694,8 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
         if (const char *e = getenv("BLTCU_FEED_PCT")) if (shared) nstat = idx.size() - idx.size() * (size_t)std::min(95, std::max(1, atoi(e))) / 100;
         size_t dealt = 0;
         for (size_t i = 0; i < idx.size(); ++i) {
-            const bool on_demand = shared && (feed_tail ? i >= nstat : (i % (size_t)feed_div) == (size_t)feed_div - 1);
+            // (with a work-sharing block every subtree is dealt now and records move between the GPUs later)
+            const bool on_demand = shared && !share.on() && (feed_tail ? i >= nstat : (i % (size_t)feed_div) == (size_t)feed_div - 1);
             if (on_demand) dyn.push_back(out[idx[i]]);
             else if ((int)(dealt++ % (size_t)world) == rank) {
                 initial.push_back(out[idx[i]]);
@@ -2458,7 +2706,12 @@ static int search_impl(DevWs *w, const int64_t *d_lat, const int64_t *d_con, int
                 }
             }
         }
-        feeding = !dyn.empty();
+        feeding = !dyn.empty() || share.on();
+        if (share.on()) {
+            want_resv = std::min(2048 + SHARE_EXPORT_SLOTS, std::max(0, (pool_cap - (int)initial.size()) / 2));
+            P.exp_slots = (int *)(base + L.o_exp); P.exp_list = P.exp_slots + EXP_TICKETS;
+            CK(cudaMemsetAsync(P.exp_slots, 0, (size_t)2 * EXP_TICKETS * 4, st));
+        }
         const bool stop = (status != BLTCU_STATUS_OK) || (found && !o.no_early_exit && (hq.abort != 0)) || (host_stop && *host_stop);
         if (!stop && (!initial.empty() || feeding)) {
             if (reset_ctl(initial)) return BLTCU_STATUS_ERROR;
@@ -2575,8 +2828,13 @@ static int closest_one_device(const int64_t *lat, const int64_t *con, int n, int
 static int closest_multi_device(const int64_t *lat, const int64_t *con, int n, int m, const bltcu_opts &base, int gpus, int64_t *sol,
                                 bltcu_stats *stats) {
     const auto t0 = std::chrono::steady_clock::now();
-    int shared_words[16] = {0};  // [0] stop word, [1] counter of the subtrees dealt on demand (bltcu_opts.stop_flag)
-    int *flag = shared_words;
+    // the ranks' shared block (bltcu_opts.stop_flag): stop word, counter of the subtrees dealt on demand, and the
+    // mailboxes through which records move between the GPUs (struct Share, used when BLTCU_SHARE=1)
+    const size_t share_entry = 64 + ((rec_layout(n, m).stride + 63) / 64) * 64;
+    const size_t block_bytes = 4096 + (size_t)gpus * 8 * share_entry;
+    std::vector<unsigned long long> block((block_bytes + 7) / 8, 0ull);
+    int *flag = (int *)block.data();
+    flag[2] = (gpus <= Share::MAXW && block_bytes < (1ull << 31)) ? (int)block_bytes : 0;
     std::vector<bltcu_stats> st((size_t)gpus);
     std::vector<std::vector<int64_t>> sols((size_t)gpus, std::vector<int64_t>((size_t)n, 0));
     std::vector<int> rcs((size_t)gpus, BLTCU_STATUS_ERROR);
@@ -2924,6 +3182,7 @@ extern "C" void bltcu_release(void) {
         if (w->stream) cudaStreamDestroy(w->stream);
         if (w->stream2) cudaStreamDestroy(w->stream2);
         if (w->pin) cudaFreeHost(w->pin);
+        if (w->rec_pin) cudaFreeHost(w->rec_pin);
         delete w;
     }
     g_ws.clear();

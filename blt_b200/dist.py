@@ -72,7 +72,12 @@ class StopFlag:
     at the first point (closest.cc:300-312).  No collective is involved: torch.distributed only provides the barriers
     around reset()."""
 
-    def __init__(self, name: str | None = None):
+    HEADER_INTS = 1024   # the first 4096 bytes: flags and counters (search.cu, struct Share); mailboxes follow
+
+    def __init__(self, name: str | None = None, size_bytes: int = 16 << 20):
+        """size_bytes: 4096 gives the legacy block (stop word and on-demand counter only); anything larger also holds
+        the mailboxes through which the ranks' host threads pass subtree records between the GPUs (8 records per rank
+        when they fit)."""
         import ctypes
         import mmap
         import os
@@ -80,28 +85,35 @@ class StopFlag:
         import torch.distributed as dist
 
         self.rank = dist.get_rank() if dist.is_initialized() else 0
+        self.size = max(mmap.PAGESIZE, (int(size_bytes) + mmap.PAGESIZE - 1) // mmap.PAGESIZE * mmap.PAGESIZE)
         self.path = "/dev/shm/" + (name or f"bltcu_stop_{os.environ.get('MASTER_PORT', '0')}_{os.getuid()}")
         if self.rank == 0:
             fd = os.open(self.path, os.O_CREAT | os.O_RDWR | os.O_TRUNC, 0o600)
-            os.ftruncate(fd, mmap.PAGESIZE)
+            os.ftruncate(fd, self.size)
         if dist.is_initialized():
             dist.barrier()
         if self.rank != 0:
             fd = os.open(self.path, os.O_RDWR)
-        self._mm = mmap.mmap(fd, mmap.PAGESIZE)
+        self._mm = mmap.mmap(fd, self.size)
         os.close(fd)
-        self._words = (ctypes.c_int * 16).from_buffer(self._mm)   # [0] stop word, [1] on-demand subtree counter
+        # [0] stop word, [1] on-demand subtree counter, [2] bytes of the block, [7] epoch of the mailbox sequence numbers
+        self._words = (ctypes.c_int * self.HEADER_INTS).from_buffer(self._mm)
         self.address = ctypes.addressof(self._words)
+        self._epoch = 0
 
     def reset(self):
-        """Zeroes the word; collective (every rank calls it before the search starts)."""
+        """Zeroes the header and starts a new epoch; collective (every rank calls it before the search starts)."""
+        import ctypes
+
         import torch.distributed as dist
 
         if dist.is_initialized():
             dist.barrier()
         if self.rank == 0:
-            for i in range(16):
-                self._words[i] = 0
+            self._epoch = (self._epoch + 1) & 0x7fff
+            ctypes.memset(self.address, 0, 4 * self.HEADER_INTS)
+            self._words[2] = self.size if self.size > 4096 else 0
+            self._words[7] = self._epoch
         if dist.is_initialized():
             dist.barrier()
 

@@ -54,7 +54,14 @@ typedef struct bltcu_opts {
                             last eighth of the split's subtrees in small chunks, whoever has idle warps (load balance
                             between GPUs; the rest is dealt i % world).  GPUs never access the block; each rank's host
                             thread relays between it and its device while the kernel runs.  NULL = static deal only,
-                            each rank stops only on its own find */
+                            each rank stops only on its own find.
+                            A LARGER block (its size in bytes in word 2, words 3..1023 zeroed, word 7 an epoch number that
+                            changes from search to search; at most 16 ranks) also holds one mailbox per rank behind the
+                            first 4096 bytes; with BLTCU_SHARE=1 in the environment the ranks then pass subtree records
+                            to each other through it while they search (a rank that runs dry asks, the warps of a busy
+                            one hand over the oldest records of their stacks, every copy made by the host threads), and
+                            no part of the split is dealt on demand.  Results do not depend on it.
+                            blt_b200.dist.StopFlag and bltcu_closest_ex(gpus > 1) make such a block */
 } bltcu_opts;
 
 /* Statistics of one search.  niter/nprune are SolverStats of libblt/closest.h:14-17. */

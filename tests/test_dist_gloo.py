@@ -143,6 +143,7 @@ def _flag_worker(rank, world, port, q):
     flag = StopFlag(name=f"bltcu_test_{port}")
     flag.reset()
     words = (ctypes.c_int * 16).from_address(flag.address)
+    size_word, epoch1 = int(words[2]), int(words[7])   # bytes of the block (mailboxes beyond the header), mailbox epoch
     if rank == 1:
         words[0] = 1                      # what the finder's host thread does
     dist.barrier()
@@ -160,13 +161,15 @@ def _flag_worker(rank, world, port, q):
     total = int(words[1])
     flag.reset()
     cleared = flag.value
+    assert size_word == flag.size == 16 << 20 and int(words[2]) == size_word and int(words[7]) == epoch1 + 1
     q.put((rank, seen, sorted(mine), total, cleared))
     flag.close()
     dist.destroy_process_group()
 
 
 def test_shared_block_is_visible_to_both_ranks():
-    """blt_b200.dist.StopFlag: the 16-int block of bltcu_opts.stop_flag in POSIX shared memory (one process per GPU)."""
+    """blt_b200.dist.StopFlag: the block of bltcu_opts.stop_flag in POSIX shared memory (one process per GPU): stop word,
+    on-demand counter, and the size and epoch words that describe the mailboxes behind the header."""
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29100 + os.getpid() % 150

@@ -75,6 +75,25 @@ def test_one_process_two_gpus_exhaustive(gpu, golden):
     assert (got["sol"] == z["sol"]).all()
 
 
+def test_records_shared_between_two_gpus(gpu, golden, monkeypatch):
+    """BLTCU_SHARE=1: a GPU that runs dry asks, the other one's warps hand records over through the host threads
+    (search.cu, struct Share), and the search ends when every rank is idle and every record sent has arrived.  Whatever
+    moves where, counts, histogram, pivots and uhat are those of the oracle, twice in a row."""
+    if _device_count() < 2:
+        pytest.skip("needs two GPUs")
+    monkeypatch.setenv("BLTCU_SHARE", "1")
+    z = np.load(f"{golden}/bench_dense60.npz")
+    for _ in range(2):
+        got = gpu.closest(z["lat"], z["con"], gpus=2, timeout_ms=300000)
+        assert got["rc"] == 0 and not got["found"] and got["gpus"] == 2
+        assert got["niter"] == int(z["niter"]) and got["nprune"] == int(z["nprune"]) and got["nodes"] == int(z["nodes"])
+        assert (got["hist"] == z["hist"]).all() and got["pivots"] == int(z["pivots"])
+        assert (got["sol"] == z["sol"]).all()
+    lat, con = _sat_instance()
+    got = gpu.closest(lat, con, gpus=2)
+    assert got["rc"] == 0 and got["found"] and oracle.check_soln(lat, con, got["sol"])
+
+
 def test_one_process_two_gpus_sat_and_blt_check(gpu, monkeypatch):
     """A SAT instance over two GPUs returns a valid point; BLT_GPUS makes blt_check() do the same behind blt.h."""
     if _device_count() < 2:
