@@ -981,6 +981,29 @@ __device__ __forceinline__ void copy_words(void *dst, const void *src, size_t by
     }
 }
 // writes the record of an explored child (children level k-1) whose vertex is the current working state
+// Takes an export ticket if the host has granted one (QCtl::export_want) and copies the record there; 1 if it did.
+__device__ __noinline__ int export_oldest(QCtl *q, const int *exp_slots, int *exp_list, unsigned char *pool, size_t stride,
+                                          const unsigned char *src, size_t bytes, int lane) {
+    int ticket = -1, eslot = -1;
+    if (lane == 0) {
+        const int want = *(volatile int *)&q->export_want;
+        int c = *(volatile int *)&q->export_claim;
+        while (c < want) {
+            const int old = atomicCAS(&q->export_claim, c, c + 1);
+            if (old == c) { ticket = c; eslot = ((const volatile int *)exp_slots)[c]; break; }
+            c = old;
+        }
+    }
+    ticket = __shfl_sync(FULLMASK, ticket, 0);
+    eslot = __shfl_sync(FULLMASK, eslot, 0);
+    if (ticket < 0) return 0;
+    copy_words(pool + (size_t)eslot * stride, src, bytes, lane);
+    __syncwarp();
+    __threadfence_system();
+    if (lane == 0) ((volatile int *)exp_list)[ticket] = 1;
+    return 1;
+}
+
 __device__ __forceinline__ void write_child(const Params &P, const RecLayout &RL, WS &s, unsigned char *C, int k, double xlast,
                                             double gn) {
     const int n = P.n, m = P.m, lane = s.lane, qd = s.qd;
@@ -1464,26 +1487,10 @@ __global__ void __launch_bounds__(384, 1) bltcu_search_kernel(const Params P) {
         }
         { const unsigned long long t = gtimer(); if (lane == 0) s.ctr[C_BUSY_NS] += t - t_mark; t_mark = t; }
         // another GPU of the search asked for work: the oldest record of the stack goes into the slot its ticket names
+        // (a call, so that searches without a work-sharing block carry one uniform test here and nothing else)
         if (P.exp_list && A.acount > A.abot) {
-            int ticket = -1, eslot = -1;
-            if (lane == 0) {
-                const int want = *(volatile int *)&q->export_want;
-                int c = *(volatile int *)&q->export_claim;
-                while (c < want) {
-                    const int old = atomicCAS(&q->export_claim, c, c + 1);
-                    if (old == c) { ticket = c; eslot = ((volatile int *)P.exp_slots)[c]; break; }
-                    c = old;
-                }
-            }
-            ticket = __shfl_sync(FULLMASK, ticket, 0);
-            eslot = __shfl_sync(FULLMASK, eslot, 0);
-            if (ticket >= 0) {
-                const unsigned char *src = A.base + A.offs[A.abot];
-                const size_t bytes = (size_t)(A.offs[A.abot + 1] - A.offs[A.abot]);
-                copy_words(P.pool + (size_t)eslot * RL.stride, src, bytes, lane);
-                __syncwarp();
-                __threadfence_system();
-                if (lane == 0) ((volatile int *)P.exp_list)[ticket] = 1;
+            if (export_oldest(q, P.exp_slots, P.exp_list, P.pool, RL.stride, A.base + A.offs[A.abot],
+                              (size_t)(A.offs[A.abot + 1] - A.offs[A.abot]), lane)) {
                 A.abot++;
                 CTR(s, C_DONATED);
                 if (A.acount == A.abot) { A.acount = 0; A.abot = 0; if (lane == 0) A.offs[0] = 0; }
