@@ -2838,10 +2838,11 @@ static int closest_multi_device(const int64_t *lat, const int64_t *con, int n, i
     // the ranks' shared block (bltcu_opts.stop_flag): stop word, counter of the subtrees dealt on demand, and the
     // mailboxes through which records move between the GPUs (struct Share, used when BLTCU_SHARE=1)
     const size_t share_entry = 64 + ((rec_layout(n, m).stride + 63) / 64) * 64;
-    const size_t block_bytes = 4096 + (size_t)gpus * 8 * share_entry;
+    const char *share_env = getenv("BLTCU_SHARE");
+    const size_t block_bytes = 4096 + ((share_env && atoi(share_env)) ? (size_t)gpus * 8 * share_entry : 0);
     std::vector<unsigned long long> block((block_bytes + 7) / 8, 0ull);
     int *flag = (int *)block.data();
-    flag[2] = (gpus <= Share::MAXW && block_bytes < (1ull << 31)) ? (int)block_bytes : 0;
+    flag[2] = (block_bytes > 4096 && gpus <= Share::MAXW && block_bytes < (1ull << 31)) ? (int)block_bytes : 0;
     std::vector<bltcu_stats> st((size_t)gpus);
     std::vector<std::vector<int64_t>> sols((size_t)gpus, std::vector<int64_t>((size_t)n, 0));
     std::vector<int> rcs((size_t)gpus, BLTCU_STATUS_ERROR);
