@@ -29,12 +29,12 @@
 namespace lllfp {
 
 struct HostLanes {
-    int lane() const { return 0; }
-    int width() const { return 1; }
-    void sync() const {}
-    double sum(double x) const { return x; }
-    int any(int x) const { return x; }
-    double bcast(double x, int) const { return x; }
+    LLLFP_HD int lane() const { return 0; }
+    LLLFP_HD int width() const { return 1; }
+    LLLFP_HD void sync() const {}
+    LLLFP_HD double sum(double x) const { return x; }
+    LLLFP_HD int any(int x) const { return x; }
+    LLLFP_HD double bcast(double x, int) const { return x; }
 };
 #if defined(__CUDACC__)
 struct WarpLanes {
