@@ -593,6 +593,19 @@ static uint64_t g_inband = 0;
 void oracle_set_sound(double margin) { g_sound_margin = margin; }
 uint64_t oracle_inband(void) { return g_inband; }
 
+#ifdef ORACLE_CENSUS
+/* Study aid (profiles/census_study.py compiles its own copy with -DORACLE_CENSUS; the checker is built without it):
+ * sizes of the subtrees below the explored nodes of one level, and how many of their nodes lie within `near`
+ * levels of the root. */
+static int g_census_level = 0, g_census_near = 2, g_census_cap = 0, g_census_count = 0, g_census_cur = -1;
+static uint64_t *g_census_size = 0, *g_census_probe = 0;
+void oracle_set_census(int level, int near, uint64_t *size, uint64_t *probe, int cap) {
+    g_census_level = level; g_census_near = near; g_census_size = size; g_census_probe = probe; g_census_cap = cap;
+    g_census_count = 0; g_census_cur = -1;
+}
+int oracle_census_count(void) { return g_census_count; }
+#endif
+
 int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t *sol, uint64_t *niter_out,
                    uint64_t *nprune_out, uint64_t *hist, uint64_t *stats, uint64_t max_nodes) {
     if (n <= 0 || m <= 0 || m < n) return BLT_STATUS_INPUT_ERROR; /* closest.cc:173-177 */
@@ -673,6 +686,12 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
         int status, side = 0;
         nodes++;
         if (hist) hist[k - 1]++;
+#ifdef ORACLE_CENSUS
+        if (g_census_size) {
+            if (k >= g_census_level) g_census_cur = -1;
+            else if (g_census_cur >= 0) { g_census_size[g_census_cur]++; if (k >= g_census_level - g_census_near) g_census_probe[g_census_cur]++; }
+        }
+#endif
         if (k == 1) { /* LP(0): plain max-abs */
             d = cmax;
             status = approximatelyLE(d, radius, DIST_EPS) ? NODE_EXPLORE : NODE_PRUNE;
@@ -724,6 +743,11 @@ int oracle_closest(const int64_t *lat, const int64_t *con, int n, int m, int64_t
             goto done;
         }
         /* explore */
+#ifdef ORACLE_CENSUS
+        if (g_census_size && k == g_census_level && g_census_count < g_census_cap) {
+            g_census_cur = g_census_count++; g_census_size[g_census_cur] = 0; g_census_probe[g_census_cur] = 0;
+        }
+#endif
         if (k > 1) { /* descend, closest.cc:88-95 */
             curside[k] = side;
             memcpy(cparL[k - 1], c, (size_t)m * sizeof(double));
